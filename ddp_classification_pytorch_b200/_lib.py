@@ -1,0 +1,121 @@
+"""ctypes binding of ``libarcface_b200.so`` (the C ABI in ``include/arcface_b200.h``).
+
+The shared library is built in-tree by :func:`build` (``nvcc`` for sm_100a) and lives next to
+this file so that it travels with the repository snapshot.  There is deliberately no fallback:
+if the library is missing or a call fails, a ``RuntimeError`` is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import shutil
+import subprocess
+import threading
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_PKG_DIR)
+LIB_PATH = os.path.join(_PKG_DIR, "libarcface_b200.so")
+_SRC = os.path.join(_PKG_DIR, "csrc", "arcface_b200.cu")
+_HDRS = [
+    os.path.join(_PKG_DIR, "csrc", n) for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "epilogues.cuh", "rowwise.cuh")
+] + [os.path.join(_ROOT, "include", "arcface_b200.h")]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-shared", "-Xcompiler", "-fPIC",
+]
+
+# every symbol include/arcface_b200.h declares (checked by the CPU test-suite)
+EXPORTED = [
+    "arcb_version", "arcb_last_error", "arcb_check_watchdog", "arcb_l2norm_rows", "arcb_l2norm_rows_bwd",
+    "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
+    "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim",
+]
+
+_lock = threading.Lock()
+_lib = None
+
+
+def _nvcc() -> str:
+    exe = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(exe):
+        raise RuntimeError("nvcc not found: cannot build libarcface_b200.so")
+    return exe
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    built = os.path.getmtime(LIB_PATH)
+    return any(os.path.getmtime(p) > built for p in [_SRC] + _HDRS)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile the CUDA extension for sm_100a in-tree.  Returns the library path."""
+    if not force and not needs_build():
+        return LIB_PATH
+    cmd = [_nvcc()] + NVCC_FLAGS + ["-I", os.path.join(_ROOT, "include"), "-o", LIB_PATH, _SRC]
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+def _declare(lib):
+    c = ctypes
+    vp, i64, i32, f32 = c.c_void_p, c.c_int64, c.c_int, c.c_float
+    lib.arcb_version.restype = i32
+    lib.arcb_version.argtypes = []
+    lib.arcb_last_error.restype = c.c_char_p
+    lib.arcb_last_error.argtypes = []
+    lib.arcb_check_watchdog.restype = i32
+    lib.arcb_check_watchdog.argtypes = [vp]
+    lib.arcb_padded_dim.restype = i64
+    lib.arcb_padded_dim.argtypes = [i64]
+    lib.arcb_l2norm_rows.restype = i32
+    lib.arcb_l2norm_rows.argtypes = [vp, i64, i64, i64, vp, i64, vp, vp]
+    lib.arcb_l2norm_rows_bwd.restype = i32
+    lib.arcb_l2norm_rows_bwd.argtypes = [vp, i64, vp, i64, i64, i64, vp, i64, vp]
+    lib.arcb_gemm_bf16.restype = i32
+    lib.arcb_gemm_bf16.argtypes = [vp, i32, vp, i32, i64, i64, i64, i64, i64, vp, i64, i32, vp]
+    lib.arcb_ws_bytes.restype = i64
+    lib.arcb_ws_bytes.argtypes = [i64, i64, i64]
+    lib.arcb_scratch_bytes.restype = i64
+    lib.arcb_scratch_bytes.argtypes = [i64, i64]
+    fwd_args = [vp, i64, vp, i64, vp, i64, i64, i64, i64, f32, f32, i32, vp, i64]
+    lib.arcb_shard_forward.restype = i32
+    lib.arcb_shard_forward.argtypes = fwd_args + [vp, vp]
+    lib.arcb_shard_logits.restype = i32
+    lib.arcb_shard_logits.argtypes = fwd_args + [vp, i64, vp]
+    lib.arcb_merge_loss.restype = i32
+    lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
+    lib.arcb_shard_backward.restype = i32
+    lib.arcb_shard_backward.argtypes = [i64, i64, i64, f32, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp]
+
+
+def lib():
+    """The loaded library.  Raises RuntimeError when it has not been built (no fallback path)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(
+                    f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                    "(the ArcFace head has no CPU or eager-PyTorch fallback)")
+            handle = ctypes.CDLL(LIB_PATH)
+            _declare(handle)
+            _lib = handle
+    return _lib
+
+
+def check(rc: int, what: str = "arcface_b200") -> None:
+    if rc != 0:
+        msg = lib().arcb_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")

@@ -1,0 +1,340 @@
+// C ABI of the B200-native ArcFace head.  See include/arcface_b200.h for the contract and the
+// reference lines (ARCFACE/arc_main.py) each entry point replaces.
+//
+// Build (in-tree, see __graft_entry__.build()):
+//   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC \
+//        -Iinclude -o ddp_classification_pytorch_b200/libarcface_b200.so csrc/arcface_b200.cu
+#include "../../include/arcface_b200.h"
+
+#include <cuda_bf16.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "epilogues.cuh"
+#include "gemm_sm100.cuh"
+#include "rowwise.cuh"
+
+using namespace arcb;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define ARCB_CUDA(expr)                                                                        \
+  do {                                                                                         \
+    cudaError_t e_ = (expr);                                                                   \
+    if (e_ != cudaSuccess) return fail(ARCB_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+constexpr int kBNTile = 256;
+
+// Persistent per-shard workspace, carved deterministically from one caller-owned buffer.
+struct Workspace {
+  int64_t B, Cs, D, Bp, Dp;
+  __nv_bfloat16* xhat;   // [B, Dp]
+  __nv_bfloat16* what;   // [Cs, Dp]
+  float* inv_nx;         // [Bp]
+  float* inv_nw;         // [Cs]
+  int* lbl_local;        // [Bp]
+  float* sub;            // [Bp]
+  float* zt;             // [Bp]
+  float* dphi;           // [Bp]
+  float* cos_t;          // [Bp]
+  unsigned char* tile_flag;  // [ceil(Cs/128)]
+  float2* part;          // [tiles_n, Bp]
+  float2* rec;           // [Bp]
+  float* lse2;           // [Bp]
+  float* zt2;            // [Bp]
+  float* gscale;         // [1]
+  float* tproj;          // [Cs]
+  int64_t total;
+};
+
+Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
+  Workspace w;
+  w.B = B; w.Cs = Cs; w.D = D;
+  w.Bp = round_up(B, kBNTile);
+  w.Dp = round_up(D, 64);
+  const int64_t tiles_n = (Cs + kBNTile - 1) / kBNTile;
+  char* p = reinterpret_cast<char*>(base);
+  int64_t off = 0;
+  auto take = [&](int64_t bytes) {
+    char* r = p ? p + off : nullptr;
+    off += round_up(bytes, 256);
+    return r;
+  };
+  w.xhat = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
+  w.what = reinterpret_cast<__nv_bfloat16*>(take(Cs * w.Dp * 2));
+  w.inv_nx = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.inv_nw = reinterpret_cast<float*>(take(Cs * 4));
+  w.lbl_local = reinterpret_cast<int*>(take(w.Bp * 4));
+  w.sub = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.zt = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.dphi = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.cos_t = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.tile_flag = reinterpret_cast<unsigned char*>(take((Cs + 127) / 128));
+  w.part = reinterpret_cast<float2*>(take(tiles_n * w.Bp * 8));
+  w.rec = reinterpret_cast<float2*>(take(w.Bp * 8));
+  w.lse2 = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.zt2 = reinterpret_cast<float*>(take(w.Bp * 4));
+  w.gscale = reinterpret_cast<float*>(take(4));
+  w.tproj = reinterpret_cast<float*>(take(Cs * 4));
+  w.total = off;
+  return w;
+}
+
+int check_dims(int64_t B, int64_t Cs, int64_t D) {
+  if (B <= 0 || Cs <= 0 || D <= 0) return fail(ARCB_ERR_INVALID, "B, Cs, D must be positive (got %lld, %lld, %lld)",
+                                                (long long)B, (long long)Cs, (long long)D);
+  if (B > (1ll << 30) || Cs > (1ll << 30) || D > (1 << 20))
+    return fail(ARCB_ERR_INVALID, "size out of range (B=%lld, Cs=%lld, D=%lld)", (long long)B, (long long)Cs,
+                (long long)D);
+  return ARCB_OK;
+}
+
+int launch_l2norm(const float* x, int64_t rows, int64_t D, int64_t ldx, __nv_bfloat16* out, int64_t Dp, float* inv,
+                  cudaStream_t st) {
+  if (rows == 0) return ARCB_OK;
+  const int warps_per_block = 8;
+  int64_t blocks = (rows + warps_per_block - 1) / warps_per_block;
+  if (blocks > 148 * 64) blocks = 148 * 64;  // grid-stride beyond that
+  const bool vec = (D % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+  const int g = static_cast<int>(blocks);
+#define ARCB_L2N(NV) l2norm_rows_kernel<NV><<<g, 256, 0, st>>>(x, rows, (int)D, ldx, out, (int)Dp, inv)
+  if (vec && Dp <= 128) ARCB_L2N(1);
+  else if (vec && Dp <= 256) ARCB_L2N(2);
+  else if (vec && Dp <= 512) ARCB_L2N(4);
+  else if (vec && Dp <= 1024) ARCB_L2N(8);
+  else if (vec && Dp <= 2048) ARCB_L2N(16);
+  else ARCB_L2N(0);
+#undef ARCB_L2N
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
+// Steps shared by the fused and the materialising forward: normalise, target preparation.
+int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                   int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy, void* ws_ptr,
+                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st) {
+  int rc = check_dims(B, Cs, D);
+  if (rc) return rc;
+  if (!x || !w || !labels || !ws_ptr) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (ldx < D || ldw < D) return fail(ARCB_ERR_INVALID, "leading dimension smaller than D");
+  if (!(s > 0.f)) return fail(ARCB_ERR_INVALID, "scale s must be positive (got %g)", (double)s);
+  if (reinterpret_cast<uintptr_t>(ws_ptr) & 255) return fail(ARCB_ERR_INVALID, "workspace must be 256-byte aligned");
+  Workspace W = carve(ws_ptr, B, Cs, D);
+  if (W.total > ws_bytes)
+    return fail(ARCB_ERR_WORKSPACE, "workspace too small: need %lld bytes, got %lld", (long long)W.total,
+                (long long)ws_bytes);
+  rc = launch_l2norm(x, B, D, ldx, W.xhat, W.Dp, W.inv_nx, st);
+  if (rc) return rc;
+  rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st);
+  if (rc) return rc;
+  ARCB_CUDA(cudaMemsetAsync(W.tile_flag, 0, (Cs + 127) / 128, st));
+  const double md = static_cast<double>(m);
+  const float cos_m = static_cast<float>(cos(md)), sin_m = static_cast<float>(sin(md));
+  const float th = static_cast<float>(cos(M_PI - md)), mm = static_cast<float>(sin(M_PI - md) * md);
+  const int blocks = static_cast<int>((W.Bp + 7) / 8);
+  target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.inv_nx, W.inv_nw, (int)B, (int)W.Bp, (int)D, Cs,
+                                             class_offset, s, cos_m, sin_m, th, mm, easy, W.lbl_local, W.sub, W.zt,
+                                             W.dphi, W.cos_t, W.tile_flag);
+  ARCB_CUDA(cudaGetLastError());
+  *out_ws = W;
+  return ARCB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int arcb_version(void) { return 100; }
+
+const char* arcb_last_error(void) { return g_err; }
+
+int arcb_check_watchdog(void* stream) {
+  ARCB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  unsigned int h[4] = {0, 0, 0, 0};
+  ARCB_CUDA(cudaMemcpyFromSymbol(h, g_wait_timeout, sizeof(h)));
+  if (h[0]) {
+    unsigned int z[4] = {0, 0, 0, 0};
+    cudaMemcpyToSymbol(g_wait_timeout, z, sizeof(z));
+    return fail(ARCB_ERR_TIMEOUT, "pipeline watchdog fired: barrier tag 0x%x, block %u, parity %u", h[1], h[2], h[3]);
+  }
+  return ARCB_OK;
+}
+
+int64_t arcb_padded_dim(int64_t D) { return round_up(D, 64); }
+
+int arcb_l2norm_rows(const float* x, int64_t rows, int64_t D, int64_t ldx, void* out_bf16, int64_t Dp, float* inv_norm,
+                     void* stream) {
+  if (!x || !out_bf16 || !inv_norm) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (rows < 0 || D <= 0 || ldx < D || Dp < D || Dp % 64) return fail(ARCB_ERR_INVALID, "bad sizes for l2norm_rows");
+  return launch_l2norm(x, rows, D, ldx, static_cast<__nv_bfloat16*>(out_bf16), Dp, inv_norm,
+                       static_cast<cudaStream_t>(stream));
+}
+
+int arcb_l2norm_rows_bwd(const float* x, int64_t ldx, const float* dxhat, int64_t ldg, int64_t rows, int64_t D,
+                         float* dx, int64_t ldo, void* stream) {
+  if (!x || !dxhat || !dx) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (rows <= 0 || D <= 0 || ldx < D || ldg < D || ldo < D) return fail(ARCB_ERR_INVALID, "bad sizes");
+  const int blocks = static_cast<int>((rows + 7) / 8);
+  l2norm_rows_bwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, ldx, dxhat, ldg, (int)rows, (int)D,
+                                                                               dx, ldo);
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
+int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, int64_t N, int64_t K, int64_t lda,
+                   int64_t ldb, float* out, int64_t ldo, int split_k, void* stream) {
+  if (!A || !B || !out) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (M <= 0 || N <= 0 || K <= 0 || (lda % 8) || (ldb % 8)) return fail(ARCB_ERR_INVALID, "bad GEMM sizes");
+  Operand a{A, M, K, lda}, b{B, N, K, ldb};
+  EpiStore::Params ep{out, ldo, (int)M, (int)N, split_k > 1 ? 1 : 0};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e;
+  if (!a_mn && !b_mn) e = launch_gemm<EpiStore, 256, 4, false, false>(a, b, nullptr, M, N, K, split_k, ep, st);
+  else if (a_mn && !b_mn) e = launch_gemm<EpiStore, 256, 4, true, false>(a, b, nullptr, M, N, K, split_k, ep, st);
+  else if (!a_mn && b_mn) e = launch_gemm<EpiStore, 256, 4, false, true>(a, b, nullptr, M, N, K, split_k, ep, st);
+  else e = launch_gemm<EpiStore, 256, 4, true, true>(a, b, nullptr, M, N, K, split_k, ep, st);
+  if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "gemm launch: %s", cudaGetErrorString(e));
+  return ARCB_OK;
+}
+
+int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D) {
+  if (B <= 0 || Cs <= 0 || D <= 0) return -1;
+  return carve(nullptr, B, Cs, D).total;
+}
+
+int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes) {
+  if (B <= 0 || chunk_classes <= 0) return -1;
+  return round_up(chunk_classes, 128) * round_up(B, kBNTile) * 2;
+}
+
+int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                       int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                       int64_t ws_bytes, float* stats, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!stats) return fail(ARCB_ERR_INVALID, "null stats pointer");
+  Workspace W;
+  int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st);
+  if (rc) return rc;
+  Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
+  EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
+  cudaError_t e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+  if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
+  const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
+  const int blocks = static_cast<int>((B + 255) / 256);
+  merge_stats_kernel<<<blocks, 256, 0, st>>>(W.part, tiles_n, W.Bp, (int)B, W.rec);
+  pack_stats_kernel<<<blocks, 256, 0, st>>>(W.rec, W.zt, (int)B, stats);
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
+int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                      int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                      int64_t ws_bytes, float* logits, int64_t ldl, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!logits || ldl < Cs) return fail(ARCB_ERR_INVALID, "bad logits buffer");
+  Workspace W;
+  int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st);
+  if (rc) return rc;
+  Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
+  EpiLogits::Params ep{W.lbl_local, W.sub, logits, ldl, (int)B, (int)Cs, s};
+  cudaError_t e = launch_gemm<EpiLogits, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+  if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "logits GEMM launch: %s", cudaGetErrorString(e));
+  return ARCB_OK;
+}
+
+int arcb_merge_loss(const float* stats, int64_t P, int64_t B, float* lse, float* target_logit, float* loss,
+                    void* stream) {
+  if (!stats || !lse || !loss) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (P <= 0 || B <= 0) return fail(ARCB_ERR_INVALID, "bad sizes for merge_loss");
+  loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(stats, (int)P, (int)B, lse, target_logit, loss);
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
+int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int64_t ws_bytes, const float* lse,
+                        const float* target_logit, const float* grad_loss, const float* grad_logits, int64_t ldgl,
+                        void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_dims(B, Cs, D);
+  if (rc) return rc;
+  if (!ws || !scratch || !dw || !dxhat) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  const bool ext = grad_logits != nullptr;
+  if (!ext && (!lse || !target_logit)) return fail(ARCB_ERR_INVALID, "lse / target_logit required");
+  if (ext && ldgl < Cs) return fail(ARCB_ERR_INVALID, "grad_logits leading dimension smaller than Cs");
+  if (reinterpret_cast<uintptr_t>(scratch) & 1023) return fail(ARCB_ERR_INVALID, "scratch must be 1024-byte aligned");
+  Workspace W = carve(ws, B, Cs, D);
+  if (W.total > ws_bytes) return fail(ARCB_ERR_WORKSPACE, "workspace too small");
+  int64_t chunk = scratch_bytes / (W.Bp * 2) / 128 * 128;
+  if (chunk < 128)
+    return fail(ARCB_ERR_WORKSPACE, "scratch too small: need at least %lld bytes", (long long)(128 * W.Bp * 2));
+  if (chunk > round_up(Cs, 128)) chunk = round_up(Cs, 128);
+  __nv_bfloat16* gt = static_cast<__nv_bfloat16*>(scratch);
+
+  if (!ext) {
+    const int blocks = static_cast<int>((W.Bp + 255) / 256);
+    bwd_prep_kernel<<<blocks, 256, 0, st>>>(lse, target_logit, grad_loss, s, (int)B, (int)W.Bp, W.lse2, W.zt2,
+                                            W.gscale);
+    ARCB_CUDA(cudaGetLastError());
+  }
+  ARCB_CUDA(cudaMemsetAsync(W.tproj, 0, Cs * 4, st));
+  ARCB_CUDA(cudaMemsetAsync(dxhat, 0, B * W.Dp * 4, st));
+
+  const int sms = device_sm_count();
+  for (int64_t c0 = 0; c0 < Cs; c0 += chunk) {
+    const int64_t rows = (Cs - c0 < chunk) ? (Cs - c0) : chunk;
+    const __nv_bfloat16* wch = W.what + c0 * W.Dp;
+    // (1) recompute cos^T for the chunk, write G^T = dLoss/dcos (bf16) and the projections t_j
+    {
+      CUtensorMap tmG;
+      if (!make_tmap_2d(&tmG, gt, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W.Bp, rows, W.Bp * 2, 64, kBM))
+        return fail(ARCB_ERR_CUDA, "tensor map for the G^T scratch could not be encoded");
+      Operand a{wch, rows, W.Dp, W.Dp}, b{W.xhat, B, W.Dp, W.Dp};
+      cudaError_t e;
+      if (!ext) {
+        EpiBwdG<false>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tile_flag, W.tproj,
+                                  (int)c0, (int)rows, (int)B, (int)W.Bp, s * kLog2e, nullptr, 0, 0.f};
+        e = launch_gemm<EpiBwdG<false>, kBNTile, 3, false, false>(a, b, &tmG, rows, B, W.Dp, 1, ep, st);
+      } else {
+        EpiBwdG<true>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tile_flag, W.tproj,
+                                 (int)c0, (int)rows, (int)B, (int)W.Bp, s * kLog2e, grad_logits + c0, ldgl, s};
+        e = launch_gemm<EpiBwdG<true>, kBNTile, 3, false, false>(a, b, &tmG, rows, B, W.Dp, 1, ep, st);
+      }
+      if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "backward recompute GEMM launch: %s", cudaGetErrorString(e));
+    }
+    // (2) dxhat[B, D] += G[B, rows] * what[rows, D]      (both operands have the class index slowest)
+    {
+      Operand a{gt, W.Bp, rows, W.Bp}, b{wch, W.Dp, rows, W.Dp};
+      const int tiles = static_cast<int>(((B + kBM - 1) / kBM) * ((D + kBNTile - 1) / kBNTile));
+      int split = sms / (tiles > 0 ? tiles : 1);
+      if (split < 1) split = 1;
+      EpiRedAdd::Params ep{dxhat, W.Dp, (int)B, (int)D};
+      cudaError_t e = launch_gemm<EpiRedAdd, kBNTile, 4, true, true>(a, b, nullptr, B, D, rows, split, ep, st);
+      if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
+    }
+    // (3) dW[rows, D] = inv_norm * (G^T[rows, B] * xhat[B, D] - t * what)
+    {
+      Operand a{gt, rows, W.Bp, W.Bp}, b{W.xhat, W.Dp, B, W.Dp};
+      EpiDW::Params ep{dw, W.what, W.tproj, W.inv_nw, (int)c0, (int)rows, (int)D, (int)W.Dp};
+      cudaError_t e = launch_gemm<EpiDW, kBNTile, 4, false, true>(a, b, nullptr, rows, D, B, 1, ep, st);
+      if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
+    }
+  }
+  return ARCB_OK;
+}
+
+}  // extern "C"

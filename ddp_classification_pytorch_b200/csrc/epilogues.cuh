@@ -1,0 +1,417 @@
+// Epilogue policies for gemm_sm100_kernel.  Each thread owns ONE accumulator row (a TMEM lane)
+// and walks the tile's BN columns in chunks of 32 fp32 values pulled with tcgen05.ld.
+//
+//   EpiStore      plain fp32 store (unit tests of the GEMM core)
+//   EpiFwdStats   forward: margin substitution at the label column, online (max, sum-exp)
+//                 -> the B x C logits never leave the SM            (arc_main.py:160-172 + :245/:327)
+//   EpiLogits     forward, materialising: s * (phi at label, cos elsewhere) -> [B, C] fp32
+//                 (the strict drop-in ArcMarginProduct.forward, arc_main.py:157-176)
+//   EpiBwdG       backward recompute: G^T = dLoss/dcos for a class chunk, bf16, through a
+//                 swizzled smem tile + TMA store; also the per-class projection term used by
+//                 the weight-normalisation backward                 (autograd behind arc_main.py:329)
+//   EpiRedAdd     split-K accumulate into fp32 global (dX_hat partial sums)
+//   EpiDW         dW = inv_norm * (dW_hat - t * w_hat): F.normalize backward fused into the store
+#pragma once
+
+#include <cuda_bf16.h>
+#include <math.h>
+
+#include "gemm_sm100.cuh"
+
+namespace arcb {
+
+struct EpiNoState {};
+
+// ------------------------------------------------------------------------------------
+struct EpiStore {
+  static constexpr int kSmemBytes = 0;
+  static constexpr bool kUsesTmC = false;
+  struct Params {
+    float* out;
+    int64_t ldo;
+    int M, N;
+    int accumulate;  // 1: atomicAdd (split-K), 0: store
+  };
+  using State = EpiNoState;
+  __device__ static void init(const Params&, State&) {}
+  __device__ static void drain(int) {}
+  template <int BN>
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
+                                 uint8_t*) {
+    const int row = tc.m_blk * kBM + row_in_tile;
+    for (int c = 0; c < BN; c += 32) {
+      const int col0 = tc.n_blk * BN + c;
+      if (col0 >= p.N) break;
+      float v[32];
+      tmem_ld32(taddr + c, v);
+      if (row < p.M) {
+        float* o = p.out + static_cast<int64_t>(row) * p.ldo + col0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) {
+            if (p.accumulate) atomicAdd(o + j, v[j]); else o[j] = v[j];
+          }
+      }
+    }
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
+// ------------------------------------------------------------------------------------
+// Forward statistics.  Rows = batch samples, columns = classes of this shard.
+// Works in base-2 units: u = cos * s2 with s2 = s * log2(e); a partial is (max u, sum 2^(u-max)).
+struct EpiFwdStats {
+  static constexpr int kSmemBytes = 0;
+  static constexpr bool kUsesTmC = false;
+  struct Params {
+    const int* lbl_local;  // [Bp] label - class_offset if this shard owns it, else -1
+    const float* phi;      // [Bp] value that replaces the target cosine (phi or the fallback)
+    float2* part;          // [tiles_n][ldp]
+    int ldp;
+    int B, C;
+    float s2;
+  };
+  using State = EpiNoState;
+  __device__ static void init(const Params&, State&) {}
+  __device__ static void drain(int) {}
+  template <int BN>
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
+                                 uint8_t*) {
+    const int row = tc.m_blk * kBM + row_in_tile;
+    int lbl = -1;
+    float phi = 0.f;
+    if (row < p.B) {
+      lbl = __ldg(p.lbl_local + row);
+      phi = __ldg(p.phi + row);
+    }
+    float run_m = -INFINITY, run_l = 0.f;
+    const int col_base = tc.n_blk * BN;
+    for (int c = 0; c < BN; c += 32) {
+      const int col0 = col_base + c;
+      if (col0 >= p.C) break;
+      float v[32];
+      tmem_ld32(taddr + c, v);
+      if (col0 + 32 > p.C) {  // ragged last tile: padded classes must not enter the softmax
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j >= p.C) v[j] = -INFINITY;
+      }
+      const unsigned d = static_cast<unsigned>(lbl - col0);
+      if (d < 32u) {  // rare: this chunk holds the row's label column
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j == static_cast<int>(d)) v[j] = phi;
+      }
+      float cm = v[0];
+#pragma unroll
+      for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
+      const float nm = fmaxf(run_m, cm);
+      run_l *= ex2_approx((run_m - nm) * p.s2);
+      const float off = nm * p.s2;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        a0 += ex2_approx(fmaf(v[j + 0], p.s2, -off));
+        a1 += ex2_approx(fmaf(v[j + 1], p.s2, -off));
+        a2 += ex2_approx(fmaf(v[j + 2], p.s2, -off));
+        a3 += ex2_approx(fmaf(v[j + 3], p.s2, -off));
+      }
+      run_l += (a0 + a1) + (a2 + a3);
+      run_m = nm;
+    }
+    if (row < p.B) p.part[static_cast<int64_t>(tc.n_blk) * p.ldp + row] = make_float2(run_m * p.s2, run_l);
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
+// ------------------------------------------------------------------------------------
+struct EpiLogits {
+  static constexpr int kSmemBytes = 0;
+  static constexpr bool kUsesTmC = false;
+  struct Params {
+    const int* lbl_local;
+    const float* phi;
+    float* out;  // [B, ldo]
+    int64_t ldo;
+    int B, C;
+    float s;
+  };
+  using State = EpiNoState;
+  __device__ static void init(const Params&, State&) {}
+  __device__ static void drain(int) {}
+  template <int BN>
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
+                                 uint8_t*) {
+    const int row = tc.m_blk * kBM + row_in_tile;
+    int lbl = -1;
+    float phi = 0.f;
+    if (row < p.B) {
+      lbl = __ldg(p.lbl_local + row);
+      phi = __ldg(p.phi + row);
+    }
+    const bool vec_ok = (p.ldo & 3) == 0;
+    for (int c = 0; c < BN; c += 32) {
+      const int col0 = tc.n_blk * BN + c;
+      if (col0 >= p.C) break;
+      float v[32];
+      tmem_ld32(taddr + c, v);
+      const unsigned d = static_cast<unsigned>(lbl - col0);
+      if (d < 32u) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j == static_cast<int>(d)) v[j] = phi;
+      }
+      if (row < p.B) {
+        float* o = p.out + static_cast<int64_t>(row) * p.ldo + col0;
+        if (vec_ok && col0 + 32 <= p.C) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(o + j) = make_float4(v[j] * p.s, v[j + 1] * p.s, v[j + 2] * p.s, v[j + 3] * p.s);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < p.C) o[j] = v[j] * p.s;
+        }
+      }
+    }
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
+// ------------------------------------------------------------------------------------
+// Backward recompute.  Rows = classes of the current chunk, columns = batch samples.
+//   g_ij = gscale * (softmax_ij - onehot_ij) * d logit / d cos     with gscale = dLoss * 1/B
+// (the factor s of d logit/d cos is folded into gscale by the caller: gscale = grad * s / B).
+// Non-target: g = gscale * 2^(cos*s2 - lse2_i).  Target: g = gscale * (2^(zt2_i - lse2_i) - 1) * dphi_i.
+// The tile is written as bf16 G^T[class, sample] through a 128B-swizzled smem tile and TMA.
+// t_j = sum_i g_ij * cos_ij is the projection w_hat_j . dW_hat_j needed by F.normalize's backward.
+// EXT = true is the materialising path: dLoss/dlogits arrives from autograd as grad_out[B, ldgo]
+// and g_ij = grad_out_ij * s * (dphi_i at the label column, 1 elsewhere).
+template <bool EXT>
+struct EpiBwdG {
+  static constexpr int kSmemBytes = kBM * 256 * 2;  // one bf16 tile, 4 boxes of [128 x 64]
+  static constexpr bool kUsesTmC = true;
+  struct Params {
+    const float* lse2;       // [Bp] lse * log2(e); +inf beyond B
+    const float* gscale;     // device scalar: upstream grad * s / B
+    const int* lbl_local;    // [Bp]
+    const float* zt2;        // [Bp] target logit * log2(e)
+    const float* dphi;       // [Bp] d(target value)/d cos
+    const float* cos_t;      // [Bp] exact fp32 target cosine
+    const unsigned char* tile_flag;  // [ceil(Cs/128)] 1 if some label falls into that class tile
+    float* t_out;            // [Cs] accumulates t_j (atomicAdd across batch tiles)
+    int row_off;             // first class of this chunk inside the shard (multiple of 128)
+    int rows_valid;          // classes in this chunk
+    int B, Bp;
+    float s2;
+    const float* grad_out;   // EXT only: [B, ldgo] columns of this chunk
+    int64_t ldgo;
+    float s_ext;
+  };
+  struct State {
+    float gscale;
+  };
+  __device__ static void init(const Params& p, State& st) { st.gscale = EXT ? 0.f : __ldg(p.gscale); }
+  __device__ static void drain(int epi_tid) {
+    if (epi_tid == 0) tma_store_wait_all0();
+  }
+  template <int BN>
+  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, uint32_t taddr, int row_in_tile,
+                                 int epi_tid, uint8_t* smem) {
+    static_assert(BN == 256, "staging tile is sized for BN = 256");
+    // the previous tile's TMA stores must have finished reading the staging tile
+    if (epi_tid == 0) tma_store_wait_read0();
+    named_bar_sync(1, kEpiThreads);
+    const int row_local = tc.m_blk * kBM + row_in_tile;
+    const int cls = p.row_off + row_local;
+    const bool slow = p.tile_flag[(p.row_off >> 7) + tc.m_blk] != 0;
+    float tsum = 0.f;
+    const uint32_t srow = smem_u32(smem) + row_in_tile * 128;
+    const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
+    for (int c = 0; c < BN; c += 32) {
+      const int col0 = tc.n_blk * BN + c;
+      if (col0 >= p.Bp) break;
+      float v[32];
+      tmem_ld32(taddr + c, v);
+      float g[32];
+      if constexpr (!EXT) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 l4 = __ldg(reinterpret_cast<const float4*>(p.lse2 + col0 + j));
+          g[j + 0] = ex2_approx(fmaf(v[j + 0], p.s2, -l4.x)) * st.gscale;
+          g[j + 1] = ex2_approx(fmaf(v[j + 1], p.s2, -l4.y)) * st.gscale;
+          g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * st.gscale;
+          g[j + 3] = ex2_approx(fmaf(v[j + 3], p.s2, -l4.w)) * st.gscale;
+        }
+        if (slow) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (__ldg(p.lbl_local + col0 + j) == cls) {
+              const int i = col0 + j;
+              g[j] = st.gscale * (ex2_approx(__ldg(p.zt2 + i) - __ldg(p.lse2 + i)) - 1.f) * __ldg(p.dphi + i);
+              v[j] = __ldg(p.cos_t + i);
+            }
+          }
+        }
+      } else {
+        const bool row_ok = row_local < p.rows_valid;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int i = col0 + j;
+          float gj = 0.f;
+          if (row_ok && i < p.B) gj = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext;
+          g[j] = gj;
+        }
+        if (slow) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (__ldg(p.lbl_local + col0 + j) == cls) {
+              const int i = col0 + j;
+              g[j] *= __ldg(p.dphi + i);
+              v[j] = __ldg(p.cos_t + i);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) tsum = fmaf(g[j], v[j], tsum);
+      // 32 bf16 = 64 B = four 16 B chunks of this row inside box (c / 64)
+      const uint32_t box = srow + static_cast<uint32_t>(c >> 6) * (kBM * 128);
+      const uint32_t q0 = static_cast<uint32_t>((c & 63) >> 3);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t a = box + (((q0 + q) ^ sw) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(g[q * 8 + 0], g[q * 8 + 1])),
+                     "r"(pack_bf16x2(g[q * 8 + 2], g[q * 8 + 3])), "r"(pack_bf16x2(g[q * 8 + 4], g[q * 8 + 5])),
+                     "r"(pack_bf16x2(g[q * 8 + 6], g[q * 8 + 7]))
+                     : "memory");
+      }
+    }
+    if (row_local < p.rows_valid) atomicAdd(p.t_out + cls, tsum);
+  }
+  template <int BN>
+  __device__ static void finish(const Params& p, State&, const TileCoord& tc, const CUtensorMap& tmC, int, int epi_tid,
+                                uint8_t* smem) {
+    fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
+    named_bar_sync(1, kEpiThreads);
+    if (epi_tid == 0) {
+#pragma unroll
+      for (int bx = 0; bx < BN / 64; ++bx) {
+        const int col0 = tc.n_blk * BN + bx * 64;
+        if (col0 < p.Bp) tma_store_2d(&tmC, smem + bx * (kBM * 128), col0, tc.m_blk * kBM);
+      }
+      tma_store_commit();
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------
+struct EpiRedAdd {
+  static constexpr int kSmemBytes = 0;
+  static constexpr bool kUsesTmC = false;
+  struct Params {
+    float* out;  // [M, ldo] fp32, ldo % 4 == 0, zero-initialised by the caller
+    int64_t ldo;
+    int M, N;
+  };
+  using State = EpiNoState;
+  __device__ static void init(const Params&, State&) {}
+  __device__ static void drain(int) {}
+  template <int BN>
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
+                                 uint8_t*) {
+    const int row = tc.m_blk * kBM + row_in_tile;
+    for (int c = 0; c < BN; c += 32) {
+      const int col0 = tc.n_blk * BN + c;
+      if (col0 >= p.N) break;
+      float v[32];
+      tmem_ld32(taddr + c, v);
+      if (row < p.M) {
+        float* o = p.out + static_cast<int64_t>(row) * p.ldo + col0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          if (col0 + j + 3 < p.N) {
+            red_add_v4(o + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            for (int e = 0; e < 4; ++e)
+              if (col0 + j + e < p.N) atomicAdd(o + j + e, v[j + e]);
+          }
+        }
+      }
+    }
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
+// ------------------------------------------------------------------------------------
+// Rows = classes of the chunk, columns = feature index.  Final dW for those rows:
+//   dW_j = inv_norm_j * (dW_hat_j - t_j * w_hat_j)          (||w_j|| above the F.normalize eps)
+//   dW_j = inv_norm_j * dW_hat_j                            (clamped rows: y = w / eps)
+struct EpiDW {
+  static constexpr int kSmemBytes = 0;
+  static constexpr bool kUsesTmC = false;
+  struct Params {
+    float* dw;                  // [Cs, D] fp32, pitch D
+    const __nv_bfloat16* what;  // [Cs, Dp] bf16
+    const float* t;             // [Cs]
+    const float* inv_norm;      // [Cs] 1 / max(||w||, eps)
+    int row_off, rows_valid;
+    int D, Dp;
+  };
+  using State = EpiNoState;
+  __device__ static void init(const Params&, State&) {}
+  __device__ static void drain(int) {}
+  template <int BN>
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
+                                 uint8_t*) {
+    const int row_local = tc.m_blk * kBM + row_in_tile;
+    const bool valid = row_local < p.rows_valid;
+    const int cls = p.row_off + row_local;
+    float tj = 0.f, inv = 0.f;
+    if (valid) {
+      inv = __ldg(p.inv_norm + cls);
+      tj = (inv < 0.5e12f) ? __ldg(p.t + cls) : 0.f;  // clamped rows take no projection
+    }
+    const bool vec_ok = (p.D & 3) == 0;
+    for (int c = 0; c < BN; c += 32) {
+      const int col0 = tc.n_blk * BN + c;
+      if (col0 >= p.D) break;
+      float v[32];
+      tmem_ld32(taddr + c, v);
+      if (valid) {
+        const uint4* wp = reinterpret_cast<const uint4*>(p.what + static_cast<int64_t>(cls) * p.Dp + col0);
+        float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint4 wq = __ldg(wp + q);
+          const uint32_t wr[4] = {wq.x, wq.y, wq.z, wq.w};
+          float r[8];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float w0 = __uint_as_float(wr[e] << 16);
+            const float w1 = __uint_as_float(wr[e] & 0xffff0000u);
+            r[2 * e + 0] = inv * fmaf(-tj, w0, v[q * 8 + 2 * e + 0]);
+            r[2 * e + 1] = inv * fmaf(-tj, w1, v[q * 8 + 2 * e + 1]);
+          }
+          const int cq = col0 + q * 8;
+          if (vec_ok && cq + 8 <= p.D) {
+            *reinterpret_cast<float4*>(o + q * 8) = make_float4(r[0], r[1], r[2], r[3]);
+            *reinterpret_cast<float4*>(o + q * 8 + 4) = make_float4(r[4], r[5], r[6], r[7]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              if (cq + e < p.D) o[q * 8 + e] = r[e];
+          }
+        }
+      }
+    }
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
+}  // namespace arcb

@@ -1,0 +1,243 @@
+// HBM-bound row kernels of the ArcFace head (one warp per row, 128-bit accesses, shuffle reduce).
+//   l2norm_rows_kernel     F.normalize(x) / F.normalize(weight)      arc_main.py:159
+//   target_prep_kernel     exact fp32 target cosine + margin branch   arc_main.py:160-165 at the label column
+//   merge_stats_kernel     (max, sum-exp) partials -> one record per row
+//   loss_kernel            nn.CrossEntropyLoss() mean                 arc_main.py:245,:327
+//   l2norm_rows_bwd_kernel F.normalize backward for the embeddings    autograd behind arc_main.py:329
+#pragma once
+
+#include <cuda_bf16.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "ptx_sm100.cuh"
+
+namespace arcb {
+
+constexpr float kNormEps = 1e-12f;  // F.normalize default eps
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// rows x D fp32 (pitch ldx) -> rows x Dp bf16 (zero padded to Dp) + inv_norm[rows].
+// NV = float4 per lane kept in registers (D <= 128 * NV); NV == 0: generic two-pass path.
+template <int NV>
+__global__ void __launch_bounds__(256) l2norm_rows_kernel(const float* __restrict__ x, int64_t rows, int D, int64_t ldx,
+                                                          __nv_bfloat16* __restrict__ out, int Dp,
+                                                          float* __restrict__ inv_norm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps_total = static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5);
+  for (int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows;
+       row += warps_total) {
+    const float* xr = x + row * ldx;
+    __nv_bfloat16* orow = out + row * Dp;
+    if constexpr (NV > 0) {
+      float4 v[NV];
+      float ss = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int e = (i * 32 + lane) * 4;
+        v[i] = (e < D) ? ld_stream_f4(xr + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+        ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      }
+      ss = warp_sum(ss);
+      const float inv = 1.f / fmaxf(sqrtf(ss), kNormEps);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int e = (i * 32 + lane) * 4;
+        if (e < Dp) {
+          uint2 pk;
+          pk.x = pack_bf16x2(v[i].x * inv, v[i].y * inv);
+          pk.y = pack_bf16x2(v[i].z * inv, v[i].w * inv);
+          *reinterpret_cast<uint2*>(orow + e) = pk;
+        }
+      }
+      if (lane == 0) inv_norm[row] = inv;
+    } else {
+      float ss = 0.f;
+      for (int e = lane; e < D; e += 32) {
+        const float a = xr[e];
+        ss += a * a;
+      }
+      ss = warp_sum(ss);
+      const float inv = 1.f / fmaxf(sqrtf(ss), kNormEps);
+      for (int e = lane; e < Dp; e += 32) orow[e] = __float2bfloat16_rn(e < D ? xr[e] * inv : 0.f);
+      if (lane == 0) inv_norm[row] = inv;
+    }
+  }
+}
+
+// One warp per sample: exact fp32 target cosine and everything derived from it.
+//   lbl_local : label - class_offset when this shard owns the class, else -1
+//   sub       : value substituted for the target cosine (phi, or the fallback branch)
+//   zt        : s * sub (natural units) or -inf when the label is not in this shard
+//   dphi      : d sub / d cos   (finite limit cos_m where the reference produces NaN)
+//   cos_t     : the fp32 cosine itself
+//   tile_flag : 1 for every 128-class tile that contains at least one label
+__global__ void __launch_bounds__(256)
+target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, int64_t ldw,
+                   const int64_t* __restrict__ labels, const float* __restrict__ inv_nx,
+                   const float* __restrict__ inv_nw, int B, int Bp, int D, int64_t Cs, int64_t class_offset, float s,
+                   float cos_m, float sin_m, float th, float mm, int easy, int* __restrict__ lbl_local,
+                   float* __restrict__ sub, float* __restrict__ zt, float* __restrict__ dphi,
+                   float* __restrict__ cos_t, unsigned char* __restrict__ tile_flag) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= Bp) return;
+  if (i >= B) {  // padding rows
+    if (lane == 0) {
+      lbl_local[i] = -1;
+      sub[i] = 0.f;
+      zt[i] = -INFINITY;
+      dphi[i] = 0.f;
+      cos_t[i] = 0.f;
+    }
+    return;
+  }
+  const int64_t loc = labels[i] - class_offset;
+  if (loc < 0 || loc >= Cs) {
+    if (lane == 0) {
+      lbl_local[i] = -1;
+      sub[i] = 0.f;
+      zt[i] = -INFINITY;
+      dphi[i] = 0.f;
+      cos_t[i] = 0.f;
+    }
+    return;
+  }
+  const float* xr = x + static_cast<int64_t>(i) * ldx;
+  const float* wr = w + loc * ldw;
+  float acc = 0.f;
+  for (int e = lane; e < D; e += 32) acc = fmaf(xr[e], wr[e], acc);
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    const float c = acc * inv_nx[i] * inv_nw[loc];
+    const float om = 1.f - c * c;
+    const float sine = sqrtf(fminf(fmaxf(om, 0.f), 1.f));
+    const float phi = c * cos_m - sine * sin_m;
+    const bool take = easy ? (c > 0.f) : (c > th);
+    const float v = take ? phi : (easy ? c : c - mm);
+    float d = 1.f;
+    if (take) d = (om > 0.f && om < 1.f && sine > 0.f) ? (cos_m + sin_m * c / sine) : cos_m;
+    lbl_local[i] = static_cast<int>(loc);
+    sub[i] = v;
+    zt[i] = s * v;
+    dphi[i] = d;
+    cos_t[i] = c;
+    tile_flag[loc >> 7] = 1;
+  }
+}
+
+// part[n][ldp] (base-2 max, sum) -> rec[row] = merged (max, sum).  One thread per row.
+__global__ void __launch_bounds__(256)
+merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, float2* __restrict__ rec) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= B) return;
+  float m = -INFINITY;
+  for (int k = 0; k < n; ++k) m = fmaxf(m, part[k * ldp + row].x);
+  float l = 0.f;
+  for (int k = 0; k < n; ++k) {
+    const float2 p = part[k * ldp + row];
+    l += p.y * exp2f(p.x - m);
+  }
+  rec[row] = make_float2(m, l);
+}
+
+// stats[P][B][4] = (m2, l, zt, -) per shard -> lse[B] (natural log units), loss = mean(lse - zt).
+// Single block: deterministic reduction order.
+__global__ void __launch_bounds__(1024)
+loss_kernel(const float* __restrict__ stats, int P, int B, float* __restrict__ lse, float* __restrict__ zt_out,
+            float* __restrict__ loss) {
+  __shared__ double red[32];
+  double acc = 0.0;
+  for (int row = threadIdx.x; row < B; row += blockDim.x) {
+    float m = -INFINITY, zt = -INFINITY;
+    for (int p = 0; p < P; ++p) {
+      const float4 r = *reinterpret_cast<const float4*>(stats + (static_cast<int64_t>(p) * B + row) * 4);
+      m = fmaxf(m, r.x);
+      zt = fmaxf(zt, r.z);
+    }
+    float l = 0.f;
+    for (int p = 0; p < P; ++p) {
+      const float4 r = *reinterpret_cast<const float4*>(stats + (static_cast<int64_t>(p) * B + row) * 4);
+      l += r.y * exp2f(r.x - m);
+    }
+    const float v = (m + log2f(l)) * kLn2;
+    lse[row] = v;
+    if (zt_out) zt_out[row] = zt;
+    acc += static_cast<double>(v) - static_cast<double>(zt);
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double v = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) *loss = static_cast<float>(v / B);
+  }
+}
+
+// rec (merged (m2, l)) + zt -> shard record [B][4]
+__global__ void __launch_bounds__(256)
+pack_stats_kernel(const float2* __restrict__ rec, const float* __restrict__ zt, int B, float* __restrict__ stats) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= B) return;
+  const float2 r = rec[row];
+  *reinterpret_cast<float4*>(stats + static_cast<int64_t>(row) * 4) = make_float4(r.x, r.y, zt[row], 0.f);
+}
+
+// Backward set-up: lse2[i] = lse[i] * log2(e) (+inf on padding), zt2 likewise, gscale = grad * s / B,
+// and clears the per-chunk accumulators.
+__global__ void __launch_bounds__(256)
+bwd_prep_kernel(const float* __restrict__ lse, const float* __restrict__ zt, const float* __restrict__ grad_loss,
+                float s, int B, int Bp, float* __restrict__ lse2, float* __restrict__ zt2,
+                float* __restrict__ gscale) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) *gscale = (grad_loss ? *grad_loss : 1.f) * s / static_cast<float>(B);
+  if (i >= Bp) return;
+  lse2[i] = (i < B) ? lse[i] * kLog2e : INFINITY;
+  zt2[i] = (i < B) ? zt[i] * kLog2e : -INFINITY;
+}
+
+// dx = (dxh - xh * (xh . dxh)) / ||x||   with xh = x / ||x||;  clamped rows (||x|| <= eps): dx = dxh / eps.
+__global__ void __launch_bounds__(256)
+l2norm_rows_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ dxh, int64_t ldg, int rows,
+                       int D, float* __restrict__ dx, int64_t ldo) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float* xr = x + static_cast<int64_t>(row) * ldx;
+  const float* gr = dxh + static_cast<int64_t>(row) * ldg;
+  float ss = 0.f, dot = 0.f;
+  for (int e = lane; e < D; e += 32) {
+    const float a = xr[e];
+    ss = fmaf(a, a, ss);
+    dot = fmaf(a, gr[e], dot);
+  }
+  ss = warp_sum(ss);
+  dot = warp_sum(dot);
+  const float nrm = sqrtf(ss);
+  float* o = dx + static_cast<int64_t>(row) * ldo;
+  if (nrm > kNormEps) {
+    const float inv = 1.f / nrm;
+    const float proj = dot * inv * inv;  // (xh . dxh) / ||x|| expressed on raw x
+    for (int e = lane; e < D; e += 32) o[e] = inv * (gr[e] - xr[e] * proj);
+  } else {
+    for (int e = lane; e < D; e += 32) o[e] = gr[e] * (1.f / kNormEps);
+  }
+}
+
+}  // namespace arcb

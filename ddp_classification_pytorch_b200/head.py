@@ -1,0 +1,269 @@
+"""Drop-in ``ArcMarginProduct`` backed by the sm_100a kernels in ``libarcface_b200.so``.
+
+Mirrors the reference class at ARCFACE/arc_main.py:130-176: same constructor
+``(in_features, out_features, s=30.0, m=0.50, easy_margin=False)``, same attributes, same
+``forward(input, label)`` contract (returns the ``[B, out_features]`` fp32 scaled logits,
+differentiable w.r.t. ``input`` and ``weight``).  Added, non-breaking surface:
+
+* ``forward_loss(input, label)`` -- head + ``nn.CrossEntropyLoss()`` (arc_main.py:245,:327) fused;
+  the B x C logits are never written.  Statistics of the last call are kept in ``.aux``.
+* keyword-only ``process_group`` -- class-sharded mode: this rank owns a contiguous slice of the
+  classes and only per-row softmax statistics (forward) and the ``[B, D]`` partial of dX
+  (backward) cross NVLink through ``torch.distributed``.
+
+PyTorch is used here for device memory, streams and collectives only; all arithmetic runs in the
+hand-written CUDA kernels, reached through the C ABI with raw pointers.  There is no CPU path.
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import Optional
+
+import torch
+import torch.nn as nn
+from torch.nn import Parameter
+
+from . import _lib
+
+# classes per backward chunk: 128 * 148 keeps every wave of the three chunk GEMMs full on 148 SMs
+# and the bf16 dLoss/dcos chunk (B=1024: 38.8 MB) inside the 126 MB L2.
+DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 128 * 148))
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _prep_inputs(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor):
+    if x.dim() != 2:
+        raise IndexError(f"input must be 2-D [B, in_features], got {tuple(x.shape)}")  # F.normalize(dim=1)
+    if not x.is_cuda or not w.is_cuda:
+        raise RuntimeError("ArcMarginProduct (B200) requires CUDA tensors: there is no CPU path")
+    if x.shape[1] != w.shape[1]:
+        raise RuntimeError(f"input has {x.shape[1]} features, weight expects {w.shape[1]}")
+    xc = x.detach()
+    if xc.dtype != torch.float32:
+        xc = xc.float()
+    xc = xc.contiguous()
+    wc = w.detach()
+    if wc.dtype != torch.float32:
+        wc = wc.float()
+    wc = wc.contiguous()
+    lab = label.detach().reshape(-1)  # label.view(-1, 1).long()  (arc_main.py:169)
+    if lab.dtype != torch.int64:
+        lab = lab.long()
+    lab = lab.to(x.device).contiguous()
+    if lab.numel() != x.shape[0]:
+        raise IndexError(f"label has {lab.numel()} entries for a batch of {x.shape[0]}")
+    return xc, wc, lab
+
+
+class _ShardCtx:
+    """Buffers that live from a forward call to its backward."""
+
+    __slots__ = ("B", "Cs", "D", "Dp", "ws", "ws_bytes", "lse", "zt", "group")
+
+
+def _alloc_ws(B, Cs, D, device):
+    L = _lib.lib()
+    nbytes = L.arcb_ws_bytes(B, Cs, D)
+    if nbytes <= 0:
+        raise RuntimeError("arcb_ws_bytes rejected the sizes")
+    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+
+def _scratch_for(B, Cs, device, chunk_classes):
+    L = _lib.lib()
+    chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
+    nbytes = L.arcb_scratch_bytes(B, chunk)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+
+class _FusedLossFn(torch.autograd.Function):
+    """loss = CrossEntropy(ArcMargin(x, W, label)) without materialising the logits."""
+
+    @staticmethod
+    def forward(ctx, x, w, label, cfg):
+        L = _lib.lib()
+        xc, wc, lab = _prep_inputs(x, w, label)
+        B, D = xc.shape
+        Cs = wc.shape[0]
+        dev = xc.device
+        ws, ws_bytes = _alloc_ws(B, Cs, D, dev)
+        stats = torch.empty(B, 4, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_shard_forward(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"],
+                                        cfg["s"], cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes,
+                                        _ptr(stats), _stream()), "arcb_shard_forward")
+        group = cfg["group"]
+        if group is not None and torch.distributed.get_world_size(group) > 1:
+            P = torch.distributed.get_world_size(group)
+            gathered = torch.empty(P, B, 4, dtype=torch.float32, device=dev)
+            torch.distributed.all_gather_into_tensor(gathered, stats, group=group)
+        else:
+            P, gathered = 1, stats
+        lse = torch.empty(B, dtype=torch.float32, device=dev)
+        zt = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_merge_loss(_ptr(gathered), P, B, _ptr(lse), _ptr(zt), _ptr(loss), _stream()),
+                   "arcb_merge_loss")
+        ctx.save_for_backward(xc)
+        ctx.shard = (B, Cs, D, ws, ws_bytes, lse, zt, group, cfg["s"], cfg["chunk_classes"])
+        ctx.w_meta = (w.dtype, x.dtype)
+        cfg["aux_out"].update(lse=lse, target_logit=zt, stats=stats)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        L = _lib.lib()
+        (xc,) = ctx.saved_tensors
+        B, Cs, D, ws, ws_bytes, lse, zt, group, s, chunk_classes = ctx.shard
+        dev = xc.device
+        Dp = L.arcb_padded_dim(D)
+        g = grad_loss.detach().to(torch.float32).contiguous()
+        scratch, scratch_bytes = _scratch_for(B, Cs, dev, chunk_classes)
+        dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
+        dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_shard_backward(B, Cs, D, s, _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(g), None, 0,
+                                         _ptr(scratch), scratch_bytes, _ptr(dw), _ptr(dxhat), _stream()),
+                   "arcb_shard_backward")
+        if group is not None and torch.distributed.get_world_size(group) > 1:
+            torch.distributed.all_reduce(dxhat, group=group)  # sum of the class shards' partials
+        dx = torch.empty(B, D, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_l2norm_rows_bwd(_ptr(xc), D, _ptr(dxhat), Dp, B, D, _ptr(dx), D, _stream()),
+                   "arcb_l2norm_rows_bwd")
+        w_dtype, x_dtype = ctx.w_meta
+        return dx.to(x_dtype), dw.to(w_dtype), None, None
+
+
+class _LogitsFn(torch.autograd.Function):
+    """The literal reference forward: returns the [B, Cs] fp32 logits (arc_main.py:157-176)."""
+
+    @staticmethod
+    def forward(ctx, x, w, label, cfg):
+        L = _lib.lib()
+        xc, wc, lab = _prep_inputs(x, w, label)
+        B, D = xc.shape
+        Cs = wc.shape[0]
+        dev = xc.device
+        ws, ws_bytes = _alloc_ws(B, Cs, D, dev)
+        out = torch.empty(B, Cs, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_shard_logits(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
+                                       cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(out), Cs,
+                                       _stream()), "arcb_shard_logits")
+        ctx.save_for_backward(xc)
+        ctx.shard = (B, Cs, D, ws, ws_bytes, cfg["group"], cfg["s"], cfg["chunk_classes"])
+        ctx.w_meta = (w.dtype, x.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        L = _lib.lib()
+        (xc,) = ctx.saved_tensors
+        B, Cs, D, ws, ws_bytes, group, s, chunk_classes = ctx.shard
+        dev = xc.device
+        Dp = L.arcb_padded_dim(D)
+        go = grad_out.detach().to(torch.float32).contiguous()
+        scratch, scratch_bytes = _scratch_for(B, Cs, dev, chunk_classes)
+        dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
+        dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_shard_backward(B, Cs, D, s, _ptr(ws), ws_bytes, None, None, None, _ptr(go), Cs,
+                                         _ptr(scratch), scratch_bytes, _ptr(dw), _ptr(dxhat), _stream()),
+                   "arcb_shard_backward")
+        if group is not None and torch.distributed.get_world_size(group) > 1:
+            torch.distributed.all_reduce(dxhat, group=group)
+        dx = torch.empty(B, D, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_l2norm_rows_bwd(_ptr(xc), D, _ptr(dxhat), Dp, B, D, _ptr(dx), D, _stream()),
+                   "arcb_l2norm_rows_bwd")
+        w_dtype, x_dtype = ctx.w_meta
+        return dx.to(x_dtype), dw.to(w_dtype), None, None
+
+
+def shard_bounds(num_classes: int, world: int, rank: int):
+    """Contiguous class range [lo, hi) owned by ``rank`` (sizes differ by at most one)."""
+    base, rem = divmod(num_classes, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class ArcMarginProduct(nn.Module):
+    r"""Large-margin arc distance head, cos(theta + m)  --  drop-in for arc_main.py:130-176.
+
+    Args:
+        in_features: size of each input sample
+        out_features: number of classes (the GLOBAL count, also in class-sharded mode)
+        s: norm of input feature (logit scale), must be > 0
+        m: additive angular margin
+        easy_margin: use the ``cos > 0`` fallback instead of ``th`` / ``mm``
+        process_group (keyword-only): shard the classes over this ``torch.distributed`` group;
+            ``weight`` then holds only this rank's rows and ``forward`` returns only its columns.
+    """
+
+    def __init__(self, in_features, out_features, s=30.0, m=0.50, easy_margin=False, *, process_group=None,
+                 chunk_classes: Optional[int] = None):
+        super().__init__()
+        self.in_features = in_features
+        self.out_features = out_features
+        self.s = s
+        self.m = m
+        self.process_group = process_group
+        if process_group is not None:
+            world = torch.distributed.get_world_size(process_group)
+            rank = torch.distributed.get_rank(process_group)
+        else:
+            world, rank = 1, 0
+        self.class_lo, self.class_hi = shard_bounds(out_features, world, rank)
+        self.world_size, self.rank = world, rank
+        # weight is initialised for the full matrix (xavier bound uses the global fan-out, arc_main.py:145-146)
+        # and then sliced, so that a sharded head starts from the same distribution as a replicated one.
+        rows = self.class_hi - self.class_lo
+        self.weight = Parameter(torch.empty(rows, in_features, dtype=torch.float32))
+        bound = math.sqrt(6.0 / (in_features + out_features))
+        with torch.no_grad():
+            self.weight.uniform_(-bound, bound)
+
+        self.easy_margin = easy_margin
+        self.cos_m = math.cos(m)
+        self.sin_m = math.sin(m)
+        self.th = math.cos(math.pi - m)
+        self.mm = math.sin(math.pi - m) * m
+        self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES
+        self.aux = {}
+
+    def extra_repr(self):
+        return (f"in_features={self.in_features}, out_features={self.out_features}, s={self.s}, m={self.m}, "
+                f"easy_margin={self.easy_margin}, classes=[{self.class_lo},{self.class_hi})")
+
+    def _cfg(self):
+        if not (float(self.s) > 0.0):
+            raise ValueError("ArcMarginProduct (B200): the scale s must be positive")
+        return {
+            "s": float(self.s), "m": float(self.m), "easy_margin": bool(self.easy_margin),
+            "class_offset": int(self.class_lo), "group": self.process_group,
+            "chunk_classes": int(self.chunk_classes), "aux_out": self.aux,
+        }
+
+    def forward(self, input, label):
+        """Scaled logits ``[B, classes of this rank]`` exactly as arc_main.py:157-176 returns them."""
+        return _LogitsFn.apply(input, self.weight, label, self._cfg())
+
+    def forward_loss(self, input, label):
+        """``nn.CrossEntropyLoss()(self(input, label), label)`` fused (arc_main.py:326-327)."""
+        return _FusedLossFn.apply(input, self.weight, label, self._cfg())
+
+    @torch.no_grad()
+    def full_weight(self):
+        """The complete ``[out_features, in_features]`` weight (gathers the shards) for checkpoints."""
+        if self.process_group is None or self.world_size == 1:
+            return self.weight.detach().clone()
+        sizes = [shard_bounds(self.out_features, self.world_size, r) for r in range(self.world_size)]
+        rows = max(hi - lo for lo, hi in sizes)
+        pad = torch.zeros(rows, self.in_features, dtype=self.weight.dtype, device=self.weight.device)
+        pad[: self.weight.shape[0]] = self.weight
+        parts = [torch.empty_like(pad) for _ in range(self.world_size)]
+        torch.distributed.all_gather(parts, pad, group=self.process_group)
+        return torch.cat([p[: hi - lo] for p, (lo, hi) in zip(parts, sizes)], dim=0)

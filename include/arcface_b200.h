@@ -1,0 +1,108 @@
+/*
+ * arcface_b200 -- C ABI of the B200-native ArcFace head (libarcface_b200.so).
+ *
+ * Drop-in boundary for ONE hot path of XiaoyuWant/DDP_Classification_pytorch: the ArcFace head
+ * `ArcMarginProduct` (ARCFACE/arc_main.py:130-176) plus the `nn.CrossEntropyLoss` that consumes it
+ * (ARCFACE/arc_main.py:245, applied at :327 and :369) and their autograd backward (:329).
+ * The reference has no FFI of its own (it is eager PyTorch); these entry points are what a binding
+ * for this path would call -- see INTEGRATION.md for the ctypes stub that the Python module
+ * `ddp_classification_pytorch_b200.ArcMarginProduct` uses.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated otherwise; the caller owns every buffer,
+ *     including workspaces (sizes from the *_bytes queries); nothing is allocated or freed here;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, no host sync;
+ *   - return value 0 = success, negative = error; arcb_last_error() returns a thread-local message;
+ *   - matrices are row-major fp32 with an explicit leading dimension where one is given;
+ *   - labels are int64 GLOBAL class ids; a shard owns classes [class_offset, class_offset + Cs).
+ */
+#ifndef ARCFACE_B200_H_
+#define ARCFACE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ARCB_OK 0
+#define ARCB_ERR_INVALID (-1)   /* bad argument (null pointer, size, alignment) */
+#define ARCB_ERR_CUDA (-2)      /* a CUDA call / launch failed */
+#define ARCB_ERR_WORKSPACE (-3) /* workspace / scratch too small */
+#define ARCB_ERR_TIMEOUT (-4)   /* device-side pipeline watchdog fired (debug aid) */
+
+/* Library version (major * 10000 + minor * 100 + patch). */
+int arcb_version(void);
+
+/* Message for the last error raised on the calling thread ("" if none). */
+const char* arcb_last_error(void);
+
+/* Synchronises `stream` and reports whether the device-side pipeline watchdog fired since the
+ * last call (ARCB_ERR_TIMEOUT) -- used by the tests, never needed on the hot path. */
+int arcb_check_watchdog(void* stream);
+
+/* ---- row L2 normalisation: F.normalize(input) / F.normalize(self.weight), arc_main.py:159 ----
+ * x [rows, D] fp32 (leading dim ldx)  ->  out [rows, Dp] bf16 (zero padded, Dp % 64 == 0, Dp >= D)
+ * and inv_norm[rows] = 1 / max(||x||_2, 1e-12). */
+int arcb_l2norm_rows(const float* x, int64_t rows, int64_t D, int64_t ldx, void* out_bf16, int64_t Dp,
+                     float* inv_norm, void* stream);
+
+/* ---- F.normalize backward for the embeddings (autograd behind arc_main.py:329) ----
+ * dx = (dxhat - xhat (xhat . dxhat)) / ||x||. */
+int arcb_l2norm_rows_bwd(const float* x, int64_t ldx, const float* dxhat, int64_t ldg, int64_t rows, int64_t D,
+                         float* dx, int64_t ldo, void* stream);
+
+/* ---- tcgen05 GEMM core, exposed for unit tests: out[M,N] (+)= A * B^T with bf16 operands ----
+ * a_mn / b_mn = 0: operand stored [M|N, K] (K contiguous); 1: stored [K, M|N] (M|N contiguous).
+ * lda / ldb in elements (multiples of 8).  split_k > 1 accumulates with atomics into `out`
+ * (which must then be zeroed by the caller). */
+int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, int64_t N, int64_t K, int64_t lda,
+                   int64_t ldb, float* out, int64_t ldo, int split_k, void* stream);
+
+/* Bytes of persistent workspace a shard needs between forward and backward. */
+int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D);
+
+/* Bytes of backward scratch that hold `chunk_classes` classes of bf16 dLoss/dcos for batch B.
+ * arcb_shard_backward accepts any scratch >= arcb_scratch_bytes(B, 128). */
+int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes);
+
+/* ---- fused forward on one class shard: arc_main.py:159-172 + the softmax statistics of :245 ----
+ * x [B, D] fp32, w [Cs, D] fp32 (the shard's rows of ArcMarginProduct.weight), labels [B] int64.
+ * Writes stats [B, 4] fp32 = (row max of logits * log2e, sum 2^(logit*log2e - max), target logit
+ * or -inf if another shard owns the label, 0).  The B x Cs logits are never written. */
+int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                       int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                       int64_t ws_bytes, float* stats, void* stream);
+
+/* ---- materialising forward: the literal ArcMarginProduct.forward output, arc_main.py:157-176 ----
+ * logits [B, ldl] fp32 <- s * (phi at the label column, cos elsewhere) for this shard's columns. */
+int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                      int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                      int64_t ws_bytes, float* logits, int64_t ldl, void* stream);
+
+/* ---- merge shard records into the loss: nn.CrossEntropyLoss() mean, arc_main.py:245,:327 ----
+ * stats [P, B, 4] (P shard records, e.g. after an all_gather; P = 1 unsharded)
+ * -> lse [B], target_logit [B] (may be NULL), loss [1] = mean(lse - target_logit). */
+int arcb_merge_loss(const float* stats, int64_t P, int64_t B, float* lse, float* target_logit, float* loss,
+                    void* stream);
+
+/* ---- fused backward on one class shard (autograd of arc_main.py:326-329) ----
+ * Needs the workspace left by arcb_shard_forward / arcb_shard_logits for the same inputs.
+ * lse [B] and target_logit [B] are the GLOBAL values from arcb_merge_loss; grad_loss is a device
+ * scalar (NULL = 1.0).  If grad_logits != NULL (materialising path) it is dLoss/dlogits [B, ldgl]
+ * for this shard's columns and lse / target_logit / grad_loss are ignored.
+ * Writes dw [Cs, D] (final gradient of the weight shard) and ACCUMULATES this shard's partial of
+ * d loss / d xhat into dxhat [B, Dp] fp32 after zeroing it (sum over shards, then
+ * arcb_l2norm_rows_bwd gives dx). */
+int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int64_t ws_bytes, const float* lse,
+                        const float* target_logit, const float* grad_loss, const float* grad_logits, int64_t ldgl,
+                        void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, void* stream);
+
+/* Leading dimension (elements) of the dxhat buffer for feature size D. */
+int64_t arcb_padded_dim(int64_t D);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARCFACE_B200_H_ */

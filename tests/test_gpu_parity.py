@@ -1,0 +1,128 @@
+"""CUDA path vs the reference's golden vectors and vs the oracle, through the Python module that
+wraps the C ABI.  Tolerances are the ones BASELINE.json's north_star states:
+loss within 1e-3 relative, dX / dW cosine similarity >= 0.999, argmax bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import cosine_similarity
+from ddp_classification_pytorch_b200 import ArcMarginProduct, _lib
+from oracle import arcface_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-3
+GRAD_COS = 0.999
+
+
+def _module(w, s, m, easy, **kw):
+    C, D = w.shape
+    head = ArcMarginProduct(D, C, s=s, m=m, easy_margin=easy, **kw).cuda()
+    with torch.no_grad():
+        head.weight.copy_(torch.as_tensor(w))
+    return head
+
+
+def _sync_ok():
+    _lib.check(_lib.lib().arcb_check_watchdog(torch.cuda.current_stream().cuda_stream))
+
+
+def test_fused_loss_matches_reference_golden(golden):
+    g = golden
+    head = _module(g["w"], float(g["s"]), float(g["m"]), bool(g["easy_margin"]))
+    x = torch.tensor(g["x"], device="cuda", requires_grad=True)
+    y = torch.tensor(g["label"], device="cuda")
+    loss = head.forward_loss(x, y)
+    loss.backward()
+    _sync_ok()
+    assert loss.item() == pytest.approx(float(g["loss"]), rel=LOSS_RTOL)
+    assert cosine_similarity(x.grad.cpu().numpy(), g["dx"]) >= GRAD_COS
+    assert cosine_similarity(head.weight.grad.cpu().numpy(), g["dw"]) >= GRAD_COS
+    # magnitude as well as direction
+    assert np.linalg.norm(x.grad.cpu().numpy()) == pytest.approx(np.linalg.norm(g["dx"]), rel=2e-2)
+    assert np.linalg.norm(head.weight.grad.cpu().numpy()) == pytest.approx(np.linalg.norm(g["dw"]), rel=2e-2)
+
+
+def test_logits_forward_matches_reference_golden(golden):
+    g = golden
+    s = float(g["s"])
+    head = _module(g["w"], s, float(g["m"]), bool(g["easy_margin"]))
+    x = torch.tensor(g["x"], device="cuda", requires_grad=True)
+    y = torch.tensor(g["label"], device="cuda")
+    out = head(x, y)
+    assert out.dtype == torch.float32 and tuple(out.shape) == g["logits"].shape
+    _sync_ok()
+    o = out.detach().cpu().numpy()
+    rows = np.arange(o.shape[0])
+    # target column comes from the exact fp32 side path
+    np.testing.assert_allclose(o[rows, g["label"]], g["logits"][rows, g["label"]], atol=2e-4 * s / 30, rtol=1e-5)
+    # other columns: bf16 operands, fp32 accumulate  ->  |dcos| <= ~2^-8 worst case
+    np.testing.assert_allclose(o, g["logits"], atol=4e-3 * s)
+    # argmax must be identical wherever the fp32 reference is unambiguous at bf16 resolution
+    srt = np.sort(g["logits"], axis=1)
+    clear = (srt[:, -1] - srt[:, -2]) > 8e-3 * s
+    assert (o.argmax(1)[clear] == g["logits"].argmax(1)[clear]).all()
+    # the materialising path is differentiable like the reference's
+    loss = torch.nn.functional.cross_entropy(out, y)
+    loss.backward()
+    _sync_ok()
+    assert loss.item() == pytest.approx(float(g["loss"]), rel=LOSS_RTOL)
+    assert cosine_similarity(x.grad.cpu().numpy(), g["dx"]) >= GRAD_COS
+    assert cosine_similarity(head.weight.grad.cpu().numpy(), g["dw"]) >= GRAD_COS
+
+
+@pytest.mark.parametrize("easy", [False, True])
+@pytest.mark.parametrize("shape", [(256, 512, 5000), (300, 256, 2173), (512, 2048, 1000), (64, 100, 700)])
+def test_fused_vs_oracle_medium(shape, easy):
+    B, D, C = shape
+    gen = torch.Generator().manual_seed(B + C)
+    bound = (6.0 / (C + D)) ** 0.5
+    w = (torch.rand(C, D, generator=gen) * 2 - 1) * bound
+    x = torch.randn(B, D, generator=gen)
+    y = torch.randint(0, C, (B,), generator=gen)
+    # plant rows on both sides of every margin branch
+    for r in range(0, B, 7):
+        wy = w[y[r]] / w[y[r]].norm()
+        c = [-0.99, -0.9, -0.86, -0.01, 0.01, 0.5, 0.99][(r // 7) % 7]
+        n = torch.randn(D, generator=gen); n = n - (n @ wy) * wy; n = n / n.norm()
+        x[r] = 3.0 * (c * wy + (1 - c * c) ** 0.5 * n)
+    ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, easy)
+    head = _module(w.numpy(), 30.0, 0.5, easy, chunk_classes=1024)  # several backward chunks
+    xg = x.cuda().requires_grad_(True)
+    loss = head.forward_loss(xg, y.cuda())
+    loss.backward()
+    _sync_ok()
+    assert loss.item() == pytest.approx(ref["loss"], rel=LOSS_RTOL)
+    assert cosine_similarity(xg.grad.cpu().numpy(), ref["dx"]) >= GRAD_COS
+    assert cosine_similarity(head.weight.grad.cpu().numpy(), ref["dw"]) >= GRAD_COS
+    np.testing.assert_allclose(head.aux["lse"].cpu().numpy(), ref["lse"], rtol=2e-3)
+    np.testing.assert_allclose(head.aux["target_logit"].cpu().numpy(), ref["target_logit"], atol=1e-3, rtol=1e-5)
+
+
+def test_grad_scale_and_label_dtypes():
+    g = np.load(__import__("os").path.join(__import__("conftest").GOLDEN_DIR, "small_easy.npz"))
+    head = _module(g["w"], 30.0, 0.5, True)
+    x = torch.tensor(g["x"], device="cuda", requires_grad=True)
+    base = None
+    for lab in (torch.tensor(g["label"]).int(), torch.tensor(g["label"]).view(-1, 1), torch.tensor(g["label"]).float()):
+        head.weight.grad = None; x.grad = None
+        loss = head.forward_loss(x, lab.cuda())
+        (loss * -2.5).backward()
+        _sync_ok()
+        if base is None:
+            base = (loss.item(), x.grad.clone(), head.weight.grad.clone())
+            assert cosine_similarity(x.grad.cpu().numpy(), -g["dx"]) >= GRAD_COS
+            assert np.linalg.norm(x.grad.cpu().numpy()) == pytest.approx(2.5 * np.linalg.norm(g["dx"]), rel=2e-2)
+        else:
+            assert loss.item() == base[0]
+            assert torch.equal(x.grad, base[1]) and torch.equal(head.weight.grad, base[2])
+
+
+def test_contract_errors():
+    head = ArcMarginProduct(16, 8).cuda()
+    with pytest.raises(IndexError):
+        head(torch.randn(16, device="cuda"), torch.zeros(1, device="cuda"))
+    with pytest.raises(RuntimeError):
+        head(torch.randn(4, 16), torch.zeros(4))
+    assert list(head.state_dict().keys()) == ["weight"]
+    assert head.weight.dtype == torch.float32 and tuple(head.weight.shape) == (8, 16)

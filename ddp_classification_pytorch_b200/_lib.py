@@ -29,7 +29,13 @@ NVCC_FLAGS = [
 EXPORTED = [
     "arcb_version", "arcb_last_error", "arcb_check_watchdog", "arcb_l2norm_rows", "arcb_l2norm_rows_bwd",
     "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
-    "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim",
+    "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
+    "arcb_profile_collect",
+]
+
+KERNEL_KINDS = [
+    "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",
+    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test",
 ]
 
 _lock = threading.Lock()
@@ -96,6 +102,12 @@ def _declare(lib):
     lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
     lib.arcb_shard_backward.restype = i32
     lib.arcb_shard_backward.argtypes = [i64, i64, i64, f32, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp]
+    lib.arcb_launch_count.restype = i64
+    lib.arcb_launch_count.argtypes = []
+    lib.arcb_profile_enable.restype = i32
+    lib.arcb_profile_enable.argtypes = [i32]
+    lib.arcb_profile_collect.restype = i32
+    lib.arcb_profile_collect.argtypes = [vp, vp, i32]
 
 
 def lib():
@@ -113,6 +125,16 @@ def lib():
             _declare(handle)
             _lib = handle
     return _lib
+
+
+def profile_collect():
+    """{kind: (milliseconds, launches)} since the last collect (synchronises the device)."""
+    n = len(KERNEL_KINDS)
+    ms = (ctypes.c_double * n)()
+    cnt = (ctypes.c_int64 * n)()
+    check(lib().arcb_profile_collect(ctypes.cast(ms, ctypes.c_void_p), ctypes.cast(cnt, ctypes.c_void_p), n),
+          "arcb_profile_collect")
+    return {KERNEL_KINDS[i]: (ms[i], cnt[i]) for i in range(n)}
 
 
 def check(rc: int, what: str = "arcface_b200") -> None:

@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 #include <math.h>
 #include <stdarg.h>
+#include <atomic>
 #include <stdio.h>
 #include <string.h>
 
@@ -37,6 +38,36 @@ int fail(int code, const char* fmt, ...) {
   } while (0)
 
 inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+// ---- launch accounting and optional per-kernel CUDA-event timing (bench / tests only) ----
+// The counter is always on (one relaxed atomic per launch).  Event timing is off unless
+// arcb_profile_enable(1) was called; the event pool is created there, never on the hot path.
+std::atomic<int64_t> g_launches{0};
+constexpr int kProfMax = 8192;
+struct Profiler {
+  bool on = false;
+  int n = 0;
+  cudaEvent_t beg[kProfMax];
+  cudaEvent_t end[kProfMax];
+  int kind[kProfMax];
+  bool created = false;
+} g_prof;
+
+struct LaunchScope {
+  cudaStream_t st;
+  int slot;
+  LaunchScope(int kind, cudaStream_t s, int nkernels = 1) : st(s), slot(-1) {
+    g_launches.fetch_add(nkernels, std::memory_order_relaxed);
+    if (g_prof.on && g_prof.n < kProfMax) {
+      slot = g_prof.n++;
+      g_prof.kind[slot] = kind;
+      cudaEventRecord(g_prof.beg[slot], st);
+    }
+  }
+  ~LaunchScope() {
+    if (slot >= 0) cudaEventRecord(g_prof.end[slot], st);
+  }
+};
 
 constexpr int kBNTile = 256;
 
@@ -105,8 +136,9 @@ int check_dims(int64_t B, int64_t Cs, int64_t D) {
 }
 
 int launch_l2norm(const float* x, int64_t rows, int64_t D, int64_t ldx, __nv_bfloat16* out, int64_t Dp, float* inv,
-                  cudaStream_t st) {
+                  cudaStream_t st, int kind) {
   if (rows == 0) return ARCB_OK;
+  LaunchScope ls(kind, st);
   const int warps_per_block = 8;
   int64_t blocks = (rows + warps_per_block - 1) / warps_per_block;
   if (blocks > 148 * 64) blocks = 148 * 64;  // grid-stride beyond that
@@ -138,15 +170,16 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   if (W.total > ws_bytes)
     return fail(ARCB_ERR_WORKSPACE, "workspace too small: need %lld bytes, got %lld", (long long)W.total,
                 (long long)ws_bytes);
-  rc = launch_l2norm(x, B, D, ldx, W.xhat, W.Dp, W.inv_nx, st);
+  rc = launch_l2norm(x, B, D, ldx, W.xhat, W.Dp, W.inv_nx, st, ARCB_K_L2NORM_X);
   if (rc) return rc;
-  rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st);
+  rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
   if (rc) return rc;
   ARCB_CUDA(cudaMemsetAsync(W.tile_flag, 0, (Cs + 127) / 128, st));
   const double md = static_cast<double>(m);
   const float cos_m = static_cast<float>(cos(md)), sin_m = static_cast<float>(sin(md));
   const float th = static_cast<float>(cos(M_PI - md)), mm = static_cast<float>(sin(M_PI - md) * md);
   const int blocks = static_cast<int>((W.Bp + 7) / 8);
+  LaunchScope ls(ARCB_K_TARGET_PREP, st);
   target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.inv_nx, W.inv_nw, (int)B, (int)W.Bp, (int)D, Cs,
                                              class_offset, s, cos_m, sin_m, th, mm, easy, W.lbl_local, W.sub, W.zt,
                                              W.dphi, W.cos_t, W.tile_flag);
@@ -177,12 +210,48 @@ int arcb_check_watchdog(void* stream) {
 
 int64_t arcb_padded_dim(int64_t D) { return round_up(D, 64); }
 
+int64_t arcb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int arcb_profile_enable(int on) {
+  if (on && !g_prof.created) {
+    for (int i = 0; i < kProfMax; ++i) {
+      ARCB_CUDA(cudaEventCreate(&g_prof.beg[i]));
+      ARCB_CUDA(cudaEventCreate(&g_prof.end[i]));
+    }
+    g_prof.created = true;
+  }
+  g_prof.on = on != 0;
+  g_prof.n = 0;
+  return ARCB_OK;
+}
+
+int arcb_profile_collect(double* ms_by_kind, int64_t* launches_by_kind, int nkinds) {
+  if (!ms_by_kind || !launches_by_kind || nkinds <= 0) return fail(ARCB_ERR_INVALID, "bad profile buffers");
+  for (int k = 0; k < nkinds; ++k) {
+    ms_by_kind[k] = 0.0;
+    launches_by_kind[k] = 0;
+  }
+  ARCB_CUDA(cudaDeviceSynchronize());
+  for (int i = 0; i < g_prof.n; ++i) {
+    float ms = 0.f;
+    ARCB_CUDA(cudaEventElapsedTime(&ms, g_prof.beg[i], g_prof.end[i]));
+    const int k = g_prof.kind[i];
+    if (k >= 0 && k < nkinds) {
+      ms_by_kind[k] += ms;
+      launches_by_kind[k] += 1;
+    }
+  }
+  const int dropped = g_prof.n >= kProfMax;
+  g_prof.n = 0;
+  return dropped ? fail(ARCB_ERR_WORKSPACE, "profile record pool overflowed (%d records)", kProfMax) : ARCB_OK;
+}
+
 int arcb_l2norm_rows(const float* x, int64_t rows, int64_t D, int64_t ldx, void* out_bf16, int64_t Dp, float* inv_norm,
                      void* stream) {
   if (!x || !out_bf16 || !inv_norm) return fail(ARCB_ERR_INVALID, "null pointer argument");
   if (rows < 0 || D <= 0 || ldx < D || Dp < D || Dp % 64) return fail(ARCB_ERR_INVALID, "bad sizes for l2norm_rows");
   return launch_l2norm(x, rows, D, ldx, static_cast<__nv_bfloat16*>(out_bf16), Dp, inv_norm,
-                       static_cast<cudaStream_t>(stream));
+                       static_cast<cudaStream_t>(stream), ARCB_K_L2NORM_W);
 }
 
 int arcb_l2norm_rows_bwd(const float* x, int64_t ldx, const float* dxhat, int64_t ldg, int64_t rows, int64_t D,
@@ -190,6 +259,7 @@ int arcb_l2norm_rows_bwd(const float* x, int64_t ldx, const float* dxhat, int64_
   if (!x || !dxhat || !dx) return fail(ARCB_ERR_INVALID, "null pointer argument");
   if (rows <= 0 || D <= 0 || ldx < D || ldg < D || ldo < D) return fail(ARCB_ERR_INVALID, "bad sizes");
   const int blocks = static_cast<int>((rows + 7) / 8);
+  LaunchScope ls(ARCB_K_L2NORM_BWD, static_cast<cudaStream_t>(stream));
   l2norm_rows_bwd_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, ldx, dxhat, ldg, (int)rows, (int)D,
                                                                                dx, ldo);
   ARCB_CUDA(cudaGetLastError());
@@ -204,6 +274,7 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
   EpiStore::Params ep{out, ldo, (int)M, (int)N, split_k > 1 ? 1 : 0};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e;
+  LaunchScope ls(ARCB_K_GEMM_TEST, st);
   if (!a_mn && !b_mn) e = launch_gemm<EpiStore, 256, 4, false, false>(a, b, nullptr, M, N, K, split_k, ep, st);
   else if (a_mn && !b_mn) e = launch_gemm<EpiStore, 256, 4, true, false>(a, b, nullptr, M, N, K, split_k, ep, st);
   else if (!a_mn && b_mn) e = launch_gemm<EpiStore, 256, 4, false, true>(a, b, nullptr, M, N, K, split_k, ep, st);
@@ -232,12 +303,19 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
-  cudaError_t e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+  cudaError_t e;
+  {
+    LaunchScope ls(ARCB_K_FWD_GEMM, st);
+    e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+  }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
   const int blocks = static_cast<int>((B + 255) / 256);
-  merge_stats_kernel<<<blocks, 256, 0, st>>>(W.part, tiles_n, W.Bp, (int)B, W.rec);
-  pack_stats_kernel<<<blocks, 256, 0, st>>>(W.rec, W.zt, (int)B, stats);
+  {
+    LaunchScope ls(ARCB_K_MERGE, st, 2);
+    merge_stats_kernel<<<blocks, 256, 0, st>>>(W.part, tiles_n, W.Bp, (int)B, W.rec);
+    pack_stats_kernel<<<blocks, 256, 0, st>>>(W.rec, W.zt, (int)B, stats);
+  }
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;
 }
@@ -252,6 +330,7 @@ int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, 
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiLogits::Params ep{W.lbl_local, W.sub, logits, ldl, (int)B, (int)Cs, s};
+  LaunchScope ls(ARCB_K_LOGITS_GEMM, st);
   cudaError_t e = launch_gemm<EpiLogits, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "logits GEMM launch: %s", cudaGetErrorString(e));
   return ARCB_OK;
@@ -261,6 +340,7 @@ int arcb_merge_loss(const float* stats, int64_t P, int64_t B, float* lse, float*
                     void* stream) {
   if (!stats || !lse || !loss) return fail(ARCB_ERR_INVALID, "null pointer argument");
   if (P <= 0 || B <= 0) return fail(ARCB_ERR_INVALID, "bad sizes for merge_loss");
+  LaunchScope ls(ARCB_K_LOSS, static_cast<cudaStream_t>(stream));
   loss_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(stats, (int)P, (int)B, lse, target_logit, loss);
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;
@@ -276,7 +356,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   const bool ext = grad_logits != nullptr;
   if (!ext && (!lse || !target_logit)) return fail(ARCB_ERR_INVALID, "lse / target_logit required");
   if (ext && ldgl < Cs) return fail(ARCB_ERR_INVALID, "grad_logits leading dimension smaller than Cs");
-  if (reinterpret_cast<uintptr_t>(scratch) & 1023) return fail(ARCB_ERR_INVALID, "scratch must be 1024-byte aligned");
+  if (reinterpret_cast<uintptr_t>(scratch) & 255) return fail(ARCB_ERR_INVALID, "scratch must be 256-byte aligned");
   Workspace W = carve(ws, B, Cs, D);
   if (W.total > ws_bytes) return fail(ARCB_ERR_WORKSPACE, "workspace too small");
   int64_t chunk = scratch_bytes / (W.Bp * 2) / 128 * 128;
@@ -287,6 +367,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
 
   if (!ext) {
     const int blocks = static_cast<int>((W.Bp + 255) / 256);
+    LaunchScope ls(ARCB_K_BWD_PREP, st);
     bwd_prep_kernel<<<blocks, 256, 0, st>>>(lse, target_logit, grad_loss, s, (int)B, (int)W.Bp, W.lse2, W.zt2,
                                             W.gscale);
     ARCB_CUDA(cudaGetLastError());
@@ -305,6 +386,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
         return fail(ARCB_ERR_CUDA, "tensor map for the G^T scratch could not be encoded");
       Operand a{wch, rows, W.Dp, W.Dp}, b{W.xhat, B, W.Dp, W.Dp};
       cudaError_t e;
+      LaunchScope ls(ARCB_K_BWD_G_GEMM, st);
       if (!ext) {
         EpiBwdG<false>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tile_flag, W.tproj,
                                   (int)c0, (int)rows, (int)B, (int)W.Bp, s * kLog2e, nullptr, 0, 0.f};
@@ -323,6 +405,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       int split = sms / (tiles > 0 ? tiles : 1);
       if (split < 1) split = 1;
       EpiRedAdd::Params ep{dxhat, W.Dp, (int)B, (int)D};
+      LaunchScope ls(ARCB_K_DX_GEMM, st);
       cudaError_t e = launch_gemm<EpiRedAdd, kBNTile, 4, true, true>(a, b, nullptr, B, D, rows, split, ep, st);
       if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
     }
@@ -330,6 +413,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
     {
       Operand a{gt, rows, W.Bp, W.Bp}, b{W.xhat, W.Dp, B, W.Dp};
       EpiDW::Params ep{dw, W.what, W.tproj, W.inv_nw, (int)c0, (int)rows, (int)D, (int)W.Dp};
+      LaunchScope ls(ARCB_K_DW_GEMM, st);
       cudaError_t e = launch_gemm<EpiDW, kBNTile, 4, false, true>(a, b, nullptr, rows, D, B, 1, ep, st);
       if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
     }

@@ -102,6 +102,32 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
 /* Leading dimension (elements) of the dxhat buffer for feature size D. */
 int64_t arcb_padded_dim(int64_t D);
 
+/* ---- measurement aids (bench.py / tests; no counterpart in the reference) ----
+ * arcb_launch_count: kernels this library has launched so far in the process.
+ * arcb_profile_enable(1): from now on every launch is bracketed by CUDA events on its own stream
+ *   (the event pool is created here, so call it outside any timed region); (0) switches it off.
+ * arcb_profile_collect: synchronises the device, sums the elapsed milliseconds and launch counts
+ *   per kernel kind (ARCB_K_*) and clears the records. */
+enum {
+  ARCB_K_L2NORM_X = 0,    /* F.normalize(input)                      */
+  ARCB_K_L2NORM_W = 1,    /* F.normalize(weight)                     */
+  ARCB_K_TARGET_PREP = 2, /* fp32 target cosine + margin branch      */
+  ARCB_K_FWD_GEMM = 3,    /* cos GEMM + online softmax statistics    */
+  ARCB_K_MERGE = 4,       /* merge of per-tile statistics            */
+  ARCB_K_LOSS = 5,        /* cross-entropy from merged statistics    */
+  ARCB_K_BWD_PREP = 6,    /* backward set-up                         */
+  ARCB_K_BWD_G_GEMM = 7,  /* recompute cos, write bf16 dLoss/dcos    */
+  ARCB_K_DX_GEMM = 8,     /* dxhat += G * what                       */
+  ARCB_K_DW_GEMM = 9,     /* dW = G^T * xhat with normalise-backward */
+  ARCB_K_L2NORM_BWD = 10, /* F.normalize backward for the embeddings */
+  ARCB_K_LOGITS_GEMM = 11,/* materialising forward                   */
+  ARCB_K_GEMM_TEST = 12,  /* arcb_gemm_bf16                          */
+  ARCB_K_COUNT = 13
+};
+int64_t arcb_launch_count(void);
+int arcb_profile_enable(int on);
+int arcb_profile_collect(double* ms_by_kind, int64_t* launches_by_kind, int nkinds);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,92 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads and exports every symbol declared
+in include/arcface_b200.h, size queries work without a GPU, and the Python module keeps the
+reference's constructor / attribute / state_dict contract (arc_main.py:139-152)."""
+import ctypes
+import math
+import os
+import re
+
+import pytest
+import torch
+
+from ddp_classification_pytorch_b200 import ArcMarginProduct, _lib, shard_bounds
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    _lib.build()
+    return _lib.lib()
+
+
+def test_header_symbols_are_exported(built):
+    hdr = open(os.path.join(ROOT, "include", "arcface_b200.h")).read()
+    declared = set(re.findall(r"\b(arcb_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.EXPORTED)
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    for sym in declared:
+        assert getattr(handle, sym) is not None
+
+
+def test_size_queries_without_gpu(built):
+    L = built
+    assert L.arcb_version() >= 100
+    assert L.arcb_padded_dim(512) == 512 and L.arcb_padded_dim(72) == 128
+    ws = L.arcb_ws_bytes(1024, 1_000_000, 512)
+    # dominated by the bf16 copy of the normalised weight (2 B/elem) + per-tile softmax partials
+    assert 1_000_000 * 512 * 2 < ws < 1_000_000 * 512 * 2 * 1.1
+    assert L.arcb_scratch_bytes(1024, 128 * 148) == 128 * 148 * 1024 * 2
+    assert L.arcb_ws_bytes(0, 10, 10) < 0
+    assert L.arcb_launch_count() == 0
+
+
+def test_errors_are_codes_not_exceptions(built):
+    L = built
+    rc = L.arcb_l2norm_rows(None, 4, 8, 8, None, 64, None, None)
+    assert rc == -1 and b"null" in L.arcb_last_error()
+    rc = L.arcb_shard_backward(4, 4, 4, 30.0, None, 0, None, None, None, None, 0, None, 0, None, None, None)
+    assert rc == -1
+
+
+def test_module_contract_matches_reference():
+    head = ArcMarginProduct(256, 2173, s=30, m=0.5, easy_margin=True)  # arc_main.py:234
+    assert (head.in_features, head.out_features, head.s, head.m, head.easy_margin) == (256, 2173, 30, 0.5, True)
+    assert head.cos_m == math.cos(0.5) and head.sin_m == math.sin(0.5)
+    assert head.th == math.cos(math.pi - 0.5) and head.mm == math.sin(math.pi - 0.5) * 0.5
+    assert list(head.state_dict().keys()) == ["weight"]
+    assert tuple(head.weight.shape) == (2173, 256) and head.weight.dtype == torch.float32
+    bound = math.sqrt(6.0 / (256 + 2173))  # xavier_uniform_, arc_main.py:146
+    assert head.weight.abs().max().item() <= bound and head.weight.abs().max().item() > 0.9 * bound
+    d = ArcMarginProduct(8, 4)
+    assert d.s == 30.0 and d.m == 0.5 and d.easy_margin is False
+    opt = torch.optim.SGD(head.parameters(), lr=0.1)  # arc_main.py:252
+    assert len(opt.param_groups[0]["params"]) == 1
+    head.train(); head.eval()
+
+
+def test_no_cpu_fallback():
+    head = ArcMarginProduct(16, 8)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        head(torch.randn(4, 16), torch.zeros(4, dtype=torch.long))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        head.forward_loss(torch.randn(4, 16), torch.zeros(4, dtype=torch.long))
+    with pytest.raises(IndexError):
+        head(torch.randn(16), torch.zeros(1))
+
+
+def test_shard_bounds_partition():
+    for C, P in ((1_000_000, 8), (10, 3), (7, 8), (100_000, 4)):
+        spans = [shard_bounds(C, P, r) for r in range(P)]
+        assert spans[0][0] == 0 and spans[-1][1] == C
+        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+        sizes = [hi - lo for lo, hi in spans]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_product_package_never_imports_oracle():
+    pkg = os.path.join(ROOT, "ddp_classification_pytorch_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                assert "oracle" not in open(os.path.join(dirpath, f)).read().lower(), f

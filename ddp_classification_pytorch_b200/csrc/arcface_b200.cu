@@ -70,6 +70,7 @@ struct LaunchScope {
 };
 
 constexpr int kBNTile = 256;
+constexpr int kMergeSlices = 64;
 
 // Persistent per-shard workspace, carved deterministically from one caller-owned buffer.
 struct Workspace {
@@ -86,6 +87,7 @@ struct Workspace {
   unsigned char* tile_flag;  // [ceil(Cs/128)]
   float2* part;          // [tiles_n, Bp]
   float2* rec;           // [Bp]
+  float2* rec2;          // [kMergeSlices, Bp] first-level merge
   float* lse2;           // [Bp]
   float* zt2;            // [Bp]
   float* gscale;         // [1]
@@ -118,6 +120,7 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
   w.tile_flag = reinterpret_cast<unsigned char*>(take((Cs + 127) / 128));
   w.part = reinterpret_cast<float2*>(take(tiles_n * w.Bp * 8));
   w.rec = reinterpret_cast<float2*>(take(w.Bp * 8));
+  w.rec2 = reinterpret_cast<float2*>(take(kMergeSlices * w.Bp * 8));
   w.lse2 = reinterpret_cast<float*>(take(w.Bp * 4));
   w.zt2 = reinterpret_cast<float*>(take(w.Bp * 4));
   w.gscale = reinterpret_cast<float*>(take(4));
@@ -312,8 +315,9 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
   const int blocks = static_cast<int>((B + 255) / 256);
   {
-    LaunchScope ls(ARCB_K_MERGE, st, 2);
-    merge_stats_kernel<<<blocks, 256, 0, st>>>(W.part, tiles_n, W.Bp, (int)B, W.rec);
+    LaunchScope ls(ARCB_K_MERGE, st, 3);
+    merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, tiles_n, W.Bp, (int)B, W.rec2, W.Bp);
+    merge_stats_kernel<<<dim3(blocks, 1), 256, 0, st>>>(W.rec2, kMergeSlices, W.Bp, (int)B, W.rec, W.Bp);
     pack_stats_kernel<<<blocks, 256, 0, st>>>(W.rec, W.zt, (int)B, stats);
   }
   ARCB_CUDA(cudaGetLastError());

@@ -192,7 +192,8 @@ struct EpiLogits {
 // and g_ij = grad_out_ij * s * (dphi_i at the label column, 1 elsewhere).
 template <bool EXT>
 struct EpiBwdG {
-  static constexpr int kSmemBytes = kBM * 256 * 2;  // one bf16 tile, 4 boxes of [128 x 64]
+  static constexpr int kStageBytes = kBM * 256 * 2;  // one bf16 tile, 4 boxes of [128 x 64]
+  static constexpr int kSmemBytes = kStageBytes + 256 * 4;  // + lse2 of the tile's 256 samples
   static constexpr bool kUsesTmC = true;
   struct Params {
     const float* lse2;       // [Bp] lse * log2(e); +inf beyond B
@@ -224,6 +225,11 @@ struct EpiBwdG {
     static_assert(BN == 256, "staging tile is sized for BN = 256");
     // the previous tile's TMA stores must have finished reading the staging tile
     if (epi_tid == 0) tma_store_wait_read0();
+    float* lse_s = reinterpret_cast<float*>(smem + kStageBytes);
+    if constexpr (!EXT) {
+      const float2 l2 = __ldg(reinterpret_cast<const float2*>(p.lse2 + tc.n_blk * BN) + epi_tid);
+      reinterpret_cast<float2*>(lse_s)[epi_tid] = l2;
+    }
     named_bar_sync(1, kEpiThreads);
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const int cls = p.row_off + row_local;
@@ -240,7 +246,7 @@ struct EpiBwdG {
       if constexpr (!EXT) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-          const float4 l4 = __ldg(reinterpret_cast<const float4*>(p.lse2 + col0 + j));
+          const float4 l4 = *reinterpret_cast<const float4*>(lse_s + c + j);
           g[j + 0] = ex2_approx(fmaf(v[j + 0], p.s2, -l4.x)) * st.gscale;
           g[j + 1] = ex2_approx(fmaf(v[j + 1], p.s2, -l4.y)) * st.gscale;
           g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * st.gscale;
@@ -377,18 +383,32 @@ struct EpiDW {
       tj = (inv < 0.5e12f) ? __ldg(p.t + cls) : 0.f;  // clamped rows take no projection
     }
     const bool vec_ok = (p.D & 3) == 0;
+    const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
+    uint4 wnext[4];
+    {
+      const int col0 = tc.n_blk * BN;
+      if (col0 < p.D) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) wnext[q] = __ldg(reinterpret_cast<const uint4*>(wrow + col0) + q);
+      }
+    }
     for (int c = 0; c < BN; c += 32) {
       const int col0 = tc.n_blk * BN + c;
       if (col0 >= p.D) break;
+      uint4 wcur[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) wcur[q] = wnext[q];
+      if (c + 32 < BN && col0 + 32 < p.D) {  // prefetch the next chunk of w_hat before touching TMEM
+#pragma unroll
+        for (int q = 0; q < 4; ++q) wnext[q] = __ldg(reinterpret_cast<const uint4*>(wrow + col0 + 32) + q);
+      }
       float v[32];
       tmem_ld32(taddr + c, v);
       if (valid) {
-        const uint4* wp = reinterpret_cast<const uint4*>(p.what + static_cast<int64_t>(cls) * p.Dp + col0);
         float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const uint4 wq = __ldg(wp + q);
-          const uint32_t wr[4] = {wq.x, wq.y, wq.z, wq.w};
+          const uint32_t wr[4] = {wcur[q].x, wcur[q].y, wcur[q].z, wcur[q].w};
           float r[8];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {

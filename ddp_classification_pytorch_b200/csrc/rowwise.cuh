@@ -141,19 +141,27 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
   }
 }
 
-// part[n][ldp] (base-2 max, sum) -> rec[row] = merged (max, sum).  One thread per row.
+// part[n][ldp] (base-2 max, sum) -> out[slice][ldo] = merged (max, sum) over the slice's share of n.
+// grid = (ceil(B / 256), slices): thread = one row, block y = one slice of the partial list, so the
+// 8 B loads of a warp are coalesced and n / slices of them are in flight per thread.
 __global__ void __launch_bounds__(256)
-merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, float2* __restrict__ rec) {
+merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, float2* __restrict__ out,
+                   int64_t ldo) {
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= B) return;
-  float m = -INFINITY;
-  for (int k = 0; k < n; ++k) m = fmaxf(m, part[k * ldp + row].x);
-  float l = 0.f;
-  for (int k = 0; k < n; ++k) {
+  const int per = (n + gridDim.y - 1) / gridDim.y;
+  const int k0 = blockIdx.y * per;
+  const int k1 = min(n, k0 + per);
+  float m = -INFINITY, l = 0.f;
+  for (int k = k0; k < k1; ++k) {  // online merge: one pass, no second read
     const float2 p = part[k * ldp + row];
-    l += p.y * exp2f(p.x - m);
+    if (p.x == -INFINITY) continue;  // empty slice: nothing to add (and -inf - -inf would be NaN)
+    const float nm = fmaxf(m, p.x);
+    l = l * exp2f(m - nm) + p.y * exp2f(p.x - nm);
+    m = nm;
   }
-  rec[row] = make_float2(m, l);
+  if (k0 >= k1) { m = -INFINITY; l = 0.f; }
+  out[blockIdx.y * ldo + row] = make_float2(m, l);
 }
 
 // stats[P][B][4] = (m2, l, zt, -) per shard -> lse[B] (natural log units), loss = mean(lse - zt).

@@ -115,7 +115,9 @@ def test_grad_scale_and_label_dtypes():
             assert np.linalg.norm(x.grad.cpu().numpy()) == pytest.approx(2.5 * np.linalg.norm(g["dx"]), rel=2e-2)
         else:
             assert loss.item() == base[0]
-            assert torch.equal(x.grad, base[1]) and torch.equal(head.weight.grad, base[2])
+            # split-K / projection sums use fp32 atomics, so the summation order may differ run to run
+            torch.testing.assert_close(x.grad, base[1], rtol=1e-4, atol=1e-6)
+            torch.testing.assert_close(head.weight.grad, base[2], rtol=1e-4, atol=1e-6)
 
 
 def test_contract_errors():

@@ -84,8 +84,7 @@ struct Workspace {
   float* zt;             // [Bp]
   float* dphi;           // [Bp]
   float* cos_t;          // [Bp]
-  unsigned char* tile_flag;  // [ceil(Cs/128)]
-  float2* part;          // [tiles_n, Bp]
+  float2* part;          // [2 * tiles_n, Bp] one partial per (column block, epilogue warpgroup)
   float2* rec;           // [Bp]
   float2* rec2;          // [kMergeSlices, Bp] first-level merge
   float* lse2;           // [Bp]
@@ -117,8 +116,7 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
   w.zt = reinterpret_cast<float*>(take(w.Bp * 4));
   w.dphi = reinterpret_cast<float*>(take(w.Bp * 4));
   w.cos_t = reinterpret_cast<float*>(take(w.Bp * 4));
-  w.tile_flag = reinterpret_cast<unsigned char*>(take((Cs + 127) / 128));
-  w.part = reinterpret_cast<float2*>(take(tiles_n * w.Bp * 8));
+  w.part = reinterpret_cast<float2*>(take(2 * tiles_n * w.Bp * 8));
   w.rec = reinterpret_cast<float2*>(take(w.Bp * 8));
   w.rec2 = reinterpret_cast<float2*>(take(kMergeSlices * w.Bp * 8));
   w.lse2 = reinterpret_cast<float*>(take(w.Bp * 4));
@@ -177,7 +175,6 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   if (rc) return rc;
   rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
   if (rc) return rc;
-  ARCB_CUDA(cudaMemsetAsync(W.tile_flag, 0, (Cs + 127) / 128, st));
   const double md = static_cast<double>(m);
   const float cos_m = static_cast<float>(cos(md)), sin_m = static_cast<float>(sin(md));
   const float th = static_cast<float>(cos(M_PI - md)), mm = static_cast<float>(sin(M_PI - md) * md);
@@ -185,7 +182,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   LaunchScope ls(ARCB_K_TARGET_PREP, st);
   target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.inv_nx, W.inv_nw, (int)B, (int)W.Bp, (int)D, Cs,
                                              class_offset, s, cos_m, sin_m, th, mm, easy, W.lbl_local, W.sub, W.zt,
-                                             W.dphi, W.cos_t, W.tile_flag);
+                                             W.dphi, W.cos_t);
   ARCB_CUDA(cudaGetLastError());
   *out_ws = W;
   return ARCB_OK;
@@ -316,7 +313,7 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
   const int blocks = static_cast<int>((B + 255) / 256);
   {
     LaunchScope ls(ARCB_K_MERGE, st, 3);
-    merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, tiles_n, W.Bp, (int)B, W.rec2, W.Bp);
+    merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, 2 * tiles_n, W.Bp, (int)B, W.rec2, W.Bp);
     merge_stats_kernel<<<dim3(blocks, 1), 256, 0, st>>>(W.rec2, kMergeSlices, W.Bp, (int)B, W.rec, W.Bp);
     pack_stats_kernel<<<blocks, 256, 0, st>>>(W.rec, W.zt, (int)B, stats);
   }
@@ -380,6 +377,12 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   ARCB_CUDA(cudaMemsetAsync(dxhat, 0, B * W.Dp * 4, st));
 
   const int sms = device_sm_count();
+  // fp32 outputs leave the GEMM epilogues as bulk tensor stores / reduce-adds of [128 x 32] boxes
+  CUtensorMap tmDx, tmDw;
+  if (!make_tmap_2d(&tmDx, dxhat, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, B, W.Dp * 4, 32, kBM))
+    return fail(ARCB_ERR_CUDA, "tensor map for dxhat could not be encoded (16-byte alignment?)");
+  const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
+                      make_tmap_2d(&tmDw, dw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, Cs, D * 4, 32, kBM);
   for (int64_t c0 = 0; c0 < Cs; c0 += chunk) {
     const int64_t rows = (Cs - c0 < chunk) ? (Cs - c0) : chunk;
     const __nv_bfloat16* wch = W.what + c0 * W.Dp;
@@ -392,11 +395,11 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       cudaError_t e;
       LaunchScope ls(ARCB_K_BWD_G_GEMM, st);
       if (!ext) {
-        EpiBwdG<false>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tile_flag, W.tproj,
+        EpiBwdG<false>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tproj,
                                   (int)c0, (int)rows, (int)B, (int)W.Bp, s * kLog2e, nullptr, 0, 0.f};
         e = launch_gemm<EpiBwdG<false>, kBNTile, 3, false, false>(a, b, &tmG, rows, B, W.Dp, 1, ep, st);
       } else {
-        EpiBwdG<true>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tile_flag, W.tproj,
+        EpiBwdG<true>::Params ep{W.lse2, W.gscale, W.lbl_local, W.zt2, W.dphi, W.cos_t, W.tproj,
                                  (int)c0, (int)rows, (int)B, (int)W.Bp, s * kLog2e, grad_logits + c0, ldgl, s};
         e = launch_gemm<EpiBwdG<true>, kBNTile, 3, false, false>(a, b, &tmG, rows, B, W.Dp, 1, ep, st);
       }
@@ -408,17 +411,17 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       const int tiles = static_cast<int>(((B + kBM - 1) / kBM) * ((D + kBNTile - 1) / kBNTile));
       int split = sms / (tiles > 0 ? tiles : 1);
       if (split < 1) split = 1;
-      EpiRedAdd::Params ep{dxhat, W.Dp, (int)B, (int)D};
+      EpiRedAdd::Params ep{(int)B, (int)D};
       LaunchScope ls(ARCB_K_DX_GEMM, st);
-      cudaError_t e = launch_gemm<EpiRedAdd, kBNTile, 4, true, true>(a, b, nullptr, B, D, rows, split, ep, st);
+      cudaError_t e = launch_gemm<EpiRedAdd, kBNTile, 3, true, true>(a, b, &tmDx, B, D, rows, split, ep, st);
       if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
     }
     // (3) dW[rows, D] = inv_norm * (G^T[rows, B] * xhat[B, D] - t * what)
     {
       Operand a{gt, rows, W.Bp, W.Bp}, b{W.xhat, W.Dp, B, W.Dp};
-      EpiDW::Params ep{dw, W.what, W.tproj, W.inv_nw, (int)c0, (int)rows, (int)D, (int)W.Dp};
+      EpiDW::Params ep{dw, W.what, W.tproj, W.inv_nw, (int)c0, (int)rows, (int)D, (int)W.Dp, dw_tma ? 1 : 0};
       LaunchScope ls(ARCB_K_DW_GEMM, st);
-      cudaError_t e = launch_gemm<EpiDW, kBNTile, 4, false, true>(a, b, nullptr, rows, D, B, 1, ep, st);
+      cudaError_t e = launch_gemm<EpiDW, kBNTile, 3, false, true>(a, b, dw_tma ? &tmDw : nullptr, rows, D, B, 1, ep, st);
       if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
     }
   }

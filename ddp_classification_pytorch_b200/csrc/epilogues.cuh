@@ -1,5 +1,6 @@
-// Epilogue policies for gemm_sm100_kernel.  Each thread owns ONE accumulator row (a TMEM lane)
-// and walks the tile's BN columns in chunks of 32 fp32 values pulled with tcgen05.ld.
+// Epilogue policies for gemm_sm100_kernel.  Each epilogue thread owns ONE accumulator row (a TMEM
+// lane); the two epilogue warpgroups split the tile's BN columns in halves and walk their half in
+// chunks of 32 fp32 values pulled with tcgen05.ld (epi_tid >> 7 = warpgroup, & 127 = row).
 //
 //   EpiStore      plain fp32 store (unit tests of the GEMM core)
 //   EpiFwdStats   forward: margin substitution at the label column, online (max, sum-exp)
@@ -9,7 +10,7 @@
 //   EpiBwdG       backward recompute: G^T = dLoss/dcos for a class chunk, bf16, through a
 //                 swizzled smem tile + TMA store; also the per-class projection term used by
 //                 the weight-normalisation backward                 (autograd behind arc_main.py:329)
-//   EpiRedAdd     split-K accumulate into fp32 global (dX_hat partial sums)
+//   EpiRedAdd     split-K accumulate into fp32 global (dX_hat partial sums), TMA reduce-add
 //   EpiDW         dW = inv_norm * (dW_hat - t * w_hat): F.normalize backward fused into the store
 #pragma once
 
@@ -21,6 +22,42 @@
 namespace arcb {
 
 struct EpiNoState {};
+struct EpiOutState {
+  int it;  // chunks this warpgroup has sent so far: selects the smem buffer, survives across tiles
+};
+
+constexpr int kWgThreads = 128;
+
+// One 32-column fp32 chunk of the tile (128 rows x 128 B) goes through a 128B-swizzled smem buffer
+// and leaves as ONE bulk tensor store / reduce-add instead of 32-sector-per-instruction row stores.
+// Each warpgroup owns two 16 KB buffers and alternates between them.
+constexpr int kChunkBufBytes = kBM * 128;
+constexpr int kChunkOutSmem = 2 * 2 * kChunkBufBytes;
+
+template <bool REDUCE>
+__device__ __forceinline__ void chunk_out_tma(const CUtensorMap& tm, uint8_t* epi_smem, int wg, int wg_tid,
+                                              int row_in_tile, int iter, const float (&r)[32], int c_inner,
+                                              int c_outer) {
+  uint8_t* buf = epi_smem + (wg * 2 + (iter & 1)) * kChunkBufBytes;
+  // the store that used this buffer two chunks ago must have finished reading it
+  if (wg_tid == 0) tma_store_wait_read<1>();
+  named_bar_sync(2 + wg, kWgThreads);
+  const uint32_t base = smem_u32(buf) + row_in_tile * 128;
+  const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const uint32_t a = base + ((static_cast<uint32_t>(q) ^ sw) << 4);
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(r[4 * q]), "f"(r[4 * q + 1]),
+                 "f"(r[4 * q + 2]), "f"(r[4 * q + 3])
+                 : "memory");
+  }
+  fence_proxy_async_smem();
+  named_bar_sync(2 + wg, kWgThreads);
+  if (wg_tid == 0) {
+    if (REDUCE) tma_reduce_add_2d(&tm, buf, c_inner, c_outer); else tma_store_2d(&tm, buf, c_inner, c_outer);
+    tma_store_commit();
+  }
+}
 
 // ------------------------------------------------------------------------------------
 struct EpiStore {
@@ -36,10 +73,11 @@ struct EpiStore {
   __device__ static void init(const Params&, State&) {}
   __device__ static void drain(int) {}
   template <int BN>
-  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
-                                 uint8_t*) {
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, const CUtensorMap&, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t*) {
+    const int wg = epi_tid >> 7;
     const int row = tc.m_blk * kBM + row_in_tile;
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = wg * (BN / 2); c < (wg + 1) * (BN / 2); c += 32) {
       const int col0 = tc.n_blk * BN + c;
       if (col0 >= p.N) break;
       float v[32];
@@ -61,13 +99,14 @@ struct EpiStore {
 // ------------------------------------------------------------------------------------
 // Forward statistics.  Rows = batch samples, columns = classes of this shard.
 // Works in base-2 units: u = cos * s2 with s2 = s * log2(e); a partial is (max u, sum 2^(u-max)).
+// Each (tile column block, warpgroup) writes one partial per row: part[(n_blk * 2 + wg)][row].
 struct EpiFwdStats {
   static constexpr int kSmemBytes = 0;
   static constexpr bool kUsesTmC = false;
   struct Params {
     const int* lbl_local;  // [Bp] label - class_offset if this shard owns it, else -1
     const float* phi;      // [Bp] value that replaces the target cosine (phi or the fallback)
-    float2* part;          // [tiles_n][ldp]
+    float2* part;          // [2 * tiles_n][ldp]
     int ldp;
     int B, C;
     float s2;
@@ -76,8 +115,9 @@ struct EpiFwdStats {
   __device__ static void init(const Params&, State&) {}
   __device__ static void drain(int) {}
   template <int BN>
-  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
-                                 uint8_t*) {
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, const CUtensorMap&, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t*) {
+    const int wg = epi_tid >> 7;
     const int row = tc.m_blk * kBM + row_in_tile;
     int lbl = -1;
     float phi = 0.f;
@@ -87,7 +127,7 @@ struct EpiFwdStats {
     }
     float run_m = -INFINITY, run_l = 0.f;
     const int col_base = tc.n_blk * BN;
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = wg * (BN / 2); c < (wg + 1) * (BN / 2); c += 32) {
       const int col0 = col_base + c;
       if (col0 >= p.C) break;
       float v[32];
@@ -120,7 +160,8 @@ struct EpiFwdStats {
       run_l += (a0 + a1) + (a2 + a3);
       run_m = nm;
     }
-    if (row < p.B) p.part[static_cast<int64_t>(tc.n_blk) * p.ldp + row] = make_float2(run_m * p.s2, run_l);
+    if (row < p.B)
+      p.part[static_cast<int64_t>(tc.n_blk * 2 + wg) * p.ldp + row] = make_float2(run_m * p.s2, run_l);
   }
   template <int BN>
   __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
@@ -142,8 +183,9 @@ struct EpiLogits {
   __device__ static void init(const Params&, State&) {}
   __device__ static void drain(int) {}
   template <int BN>
-  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
-                                 uint8_t*) {
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, const CUtensorMap&, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t*) {
+    const int wg = epi_tid >> 7;
     const int row = tc.m_blk * kBM + row_in_tile;
     int lbl = -1;
     float phi = 0.f;
@@ -152,7 +194,7 @@ struct EpiLogits {
       phi = __ldg(p.phi + row);
     }
     const bool vec_ok = (p.ldo & 3) == 0;
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = wg * (BN / 2); c < (wg + 1) * (BN / 2); c += 32) {
       const int col0 = tc.n_blk * BN + c;
       if (col0 >= p.C) break;
       float v[32];
@@ -183,32 +225,32 @@ struct EpiLogits {
 
 // ------------------------------------------------------------------------------------
 // Backward recompute.  Rows = classes of the current chunk, columns = batch samples.
-//   g_ij = gscale * (softmax_ij - onehot_ij) * d logit / d cos     with gscale = dLoss * 1/B
-// (the factor s of d logit/d cos is folded into gscale by the caller: gscale = grad * s / B).
+//   g_ij = gscale * (softmax_ij - onehot_ij) * d logit / d cos     with gscale = dLoss * s / B
 // Non-target: g = gscale * 2^(cos*s2 - lse2_i).  Target: g = gscale * (2^(zt2_i - lse2_i) - 1) * dphi_i.
 // The tile is written as bf16 G^T[class, sample] through a 128B-swizzled smem tile and TMA.
 // t_j = sum_i g_ij * cos_ij is the projection w_hat_j . dW_hat_j needed by F.normalize's backward.
 // EXT = true is the materialising path: dLoss/dlogits arrives from autograd as grad_out[B, ldgo]
 // and g_ij = grad_out_ij * s * (dphi_i at the label column, 1 elsewhere).
+// The labels and log-sum-exps of the tile's 256 samples are staged in smem once per tile; a warp
+// ballot finds the (rare) chunks that contain a label of this 128-class tile.
 template <bool EXT>
 struct EpiBwdG {
-  static constexpr int kStageBytes = kBM * 256 * 2;  // one bf16 tile, 4 boxes of [128 x 64]
-  static constexpr int kSmemBytes = kStageBytes + 256 * 4;  // + lse2 of the tile's 256 samples
+  static constexpr int kStageBytes = kBM * 256 * 2;             // bf16 tile, 4 boxes of [128 x 64]
+  static constexpr int kSmemBytes = kStageBytes + 256 * 4 * 2;  // + lse2 and labels of the tile's samples
   static constexpr bool kUsesTmC = true;
   struct Params {
     const float* lse2;       // [Bp] lse * log2(e); +inf beyond B
     const float* gscale;     // device scalar: upstream grad * s / B
-    const int* lbl_local;    // [Bp]
+    const int* lbl_local;    // [Bp], -1 = not in this shard / padding
     const float* zt2;        // [Bp] target logit * log2(e)
     const float* dphi;       // [Bp] d(target value)/d cos
     const float* cos_t;      // [Bp] exact fp32 target cosine
-    const unsigned char* tile_flag;  // [ceil(Cs/128)] 1 if some label falls into that class tile
     float* t_out;            // [Cs] accumulates t_j (atomicAdd across batch tiles)
     int row_off;             // first class of this chunk inside the shard (multiple of 128)
     int rows_valid;          // classes in this chunk
     int B, Bp;
     float s2;
-    const float* grad_out;   // EXT only: [B, ldgo] columns of this chunk
+    const float* grad_out;   // EXT only: [B, ldgo], column 0 = first class of this chunk
     int64_t ldgo;
     float s_ext;
   };
@@ -220,26 +262,27 @@ struct EpiBwdG {
     if (epi_tid == 0) tma_store_wait_all0();
   }
   template <int BN>
-  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, uint32_t taddr, int row_in_tile,
-                                 int epi_tid, uint8_t* smem) {
+  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap&, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t* smem) {
     static_assert(BN == 256, "staging tile is sized for BN = 256");
+    const int wg = epi_tid >> 7;
+    const int lane = epi_tid & 31;
     // the previous tile's TMA stores must have finished reading the staging tile
     if (epi_tid == 0) tma_store_wait_read0();
     float* lse_s = reinterpret_cast<float*>(smem + kStageBytes);
-    if constexpr (!EXT) {
-      const float2 l2 = __ldg(reinterpret_cast<const float2*>(p.lse2 + tc.n_blk * BN) + epi_tid);
-      reinterpret_cast<float2*>(lse_s)[epi_tid] = l2;
-    }
+    int* lbl_s = reinterpret_cast<int*>(smem + kStageBytes + 256 * 4);
+    if constexpr (!EXT) lse_s[epi_tid] = __ldg(p.lse2 + tc.n_blk * BN + epi_tid);
+    lbl_s[epi_tid] = __ldg(p.lbl_local + tc.n_blk * BN + epi_tid);
     named_bar_sync(1, kEpiThreads);
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const int cls = p.row_off + row_local;
-    const bool slow = p.tile_flag[(p.row_off >> 7) + tc.m_blk] != 0;
+    const int tile_cls0 = p.row_off + tc.m_blk * kBM;
+    const bool row_ok = row_local < p.rows_valid;
     float tsum = 0.f;
     const uint32_t srow = smem_u32(smem) + row_in_tile * 128;
     const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = wg * (BN / 2); c < (wg + 1) * (BN / 2); c += 32) {
       const int col0 = tc.n_blk * BN + c;
-      if (col0 >= p.Bp) break;
       float v[32];
       tmem_ld32(taddr + c, v);
       float g[32];
@@ -252,18 +295,7 @@ struct EpiBwdG {
           g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * st.gscale;
           g[j + 3] = ex2_approx(fmaf(v[j + 3], p.s2, -l4.w)) * st.gscale;
         }
-        if (slow) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (__ldg(p.lbl_local + col0 + j) == cls) {
-              const int i = col0 + j;
-              g[j] = st.gscale * (ex2_approx(__ldg(p.zt2 + i) - __ldg(p.lse2 + i)) - 1.f) * __ldg(p.dphi + i);
-              v[j] = __ldg(p.cos_t + i);
-            }
-          }
-        }
       } else {
-        const bool row_ok = row_local < p.rows_valid;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int i = col0 + j;
@@ -271,15 +303,30 @@ struct EpiBwdG {
           if (row_ok && i < p.B) gj = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext;
           g[j] = gj;
         }
-        if (slow) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (__ldg(p.lbl_local + col0 + j) == cls) {
-              const int i = col0 + j;
-              g[j] *= __ldg(p.dphi + i);
-              v[j] = __ldg(p.cos_t + i);
-            }
+      }
+      // label columns of this chunk that fall into this tile's 128 classes (warp-uniform, rare)
+      const int my_lbl = lbl_s[c + lane];
+      unsigned hit = __ballot_sync(0xffffffffu, static_cast<unsigned>(my_lbl - tile_cls0) < static_cast<unsigned>(kBM));
+      while (hit) {
+        const int j = __ffs(hit) - 1;
+        hit &= hit - 1;
+        const int tl = __shfl_sync(0xffffffffu, my_lbl, j);
+        if (tl == cls) {  // the one thread that owns the label's class row
+          const int i = col0 + j;
+          const float ct = __ldg(p.cos_t + i);
+          const float dp = __ldg(p.dphi + i);
+          float gt;
+          if constexpr (!EXT) {
+            gt = st.gscale * (ex2_approx(__ldg(p.zt2 + i) - lse_s[c + j]) - 1.f) * dp;
+          } else {
+            gt = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext * dp;
           }
+#pragma unroll
+          for (int jj = 0; jj < 32; ++jj)
+            if (jj == j) {
+              g[jj] = gt;
+              v[jj] = ct;
+            }
         }
       }
 #pragma unroll
@@ -296,7 +343,7 @@ struct EpiBwdG {
                      : "memory");
       }
     }
-    if (row_local < p.rows_valid) atomicAdd(p.t_out + cls, tsum);
+    if (row_ok) atomicAdd(p.t_out + cls, tsum);
   }
   template <int BN>
   __device__ static void finish(const Params& p, State&, const TileCoord& tc, const CUtensorMap& tmC, int, int epi_tid,
@@ -315,38 +362,28 @@ struct EpiBwdG {
 };
 
 // ------------------------------------------------------------------------------------
+// Split-K partial sums: global[M, N] += tile, as bulk tensor reduce-adds (fp32) in L2.
 struct EpiRedAdd {
-  static constexpr int kSmemBytes = 0;
-  static constexpr bool kUsesTmC = false;
+  static constexpr int kSmemBytes = kChunkOutSmem;
+  static constexpr bool kUsesTmC = true;  // tmC: fp32 [M, N] destination, box [128 x 32]
   struct Params {
-    float* out;  // [M, ldo] fp32, ldo % 4 == 0, zero-initialised by the caller
-    int64_t ldo;
     int M, N;
   };
-  using State = EpiNoState;
-  __device__ static void init(const Params&, State&) {}
-  __device__ static void drain(int) {}
+  using State = EpiOutState;
+  __device__ static void init(const Params&, State& st) { st.it = 0; }
+  __device__ static void drain(int epi_tid) {
+    if ((epi_tid & 127) == 0) tma_store_wait_all0();
+  }
   template <int BN>
-  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
-                                 uint8_t*) {
-    const int row = tc.m_blk * kBM + row_in_tile;
-    for (int c = 0; c < BN; c += 32) {
+  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t* smem) {
+    const int wg = epi_tid >> 7;
+    for (int c = wg * (BN / 2); c < (wg + 1) * (BN / 2); c += 32) {
       const int col0 = tc.n_blk * BN + c;
       if (col0 >= p.N) break;
       float v[32];
       tmem_ld32(taddr + c, v);
-      if (row < p.M) {
-        float* o = p.out + static_cast<int64_t>(row) * p.ldo + col0;
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          if (col0 + j + 3 < p.N) {
-            red_add_v4(o + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-            for (int e = 0; e < 4; ++e)
-              if (col0 + j + e < p.N) atomicAdd(o + j + e, v[j + e]);
-          }
-        }
-      }
+      chunk_out_tma<true>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, v, col0, tc.m_blk * kBM);
     }
   }
   template <int BN>
@@ -357,9 +394,10 @@ struct EpiRedAdd {
 // Rows = classes of the chunk, columns = feature index.  Final dW for those rows:
 //   dW_j = inv_norm_j * (dW_hat_j - t_j * w_hat_j)          (||w_j|| above the F.normalize eps)
 //   dW_j = inv_norm_j * dW_hat_j                            (clamped rows: y = w / eps)
+// use_tma: dW leaves as bulk tensor stores (needs D % 4 == 0); otherwise plain row stores.
 struct EpiDW {
-  static constexpr int kSmemBytes = 0;
-  static constexpr bool kUsesTmC = false;
+  static constexpr int kSmemBytes = kChunkOutSmem;
+  static constexpr bool kUsesTmC = true;  // tmC: fp32 dW [Cs, D], box [128 x 32]
   struct Params {
     float* dw;                  // [Cs, D] fp32, pitch D
     const __nv_bfloat16* what;  // [Cs, Dp] bf16
@@ -367,13 +405,17 @@ struct EpiDW {
     const float* inv_norm;      // [Cs] 1 / max(||w||, eps)
     int row_off, rows_valid;
     int D, Dp;
+    int use_tma;
   };
-  using State = EpiNoState;
-  __device__ static void init(const Params&, State&) {}
-  __device__ static void drain(int) {}
+  using State = EpiOutState;
+  __device__ static void init(const Params&, State& st) { st.it = 0; }
+  __device__ static void drain(int epi_tid) {
+    if ((epi_tid & 127) == 0) tma_store_wait_all0();
+  }
   template <int BN>
-  __device__ static void consume(const Params& p, State&, const TileCoord& tc, uint32_t taddr, int row_in_tile, int,
-                                 uint8_t*) {
+  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t* smem) {
+    const int wg = epi_tid >> 7;
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const bool valid = row_local < p.rows_valid;
     const int cls = p.row_off + row_local;
@@ -382,51 +424,44 @@ struct EpiDW {
       inv = __ldg(p.inv_norm + cls);
       tj = (inv < 0.5e12f) ? __ldg(p.t + cls) : 0.f;  // clamped rows take no projection
     }
-    const bool vec_ok = (p.D & 3) == 0;
     const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
+    const int c_begin = wg * (BN / 2), c_end = (wg + 1) * (BN / 2);
     uint4 wnext[4];
-    {
-      const int col0 = tc.n_blk * BN;
-      if (col0 < p.D) {
+    if (tc.n_blk * BN + c_begin < p.D) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) wnext[q] = __ldg(reinterpret_cast<const uint4*>(wrow + col0) + q);
-      }
+      for (int q = 0; q < 4; ++q) wnext[q] = __ldg(reinterpret_cast<const uint4*>(wrow + tc.n_blk * BN + c_begin) + q);
     }
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = c_begin; c < c_end; c += 32) {
       const int col0 = tc.n_blk * BN + c;
       if (col0 >= p.D) break;
       uint4 wcur[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) wcur[q] = wnext[q];
-      if (c + 32 < BN && col0 + 32 < p.D) {  // prefetch the next chunk of w_hat before touching TMEM
+      if (c + 32 < c_end && col0 + 32 < p.D) {  // prefetch the next chunk of w_hat before touching TMEM
 #pragma unroll
         for (int q = 0; q < 4; ++q) wnext[q] = __ldg(reinterpret_cast<const uint4*>(wrow + col0 + 32) + q);
       }
       float v[32];
       tmem_ld32(taddr + c, v);
-      if (valid) {
+      float r[32];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t wr[4] = {wcur[q].x, wcur[q].y, wcur[q].z, wcur[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float w0 = __uint_as_float(wr[e] << 16);
+          const float w1 = __uint_as_float(wr[e] & 0xffff0000u);
+          r[q * 8 + 2 * e + 0] = inv * fmaf(-tj, w0, v[q * 8 + 2 * e + 0]);
+          r[q * 8 + 2 * e + 1] = inv * fmaf(-tj, w1, v[q * 8 + 2 * e + 1]);
+        }
+      }
+      if (p.use_tma) {
+        chunk_out_tma<false>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, r, col0, p.row_off + tc.m_blk * kBM);
+      } else if (valid) {
         float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t wr[4] = {wcur[q].x, wcur[q].y, wcur[q].z, wcur[q].w};
-          float r[8];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float w0 = __uint_as_float(wr[e] << 16);
-            const float w1 = __uint_as_float(wr[e] & 0xffff0000u);
-            r[2 * e + 0] = inv * fmaf(-tj, w0, v[q * 8 + 2 * e + 0]);
-            r[2 * e + 1] = inv * fmaf(-tj, w1, v[q * 8 + 2 * e + 1]);
-          }
-          const int cq = col0 + q * 8;
-          if (vec_ok && cq + 8 <= p.D) {
-            *reinterpret_cast<float4*>(o + q * 8) = make_float4(r[0], r[1], r[2], r[3]);
-            *reinterpret_cast<float4*>(o + q * 8 + 4) = make_float4(r[4], r[5], r[6], r[7]);
-          } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-              if (cq + e < p.D) o[q * 8 + e] = r[e];
-          }
-        }
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.D) o[j] = r[j];
       }
     }
   }

@@ -2,12 +2,14 @@
 //   bf16 operands staged in shared memory by TMA (SWIZZLE_128B), fp32 accumulators in TMEM,
 //   double-buffered so the epilogue of tile i overlaps the MMAs of tile i+1.
 //
-// Roles (256 threads, one CTA per SM):
+// Roles (384 threads, one CTA per SM):
 //   warp 0  lane 0 : TMA producer          (full/empty mbarrier ring of STAGES slots)
 //   warp 1  lane 0 : tcgen05.mma issuer    (one thread issues for the whole CTA)
 //   warp 2         : TMEM allocator / deallocator
-//   warps 4..7     : epilogue -- warp w owns TMEM lanes 32*(w%4) .. +31, i.e. one accumulator
-//                    row per thread, and walks the BN columns in chunks of 32.
+//   warps 4..11    : epilogue, two warpgroups -- warp w owns TMEM lanes 32*(w%4) .. +31, i.e. one
+//                    accumulator row per thread; warpgroup g = (w-4)/4 walks columns
+//                    [g*BN/2, (g+1)*BN/2) in chunks of 32, so every SM sub-partition has two
+//                    epilogue warps to hide tcgen05.ld / MUFU latency.
 //
 // Either operand may be K-major (K contiguous in global memory) or MN-major (the M / N index
 // contiguous); both are loaded as 128 B-wide swizzled boxes and described to the tensor core by
@@ -24,8 +26,8 @@ namespace arcb {
 
 constexpr int kBM = 128;  // accumulator rows per tile = TMEM lanes
 constexpr int kBK = 64;   // bf16 elements per 128 B swizzle line
-constexpr int kGemmThreads = 256;
-constexpr int kEpiThreads = 128;
+constexpr int kEpiThreads = 256;            // two epilogue warpgroups
+constexpr int kGemmThreads = 128 + kEpiThreads;
 
 struct GemmSched {
   int tiles_m;
@@ -183,7 +185,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // -------------------------------- epilogue ----------------------------------
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
     const int row_in_tile = quad * 32 + lane;
-    const int epi_tid = static_cast<int>(threadIdx.x) - (kGemmThreads - kEpiThreads);
+    const int epi_tid = static_cast<int>(threadIdx.x) - (kGemmThreads - kEpiThreads);  // 0..255, wg = epi_tid >> 7
     uint8_t* epi_smem = smem + L::kEpiOff;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -195,7 +197,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_wait(&tfull[acc], acc_phase, 0x400u + acc);
       tc_fence_after();
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * BN) + (static_cast<uint32_t>(quad * 32) << 16);
-      Epi::template consume<BN>(ep, st, tc, taddr, row_in_tile, epi_tid, epi_smem);
+      Epi::template consume<BN>(ep, st, tc, tmC, taddr, row_in_tile, epi_tid, epi_smem);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);  // TMEM stage may be overwritten

@@ -86,14 +86,13 @@ __global__ void __launch_bounds__(256) l2norm_rows_kernel(const float* __restric
 //   zt        : s * sub (natural units) or -inf when the label is not in this shard
 //   dphi      : d sub / d cos   (finite limit cos_m where the reference produces NaN)
 //   cos_t     : the fp32 cosine itself
-//   tile_flag : 1 for every 128-class tile that contains at least one label
 __global__ void __launch_bounds__(256)
 target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, int64_t ldw,
                    const int64_t* __restrict__ labels, const float* __restrict__ inv_nx,
                    const float* __restrict__ inv_nw, int B, int Bp, int D, int64_t Cs, int64_t class_offset, float s,
                    float cos_m, float sin_m, float th, float mm, int easy, int* __restrict__ lbl_local,
                    float* __restrict__ sub, float* __restrict__ zt, float* __restrict__ dphi,
-                   float* __restrict__ cos_t, unsigned char* __restrict__ tile_flag) {
+                   float* __restrict__ cos_t) {
   const int lane = threadIdx.x & 31;
   const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (i >= Bp) return;
@@ -137,7 +136,6 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
     zt[i] = s * v;
     dphi[i] = d;
     cos_t[i] = c;
-    tile_flag[loc >> 7] = 1;
   }
 }
 

@@ -17,7 +17,8 @@ _ROOT = os.path.dirname(_PKG_DIR)
 LIB_PATH = os.path.join(_PKG_DIR, "libarcface_b200.so")
 _SRC = os.path.join(_PKG_DIR, "csrc", "arcface_b200.cu")
 _HDRS = [
-    os.path.join(_PKG_DIR, "csrc", n) for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "epilogues.cuh", "rowwise.cuh")
+    os.path.join(_PKG_DIR, "csrc", n)
+    for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh")
 ] + [os.path.join(_ROOT, "include", "arcface_b200.h")]
 
 NVCC_FLAGS = [
@@ -30,12 +31,12 @@ EXPORTED = [
     "arcb_version", "arcb_last_error", "arcb_check_watchdog", "arcb_l2norm_rows", "arcb_l2norm_rows_bwd",
     "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
-    "arcb_profile_collect",
+    "arcb_profile_collect", "arcb_set_backward_mode",
 ]
 
 KERNEL_KINDS = [
     "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",
-    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test",
+    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test", "bwd_persistent",
 ]
 
 _lock = threading.Lock()
@@ -102,6 +103,8 @@ def _declare(lib):
     lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
     lib.arcb_shard_backward.restype = i32
     lib.arcb_shard_backward.argtypes = [i64, i64, i64, f32, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp]
+    lib.arcb_set_backward_mode.restype = i32
+    lib.arcb_set_backward_mode.argtypes = [i32]
     lib.arcb_launch_count.restype = i64
     lib.arcb_launch_count.argtypes = []
     lib.arcb_profile_enable.restype = i32

@@ -9,10 +9,12 @@
 #include <cuda_bf16.h>
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <atomic>
 #include <stdio.h>
 #include <string.h>
 
+#include "bwd_persistent.cuh"
 #include "epilogues.cuh"
 #include "gemm_sm100.cuh"
 #include "rowwise.cuh"
@@ -91,6 +93,7 @@ struct Workspace {
   float* zt2;            // [Bp]
   float* gscale;         // [1]
   float* tproj;          // [Cs]
+  unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
   int64_t total;
 };
 
@@ -123,6 +126,7 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
   w.zt2 = reinterpret_cast<float*>(take(w.Bp * 4));
   w.gscale = reinterpret_cast<float*>(take(4));
   w.tproj = reinterpret_cast<float*>(take(Cs * 4));
+  w.counters = reinterpret_cast<unsigned int*>(take(2 * ((Cs + 127) / 128) * 4));
   w.total = off;
   return w;
 }
@@ -188,6 +192,97 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   return ARCB_OK;
 }
 
+// ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
+template <bool EXT>
+int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
+                          int64_t chunk_rows, float* dw, float* dxhat, cudaStream_t st) {
+  const int64_t B = W.B, Cs = W.Cs, D = W.D;
+  BwdPlan pl;
+  pl.chunk_rows = static_cast<int>(chunk_rows);
+  pl.n_chunks = static_cast<int>((Cs + chunk_rows - 1) / chunk_rows);
+  pl.Cs = (int)Cs; pl.B = (int)B; pl.Bp = (int)W.Bp; pl.D = (int)D; pl.Dp = (int)W.Dp;
+  pl.g_tiles_n = (int)(W.Bp / kPBN);
+  pl.g_kb = (int)(W.Dp / kBK);
+  pl.x_tiles_m = (int)((B + kBM - 1) / kBM);
+  pl.x_tiles_n = (int)((D + kPBN - 1) / kPBN);
+  pl.w_tiles_n = pl.x_tiles_n;
+  pl.w_kb = (int)((B + kBK - 1) / kBK);
+  // dX tiles are cut along the chunk's classes so that one costs about as much as a dW tile and a
+  // chunk yields at least ~one tile per SM
+  {
+    const int kbt = (int)((chunk_rows + kBK - 1) / kBK);
+    const int tiles_mn = pl.x_tiles_m * pl.x_tiles_n;
+    int want_splits = (device_sm_count() + tiles_mn - 1) / tiles_mn;
+    int per = (kbt + want_splits - 1) / want_splits;
+    if (per < 4) per = 4;
+    if (per > pl.w_kb && pl.w_kb >= 4) per = pl.w_kb;
+    pl.x_kb_per_split = per;
+  }
+  pl.g_done = W.counters;
+  pl.xw_done = W.counters + pl.n_chunks;
+  ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * 2 * pl.n_chunks, st));
+
+  CUtensorMap tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw;
+  const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  bool ok = true;
+  ok = ok && make_tmap_2d(&tmWhatK, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, kBK, kBM);
+  ok = ok && make_tmap_2d(&tmXhatK, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, kBK, kPBN);
+  ok = ok && make_tmap_2d(&tmGtSt, gt, bf, 2, W.Bp, 2 * chunk_rows, W.Bp * 2, 64, kBM);
+  ok = ok && make_tmap_2d(&tmGtMN, gt, bf, 2, W.Bp, 2 * chunk_rows, W.Bp * 2, 64, kBK);
+  ok = ok && make_tmap_2d(&tmWhatMN, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, 64, kBK);
+  ok = ok && make_tmap_2d(&tmGtK, gt, bf, 2, W.Bp, 2 * chunk_rows, W.Bp * 2, kBK, kBM);
+  ok = ok && make_tmap_2d(&tmXhatMN, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, 64, kBK);
+  ok = ok && make_tmap_2d(&tmDx, dxhat, f32, 4, D, B, W.Dp * 4, 32, kBM);
+  if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the persistent backward could not be encoded");
+  const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
+                      make_tmap_2d(&tmDw, dw, f32, 4, D, Cs, D * 4, 32, kBM);
+  if (!dw_tma) tmDw = tmDx;
+
+  BwdArgs ar;
+  ar.lse2 = W.lse2; ar.gscale = W.gscale; ar.lbl_local = W.lbl_local; ar.zt2 = W.zt2; ar.dphi = W.dphi;
+  ar.cos_t = W.cos_t; ar.tproj = W.tproj; ar.s2 = s * kLog2e; ar.grad_out = grad_logits; ar.ldgo = ldgl;
+  ar.s_ext = s; ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.dw_tma = dw_tma ? 1 : 0;
+
+  auto kern = bwd_persistent_kernel<EXT>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!attr_set[dev]) {
+    ARCB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPSmemTotal));
+    attr_set[dev] = true;
+  }
+  long long total_items = 0;
+  for (int k = 0; k < pl.n_chunks; ++k) total_items += plan_nG(pl, k) + plan_nX(pl, k) + plan_nW(pl, k);
+  int grid = device_sm_count();
+  if (grid > total_items) grid = static_cast<int>(total_items);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = kPSmemTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: they wait on one another
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  LaunchScope ls(ARCB_K_BWD_PERSISTENT, st);
+  ARCB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw, pl,
+                               ar));
+  return ARCB_OK;
+}
+
+std::atomic<int> g_bwd_mode{-1};  // -1: from the environment (default persistent), 0: per-chunk launches, 1: persistent
+bool use_persistent_backward() {
+  int mode = g_bwd_mode.load(std::memory_order_relaxed);
+  if (mode < 0) {
+    const char* e = getenv("ARCB_BWD_PERSISTENT");
+    mode = (e && e[0] == '0') ? 0 : 1;
+    g_bwd_mode.store(mode, std::memory_order_relaxed);
+  }
+  return mode == 1;
+}
+
 }  // namespace
 
 extern "C" {
@@ -209,6 +304,11 @@ int arcb_check_watchdog(void* stream) {
 }
 
 int64_t arcb_padded_dim(int64_t D) { return round_up(D, 64); }
+
+int arcb_set_backward_mode(int persistent) {
+  g_bwd_mode.store(persistent ? 1 : 0, std::memory_order_relaxed);
+  return ARCB_OK;
+}
 
 int64_t arcb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -375,6 +475,16 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   }
   ARCB_CUDA(cudaMemsetAsync(W.tproj, 0, Cs * 4, st));
   ARCB_CUDA(cudaMemsetAsync(dxhat, 0, B * W.Dp * 4, st));
+
+  if (use_persistent_backward()) {
+    // double-buffered scratch: two buffers of `pchunk` classes each
+    int64_t pchunk = scratch_bytes / (W.Bp * 2) / 2 / 128 * 128;
+    if (pchunk >= 128) {
+      if (pchunk > round_up(Cs, 128)) pchunk = round_up(Cs, 128);
+      return ext ? launch_bwd_persistent<true>(W, s, grad_logits, ldgl, gt, pchunk, dw, dxhat, st)
+                 : launch_bwd_persistent<false>(W, s, grad_logits, ldgl, gt, pchunk, dw, dxhat, st);
+    }
+  }
 
   const int sms = device_sm_count();
   // fp32 outputs leave the GEMM epilogues as bulk tensor stores / reduce-adds of [128 x 32] boxes

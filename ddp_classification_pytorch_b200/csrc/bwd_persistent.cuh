@@ -1,0 +1,478 @@
+// Persistent backward kernel of the ArcFace head (autograd behind ARCFACE/arc_main.py:329).
+//
+// One cooperative launch replaces the per-chunk sequence of three GEMM launches.  The classes of
+// the shard are cut into chunks; every chunk k contributes three kinds of 128 x 256 output tiles:
+//
+//   G(k)  recompute cos^T = w_hat[chunk] * x_hat^T, epilogue -> bf16 dLoss/dcos tile G^T into an
+//         L2-resident double-buffered scratch (buffer k & 1) + per-class projections t_j
+//   X(k)  dX_hat[B, D] += G[B, chunk] * w_hat[chunk, D]     (split along the chunk's classes,
+//         fp32 bulk reduce-add)
+//   W(k)  dW[chunk, D] = inv_norm * (G^T[chunk, B] * x_hat[B, D] - t * w_hat)
+//
+// All CTAs walk ONE global tile list  G0, G1, XW0, G2, XW1, ..., G(n-1), XW(n-2), XW(n-1)
+// round-robin; the look-ahead of one G phase means a CTA that reaches XW(k) almost never has to
+// wait.  Dependencies are two arrays of global counters:
+//   g_done[k]   G tiles of chunk k whose stores have completed  -> gates the loads of X(k)/W(k)
+//   xw_done[k]  X/W tiles of chunk k that finished reading G^T  -> gates the stores of G(k+2)
+// Every wait targets a tile that is EARLIER in the list and all CTAs are co-resident (cooperative
+// launch), so the schedule cannot deadlock.
+//
+// Warp roles: 0 = TMA producer, 1 = tcgen05.mma issuer, 2 = TMEM allocator, 3 = G^T store issuer
+// (TMA store + completion + release of g_done, off the epilogue's critical path), 4..11 = epilogue.
+#pragma once
+
+#include "epilogues.cuh"
+
+namespace arcb {
+
+constexpr int kPBN = 256;
+constexpr int kPStages = 3;
+constexpr int kPABytes = kBM * kBK * 2;
+constexpr int kPStageBytes = kPABytes + kPBN * kBK * 2;  // 48 KB
+constexpr int kPEpiSmem =
+    (EpiBwdG<false>::kSmemBytes > kChunkOutSmem ? EpiBwdG<false>::kSmemBytes : kChunkOutSmem);  // union
+constexpr int kPNumBars = 2 * kPStages + 4 + 2;
+constexpr int kPBarOff = kPStages * kPStageBytes + kPEpiSmem;
+constexpr int kPSmemTotal = kPBarOff + kPNumBars * 8 + 16 + 1024;
+static_assert(kPSmemTotal <= 232448, "persistent backward kernel exceeds the shared memory budget");
+
+enum : int { kItemG = 0, kItemX = 1, kItemW = 2 };
+
+struct BwdPlan {
+  int n_chunks, chunk_rows;  // chunk_rows % 128 == 0
+  int Cs, B, Bp, D, Dp;
+  int g_tiles_n;             // Bp / 256
+  int g_kb;                  // Dp / 64
+  int x_tiles_m, x_tiles_n;  // ceil(B / 128), ceil(D / 256)
+  int x_kb_per_split;        // 64-class blocks per X tile
+  int w_tiles_n, w_kb;       // ceil(D / 256), ceil(B / 64)
+  unsigned int* g_done;      // [n_chunks], zeroed before the launch
+  unsigned int* xw_done;     // [n_chunks], zeroed before the launch
+};
+
+struct BwdArgs {
+  const float* lse2;
+  const float* gscale;
+  const int* lbl_local;
+  const float* zt2;
+  const float* dphi;
+  const float* cos_t;
+  float* tproj;
+  float s2;
+  const float* grad_out;  // EXT only
+  int64_t ldgo;
+  float s_ext;
+  float* dw;
+  const __nv_bfloat16* what;
+  const float* inv_nw;
+  int dw_tma;
+};
+
+struct Item {
+  int kind, chunk, m_blk, n_blk, kb0, kb1;
+};
+
+__host__ __device__ inline int plan_rows(const BwdPlan& pl, int k) {
+  const int rest = pl.Cs - k * pl.chunk_rows;
+  return rest < pl.chunk_rows ? rest : pl.chunk_rows;
+}
+__host__ __device__ inline int plan_gm(const BwdPlan& pl, int k) { return (plan_rows(pl, k) + kBM - 1) / kBM; }
+__host__ __device__ inline int plan_nG(const BwdPlan& pl, int k) { return plan_gm(pl, k) * pl.g_tiles_n; }
+__host__ __device__ inline int plan_xsplits(const BwdPlan& pl, int k) {
+  const int kbt = (plan_rows(pl, k) + kBK - 1) / kBK;
+  return (kbt + pl.x_kb_per_split - 1) / pl.x_kb_per_split;
+}
+__host__ __device__ inline int plan_nX(const BwdPlan& pl, int k) {
+  return pl.x_tiles_m * pl.x_tiles_n * plan_xsplits(pl, k);
+}
+__host__ __device__ inline int plan_nW(const BwdPlan& pl, int k) { return plan_gm(pl, k) * pl.w_tiles_n; }
+
+// phase p of the global list -> (is it a G phase, which chunk)
+__device__ __forceinline__ void phase_kind(const BwdPlan& pl, int p, bool& is_g, int& k) {
+  if (p == 0) {
+    is_g = true;
+    k = 0;
+  } else if (p & 1) {
+    k = (p + 1) >> 1;
+    is_g = k < pl.n_chunks;
+    if (!is_g) k = pl.n_chunks - 1;
+  } else {
+    is_g = false;
+    k = (p >> 1) - 1;
+  }
+}
+__device__ __forceinline__ int phase_items(const BwdPlan& pl, int p) {
+  bool is_g;
+  int k;
+  phase_kind(pl, p, is_g, k);
+  return is_g ? plan_nG(pl, k) : plan_nX(pl, k) + plan_nW(pl, k);
+}
+
+// Every role of a CTA walks the same sub-sequence of the global list: tiles blockIdx.x, +gridDim.x, ...
+struct ItemWalker {
+  int phase, phase_begin, phase_size, next_it;
+  __device__ void init(const BwdPlan& pl) {
+    phase = 0;
+    phase_begin = 0;
+    phase_size = phase_items(pl, 0);
+    next_it = blockIdx.x;
+  }
+  __device__ bool next(const BwdPlan& pl, Item& it) {
+    const int nph = 2 * pl.n_chunks;
+    while (phase < nph && next_it >= phase_begin + phase_size) {
+      phase_begin += phase_size;
+      ++phase;
+      if (phase < nph) phase_size = phase_items(pl, phase);
+    }
+    if (phase >= nph) return false;
+    bool is_g;
+    int k;
+    phase_kind(pl, phase, is_g, k);
+    int j = next_it - phase_begin;
+    it.chunk = k;
+    const int gm = plan_gm(pl, k);
+    if (is_g) {
+      it.kind = kItemG;
+      it.m_blk = j % gm;
+      it.n_blk = j / gm;
+      it.kb0 = 0;
+      it.kb1 = pl.g_kb;
+    } else {
+      const int nx = plan_nX(pl, k);
+      if (j < nx) {
+        it.kind = kItemX;
+        it.m_blk = j % pl.x_tiles_m;
+        const int r = j / pl.x_tiles_m;
+        it.n_blk = r % pl.x_tiles_n;
+        const int ks = r / pl.x_tiles_n;
+        const int kbt = (plan_rows(pl, k) + kBK - 1) / kBK;
+        it.kb0 = ks * pl.x_kb_per_split;
+        it.kb1 = min(it.kb0 + pl.x_kb_per_split, kbt);
+      } else {
+        j -= nx;
+        it.kind = kItemW;
+        it.m_blk = j % gm;
+        it.n_blk = j / gm;
+        it.kb0 = 0;
+        it.kb1 = pl.w_kb;
+      }
+    }
+    next_it += gridDim.x;
+    return true;
+  }
+};
+
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Spin until *ctr >= target (acquire, gpu scope).  Same watchdog as mbar_wait.
+__device__ __forceinline__ void wait_counter(const unsigned int* ctr, unsigned int target, uint32_t tag) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+  if (v >= target) return;
+  const long long t0 = clock64();
+  uint32_t spins = 0;
+  while (true) {
+    __nanosleep(100);
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    if (v >= target) return;
+    if ((++spins & 0xffu) == 0) {
+      if (*reinterpret_cast<volatile unsigned int*>(&g_wait_timeout[0]) != 0) return;
+      if (clock64() - t0 > 4000000000ll) {
+        if (atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) {
+          g_wait_timeout[1] = tag;
+          g_wait_timeout[2] = blockIdx.x;
+          g_wait_timeout[3] = target;
+        }
+        return;
+      }
+    }
+  }
+}
+
+template <bool EXT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [Cs, Dp]   box 64 x 128  (A of G)
+                      const __grid_constant__ CUtensorMap tmXhatK,   // x_hat [B, Dp]    box 64 x 256  (B of G)
+                      const __grid_constant__ CUtensorMap tmGtSt,    // G^T   [2R, Bp]   box 64 x 128  (store of G)
+                      const __grid_constant__ CUtensorMap tmGtMN,    // G^T   [2R, Bp]   box 64 x 64   (A of X)
+                      const __grid_constant__ CUtensorMap tmWhatMN,  // w_hat [Cs, Dp]   box 64 x 64   (B of X)
+                      const __grid_constant__ CUtensorMap tmGtK,     // G^T   [2R, Bp]   box 64 x 128  (A of W)
+                      const __grid_constant__ CUtensorMap tmXhatMN,  // x_hat [B, Dp]    box 64 x 64   (B of W)
+                      const __grid_constant__ CUtensorMap tmDx,      // dxhat [B, D] f32 box 32 x 128
+                      const __grid_constant__ CUtensorMap tmDw,      // dW    [Cs, D] f32 box 32 x 128
+                      const BwdPlan pl, const BwdArgs ar) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + kPStages * kPStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kPBarOff);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kPStages;
+  uint64_t* tfull = bars + 2 * kPStages;
+  uint64_t* tempty = bars + 2 * kPStages + 2;
+  uint64_t* stage_full = bars + 2 * kPStages + 4;  // epilogue -> store issuer: G^T tile is in smem
+  uint64_t* stage_free = bars + 2 * kPStages + 5;  // store issuer -> epilogue: tile has been read
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kPNumBars);
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = static_cast<int>(lane_id());
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmWhatK);
+    tma_prefetch_desc(&tmXhatK);
+    tma_prefetch_desc(&tmGtSt);
+    tma_prefetch_desc(&tmGtMN);
+    tma_prefetch_desc(&tmWhatMN);
+    tma_prefetch_desc(&tmGtK);
+    tma_prefetch_desc(&tmXhatMN);
+    tma_prefetch_desc(&tmDx);
+    tma_prefetch_desc(&tmDw);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kPStages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], kEpiThreads / 32);
+    }
+    mbar_init(stage_full, kEpiThreads / 32);
+    mbar_init(stage_free, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 2 * kPBN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------ TMA producer ------------------------------
+      ItemWalker w;
+      w.init(pl);
+      Item it;
+      int stage = 0;
+      uint32_t phase = 0;
+      while (w.next(pl, it)) {
+        if (it.kb0 >= it.kb1) continue;
+        if (it.kind != kItemG) {  // G^T of this chunk must be complete and visible
+          wait_counter(pl.g_done + it.chunk, static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
+          fence_proxy_async_all();
+        }
+        const int c0 = it.chunk * pl.chunk_rows;                // first class of the chunk in the shard
+        const int buf_row = (it.chunk & 1) * pl.chunk_rows;     // first row of the chunk's scratch buffer
+        for (int kb = it.kb0; kb < it.kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
+          mbar_arrive_expect_tx(&full[stage], kPStageBytes);
+          uint8_t* sa = smem + stage * kPStageBytes;
+          uint8_t* sb = sa + kPABytes;
+          if (it.kind == kItemG) {
+            tma_load_2d(sa, &tmWhatK, &full[stage], kb * kBK, c0 + it.m_blk * kBM);
+            tma_load_2d(sb, &tmXhatK, &full[stage], kb * kBK, it.n_blk * kPBN);
+          } else if (it.kind == kItemX) {
+#pragma unroll
+            for (int j = 0; j < kBM / 64; ++j)
+              tma_load_2d(sa + j * (kBK * 128), &tmGtMN, &full[stage], it.m_blk * kBM + j * 64, buf_row + kb * kBK);
+#pragma unroll
+            for (int j = 0; j < kPBN / 64; ++j)
+              tma_load_2d(sb + j * (kBK * 128), &tmWhatMN, &full[stage], it.n_blk * kPBN + j * 64, c0 + kb * kBK);
+          } else {
+            tma_load_2d(sa, &tmGtK, &full[stage], kb * kBK, buf_row + it.m_blk * kBM);
+#pragma unroll
+            for (int j = 0; j < kPBN / 64; ++j)
+              tma_load_2d(sb + j * (kBK * 128), &tmXhatMN, &full[stage], it.n_blk * kPBN + j * 64, kb * kBK);
+          }
+          if (++stage == kPStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ------------------------------ MMA issuer --------------------------------
+      ItemWalker w;
+      w.init(pl);
+      Item it;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      while (w.next(pl, it)) {
+        if (it.kb0 >= it.kb1) continue;
+        const bool a_mn = it.kind == kItemX;
+        const bool b_mn = it.kind != kItemG;
+        const uint32_t idesc = make_idesc_bf16(kBM, kPBN, a_mn, b_mn);
+        mbar_wait(&tempty[acc], acc_phase ^ 1u, 0x200u + acc);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kPBN);
+        for (int kb = it.kb0; kb < it.kb1; ++kb) {
+          mbar_wait(&full[stage], phase, 0x300u + stage);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smem + stage * kPStageBytes);
+          const uint32_t b_base = a_base + kPABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = a_mn ? make_smem_desc(a_base + k * 2048, kBK * 128, 1024)
+                                     : make_smem_desc(a_base + k * 32, 16, 1024);
+            const uint64_t db = b_mn ? make_smem_desc(b_base + k * 2048, kBK * 128, 1024)
+                                     : make_smem_desc(b_base + k * 32, 16, 1024);
+            tc_mma_bf16(tmem_d, da, db, idesc, (kb > it.kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(&empty[stage]);
+          if (++stage == kPStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        tc_commit(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0) {
+      // --------------------------- G^T store issuer -----------------------------
+      ItemWalker w;
+      w.init(pl);
+      Item it;
+      uint32_t g_n = 0;
+      while (w.next(pl, it)) {
+        if (it.kind != kItemG || it.kb0 >= it.kb1) continue;
+        mbar_wait(stage_full, g_n & 1u, 0x600u);
+        if (it.chunk >= 2) {  // the X / W tiles that read this scratch buffer two chunks ago must be done
+          const int kp = it.chunk - 2;
+          wait_counter(pl.xw_done + kp, static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
+          fence_proxy_async_all();
+        }
+        const int buf_row = (it.chunk & 1) * pl.chunk_rows;
+#pragma unroll
+        for (int bx = 0; bx < kPBN / 64; ++bx)
+          tma_store_2d(&tmGtSt, epi_smem + bx * (kBM * 128), it.n_blk * kPBN + bx * 64, buf_row + it.m_blk * kBM);
+        tma_store_commit();
+        tma_store_wait_read0();
+        mbar_arrive(stage_free);  // the epilogue may overwrite the staging tile
+        tma_store_wait_all0();    // writes (and, through the barrier chain, the t_j atomics) are done
+        __threadfence();
+        atomicAdd(pl.g_done + it.chunk, 1u);
+        ++g_n;
+      }
+    }
+  } else if (warp >= 4) {
+    // -------------------------------- epilogue ----------------------------------
+    const int quad = warp & 3;
+    const int row_in_tile = quad * 32 + lane;
+    const int epi_tid = static_cast<int>(threadIdx.x) - (kGemmThreads - kEpiThreads);
+    ItemWalker w;
+    w.init(pl);
+    Item it;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t g_count = 0;
+    int prev_kind = -1;
+    EpiOutState ost;
+    ost.it = 0;
+    const float gscale = EXT ? 0.f : __ldg(ar.gscale);
+    while (w.next(pl, it)) {
+      if (it.kb0 >= it.kb1) continue;
+      // per-tile row data is fetched before waiting for the accumulator, so its latency is hidden
+      float lse_v = 0.f;
+      int lbl_v = -1;
+      if (it.kind == kItemG) {
+        if (!EXT) lse_v = __ldg(ar.lse2 + it.n_blk * kPBN + epi_tid);
+        lbl_v = __ldg(ar.lbl_local + it.n_blk * kPBN + epi_tid);
+      }
+      mbar_wait(&tfull[acc], acc_phase, 0x400u + acc);
+      tc_fence_after();
+      if (it.kind != kItemG && epi_tid == 0) {  // this tile has finished reading its G^T chunk
+        fence_proxy_async_all();
+        __threadfence();
+        atomicAdd(pl.xw_done + it.chunk, 1u);
+      }
+      // the G^T staging tile and the X / W chunk buffers share the same shared memory
+      if (prev_kind != -1 && (it.kind == kItemG) != (prev_kind == kItemG)) {
+        if (prev_kind == kItemG) mbar_wait(stage_free, (g_count & 1u) ^ 1u, 0x800u);
+        else if ((epi_tid & 127) == 0) tma_store_wait_read<0>();
+        named_bar_sync(1, kEpiThreads);
+      }
+      const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * kPBN) + (static_cast<uint32_t>(quad * 32) << 16);
+      TileCoord tc;
+      tc.m_blk = it.m_blk;
+      tc.n_blk = it.n_blk;
+      tc.kb0 = it.kb0;
+      tc.kb1 = it.kb1;
+      const int c0 = it.chunk * pl.chunk_rows;
+      const int rows = plan_rows(pl, it.chunk);
+      if (it.kind == kItemG) {
+        mbar_wait(stage_free, (g_count & 1u) ^ 1u, 0x900u);  // previous G tile has left the staging tile
+        EpiBwdG<EXT>::stage_rows(epi_smem, epi_tid, lse_v, lbl_v);
+        named_bar_sync(1, kEpiThreads);
+        typename EpiBwdG<EXT>::Params p;
+        p.lse2 = ar.lse2;
+        p.gscale = ar.gscale;
+        p.lbl_local = ar.lbl_local;
+        p.zt2 = ar.zt2;
+        p.dphi = ar.dphi;
+        p.cos_t = ar.cos_t;
+        p.t_out = ar.tproj;
+        p.row_off = c0;
+        p.rows_valid = rows;
+        p.B = pl.B;
+        p.Bp = pl.Bp;
+        p.s2 = ar.s2;
+        p.grad_out = EXT ? ar.grad_out + c0 : nullptr;
+        p.ldgo = ar.ldgo;
+        p.s_ext = ar.s_ext;
+        EpiBwdG<EXT>::template body<kPBN>(p, gscale, tc, taddr, row_in_tile, epi_tid, epi_smem);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[acc]);
+        fence_proxy_async_smem();  // staging tile -> visible to the TMA engine
+        __syncwarp();
+        if (lane == 0) mbar_arrive(stage_full);
+        ++g_count;
+      } else if (it.kind == kItemX) {
+        EpiRedAdd::Params p;
+        p.M = pl.B;
+        p.N = pl.D;
+        EpiRedAdd::template consume<kPBN>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[acc]);
+      } else {
+        EpiDW::Params p;
+        p.dw = ar.dw;
+        p.what = ar.what;
+        p.t = ar.tproj;
+        p.inv_norm = ar.inv_nw;
+        p.row_off = c0;
+        p.rows_valid = rows;
+        p.D = pl.D;
+        p.Dp = pl.Dp;
+        p.use_tma = ar.dw_tma;
+        EpiDW::template consume<kPBN>(p, ost, tc, tmDw, taddr, row_in_tile, epi_tid, epi_smem);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[acc]);
+      }
+      prev_kind = it.kind;
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
+    }
+    if ((epi_tid & 127) == 0) tma_store_wait_all0();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * kPBN);
+  }
+}
+
+}  // namespace arcb

@@ -261,19 +261,33 @@ struct EpiBwdG {
   __device__ static void drain(int epi_tid) {
     if (epi_tid == 0) tma_store_wait_all0();
   }
+  // Stage the log-sum-exps and labels of the tile's 256 samples (one element per epilogue thread).
+  __device__ static void stage_rows(uint8_t* smem, int epi_tid, float lse_v, int lbl_v) {
+    float* lse_s = reinterpret_cast<float*>(smem + kStageBytes);
+    int* lbl_s = reinterpret_cast<int*>(smem + kStageBytes + 256 * 4);
+    if constexpr (!EXT) lse_s[epi_tid] = lse_v;
+    lbl_s[epi_tid] = lbl_v;
+  }
   template <int BN>
   __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap&, uint32_t taddr,
                                  int row_in_tile, int epi_tid, uint8_t* smem) {
     static_assert(BN == 256, "staging tile is sized for BN = 256");
-    const int wg = epi_tid >> 7;
-    const int lane = epi_tid & 31;
     // the previous tile's TMA stores must have finished reading the staging tile
     if (epi_tid == 0) tma_store_wait_read0();
-    float* lse_s = reinterpret_cast<float*>(smem + kStageBytes);
-    int* lbl_s = reinterpret_cast<int*>(smem + kStageBytes + 256 * 4);
-    if constexpr (!EXT) lse_s[epi_tid] = __ldg(p.lse2 + tc.n_blk * BN + epi_tid);
-    lbl_s[epi_tid] = __ldg(p.lbl_local + tc.n_blk * BN + epi_tid);
+    const float lse_v = EXT ? 0.f : __ldg(p.lse2 + tc.n_blk * BN + epi_tid);
+    const int lbl_v = __ldg(p.lbl_local + tc.n_blk * BN + epi_tid);
+    stage_rows(smem, epi_tid, lse_v, lbl_v);
     named_bar_sync(1, kEpiThreads);
+    body<BN>(p, st.gscale, tc, taddr, row_in_tile, epi_tid, smem);
+  }
+  // The tile proper: needs the staging tile free and stage_rows() visible to all epilogue threads.
+  template <int BN>
+  __device__ static void body(const Params& p, float gscale, const TileCoord& tc, uint32_t taddr, int row_in_tile,
+                              int epi_tid, uint8_t* smem) {
+    const int wg = epi_tid >> 7;
+    const int lane = epi_tid & 31;
+    const float* lse_s = reinterpret_cast<const float*>(smem + kStageBytes);
+    const int* lbl_s = reinterpret_cast<const int*>(smem + kStageBytes + 256 * 4);
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const int cls = p.row_off + row_local;
     const int tile_cls0 = p.row_off + tc.m_blk * kBM;
@@ -290,10 +304,10 @@ struct EpiBwdG {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const float4 l4 = *reinterpret_cast<const float4*>(lse_s + c + j);
-          g[j + 0] = ex2_approx(fmaf(v[j + 0], p.s2, -l4.x)) * st.gscale;
-          g[j + 1] = ex2_approx(fmaf(v[j + 1], p.s2, -l4.y)) * st.gscale;
-          g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * st.gscale;
-          g[j + 3] = ex2_approx(fmaf(v[j + 3], p.s2, -l4.w)) * st.gscale;
+          g[j + 0] = ex2_approx(fmaf(v[j + 0], p.s2, -l4.x)) * gscale;
+          g[j + 1] = ex2_approx(fmaf(v[j + 1], p.s2, -l4.y)) * gscale;
+          g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * gscale;
+          g[j + 3] = ex2_approx(fmaf(v[j + 3], p.s2, -l4.w)) * gscale;
         }
       } else {
 #pragma unroll
@@ -317,7 +331,7 @@ struct EpiBwdG {
           const float dp = __ldg(p.dphi + i);
           float gt;
           if constexpr (!EXT) {
-            gt = st.gscale * (ex2_approx(__ldg(p.zt2 + i) - lse_s[c + j]) - 1.f) * dp;
+            gt = gscale * (ex2_approx(__ldg(p.zt2 + i) - lse_s[c + j]) - 1.f) * dp;
           } else {
             gt = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext * dp;
           }
@@ -422,7 +436,7 @@ struct EpiDW {
     float tj = 0.f, inv = 0.f;
     if (valid) {
       inv = __ldg(p.inv_norm + cls);
-      tj = (inv < 0.5e12f) ? __ldg(p.t + cls) : 0.f;  // clamped rows take no projection
+      tj = (inv < 0.5e12f) ? __ldcg(p.t + cls) : 0.f;  // clamped rows take no projection (t is written in-kernel: coherent load)
     }
     const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
     const int c_begin = wg * (BN / 2), c_end = (wg + 1) * (BN / 2);

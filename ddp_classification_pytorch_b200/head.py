@@ -26,9 +26,10 @@ from torch.nn import Parameter
 
 from . import _lib
 
-# classes per backward chunk: 128 * 148 keeps every wave of the three chunk GEMMs full on 148 SMs
-# and the bf16 dLoss/dcos chunk (B=1024: 38.8 MB) inside the 126 MB L2.
-DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 128 * 148))
+# classes per backward chunk: the persistent backward keeps TWO chunks of bf16 dLoss/dcos in flight
+# (B=1024: 2 x 19.4 MB), which together with the matching w_hat rows stays inside the 126 MB L2;
+# 128 * 74 rows give 296 / 148 / 144 tiles per chunk for the three GEMMs on 148 SMs.
+DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 128 * 74))
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -80,7 +81,7 @@ def _alloc_ws(B, Cs, D, device):
 def _scratch_for(B, Cs, device, chunk_classes):
     L = _lib.lib()
     chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
-    nbytes = L.arcb_scratch_bytes(B, chunk)
+    nbytes = L.arcb_scratch_bytes(B, 2 * chunk)  # two buffers (double-buffered persistent backward)
     return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
 

@@ -64,7 +64,9 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
 int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D);
 
 /* Bytes of backward scratch that hold `chunk_classes` classes of bf16 dLoss/dcos for batch B.
- * arcb_shard_backward accepts any scratch >= arcb_scratch_bytes(B, 128). */
+ * arcb_shard_backward accepts any scratch >= arcb_scratch_bytes(B, 128); its default persistent
+ * kernel splits the scratch into two buffers (needs >= arcb_scratch_bytes(B, 256), otherwise it
+ * falls back to one kernel launch per GEMM and chunk). */
 int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes);
 
 /* ---- fused forward on one class shard: arc_main.py:159-172 + the softmax statistics of :245 ----
@@ -99,6 +101,10 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
                         const float* target_logit, const float* grad_loss, const float* grad_logits, int64_t ldgl,
                         void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, void* stream);
 
+/* Backward schedule: 1 (default) = one persistent cooperative kernel per shard, 0 = one launch
+ * per GEMM and class chunk.  Both produce the same gradients (A/B testing, profiling). */
+int arcb_set_backward_mode(int persistent);
+
 /* Leading dimension (elements) of the dxhat buffer for feature size D. */
 int64_t arcb_padded_dim(int64_t D);
 
@@ -122,7 +128,8 @@ enum {
   ARCB_K_L2NORM_BWD = 10, /* F.normalize backward for the embeddings */
   ARCB_K_LOGITS_GEMM = 11,/* materialising forward                   */
   ARCB_K_GEMM_TEST = 12,  /* arcb_gemm_bf16                          */
-  ARCB_K_COUNT = 13
+  ARCB_K_BWD_PERSISTENT = 13, /* whole backward of a shard, one launch */
+  ARCB_K_COUNT = 14
 };
 int64_t arcb_launch_count(void);
 int arcb_profile_enable(int on);

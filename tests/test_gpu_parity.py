@@ -128,3 +128,31 @@ def test_contract_errors():
         head(torch.randn(4, 16), torch.zeros(4))
     assert list(head.state_dict().keys()) == ["weight"]
     assert head.weight.dtype == torch.float32 and tuple(head.weight.shape) == (8, 16)
+
+
+@pytest.mark.parametrize("chunk", [128, 384, 4096])
+def test_persistent_and_per_chunk_backward_agree(chunk):
+    """The persistent cooperative backward and the per-chunk launch sequence are two schedules of the
+    same arithmetic: gradients must agree to fp32-atomic-order noise, for 1, few and many chunks."""
+    B, D, C = 300, 192, 3000
+    gen = torch.Generator().manual_seed(7)
+    w = (torch.rand(C, D, generator=gen) * 2 - 1) * 0.05
+    x = torch.randn(B, D, generator=gen)
+    y = torch.randint(0, C, (B,), generator=gen)
+    L = _lib.lib()
+    grads = []
+    try:
+        for mode in (1, 0):
+            L.arcb_set_backward_mode(mode)
+            head = _module(w.numpy(), 30.0, 0.5, False, chunk_classes=chunk)
+            xg = x.cuda().requires_grad_(True)
+            head.forward_loss(xg, y.cuda()).backward()
+            _sync_ok()
+            grads.append((xg.grad.clone(), head.weight.grad.clone()))
+    finally:
+        L.arcb_set_backward_mode(1)
+    torch.testing.assert_close(grads[0][0], grads[1][0], rtol=1e-3, atol=1e-6)
+    torch.testing.assert_close(grads[0][1], grads[1][1], rtol=1e-3, atol=1e-6)
+    ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, False)
+    assert cosine_similarity(grads[0][0].cpu().numpy(), ref["dx"]) >= GRAD_COS
+    assert cosine_similarity(grads[0][1].cpu().numpy(), ref["dw"]) >= GRAD_COS

@@ -195,10 +195,11 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
 template <bool EXT>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
-                          int64_t chunk_rows, float* dw, float* dxhat, cudaStream_t st) {
+                          int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st) {
   const int64_t B = W.B, Cs = W.Cs, D = W.D;
   BwdPlan pl;
   pl.chunk_rows = static_cast<int>(chunk_rows);
+  pl.nbuf = nbuf;
   pl.n_chunks = static_cast<int>((Cs + chunk_rows - 1) / chunk_rows);
   pl.Cs = (int)Cs; pl.B = (int)B; pl.Bp = (int)W.Bp; pl.D = (int)D; pl.Dp = (int)W.Dp;
   pl.g_tiles_n = (int)(W.Bp / kPBN);
@@ -219,6 +220,15 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     pl.x_kb_per_split = per;
   }
   pl.g_done = W.counters;
+  {
+    static int mask = -1;
+    if (mask < 0) {
+      const char* e = getenv("ARCB_DEBUG_KINDS");
+      mask = e ? atoi(e) & 7 : 7;
+      if (mask == 0) mask = 7;
+    }
+    pl.kind_mask = mask;
+  }
   pl.xw_done = W.counters + pl.n_chunks;
   ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * 2 * pl.n_chunks, st));
 
@@ -227,10 +237,10 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   bool ok = true;
   ok = ok && make_tmap_2d(&tmWhatK, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, kBK, kBM);
   ok = ok && make_tmap_2d(&tmXhatK, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, kBK, kPBN);
-  ok = ok && make_tmap_2d(&tmGtSt, gt, bf, 2, W.Bp, 2 * chunk_rows, W.Bp * 2, 64, kBM);
-  ok = ok && make_tmap_2d(&tmGtMN, gt, bf, 2, W.Bp, 2 * chunk_rows, W.Bp * 2, 64, kBK);
+  ok = ok && make_tmap_2d(&tmGtSt, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, 64, kBM);
+  ok = ok && make_tmap_2d(&tmGtMN, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, 64, kBK);
   ok = ok && make_tmap_2d(&tmWhatMN, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, 64, kBK);
-  ok = ok && make_tmap_2d(&tmGtK, gt, bf, 2, W.Bp, 2 * chunk_rows, W.Bp * 2, kBK, kBM);
+  ok = ok && make_tmap_2d(&tmGtK, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, kBK, kBM);
   ok = ok && make_tmap_2d(&tmXhatMN, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, 64, kBK);
   ok = ok && make_tmap_2d(&tmDx, dxhat, f32, 4, D, B, W.Dp * 4, 32, kBM);
   if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the persistent backward could not be encoded");
@@ -406,7 +416,13 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
   cudaError_t e;
   {
     LaunchScope ls(ARCB_K_FWD_GEMM, st);
-    e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    static int fwd_stages = 0;
+    if (!fwd_stages) {
+      const char* e3 = getenv("ARCB_FWD_STAGES");
+      fwd_stages = (e3 && e3[0] == '3') ? 3 : 4;
+    }
+    if (fwd_stages == 3) e = launch_gemm<EpiFwdStats, kBNTile, 3, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    else e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
@@ -477,12 +493,22 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   ARCB_CUDA(cudaMemsetAsync(dxhat, 0, B * W.Dp * 4, st));
 
   if (use_persistent_backward()) {
-    // double-buffered scratch: two buffers of `pchunk` classes each
-    int64_t pchunk = scratch_bytes / (W.Bp * 2) / 2 / 128 * 128;
+    // multi-buffered scratch: kScratchBufs buffers of `pchunk` classes each (two if it is small)
+    static int want_bufs = 0;
+    if (!want_bufs) {
+      const char* e = getenv("ARCB_SCRATCH_BUFS");
+      want_bufs = (e && e[0] == '2') ? 2 : 3;
+    }
+    int nbuf = want_bufs;
+    int64_t pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
+    if (pchunk < 128) {
+      nbuf = 2;
+      pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
+    }
     if (pchunk >= 128) {
       if (pchunk > round_up(Cs, 128)) pchunk = round_up(Cs, 128);
-      return ext ? launch_bwd_persistent<true>(W, s, grad_logits, ldgl, gt, pchunk, dw, dxhat, st)
-                 : launch_bwd_persistent<false>(W, s, grad_logits, ldgl, gt, pchunk, dw, dxhat, st);
+      return ext ? launch_bwd_persistent<true>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st)
+                 : launch_bwd_persistent<false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st);
     }
   }
 

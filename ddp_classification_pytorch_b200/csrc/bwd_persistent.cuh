@@ -12,13 +12,18 @@
 // All CTAs walk ONE global tile list  G0, G1, XW0, G2, XW1, ..., G(n-1), XW(n-2), XW(n-1)
 // round-robin; the look-ahead of one G phase means a CTA that reaches XW(k) almost never has to
 // wait.  Dependencies are two arrays of global counters:
-//   g_done[k]   G tiles of chunk k whose stores have completed  -> gates the loads of X(k)/W(k)
-//   xw_done[k]  X/W tiles of chunk k that finished reading G^T  -> gates the stores of G(k+2)
+//   g_done[k]   half-tiles of G(k) whose stores have completed  -> gates the loads of X(k)/W(k)
+//   xw_done[k]  X/W tiles of chunk k that finished reading G^T  -> gates the stores of G(k+nbuf)
 // Every wait targets a tile that is EARLIER in the list and all CTAs are co-resident (cooperative
 // launch), so the schedule cannot deadlock.
 //
-// Warp roles: 0 = TMA producer, 1 = tcgen05.mma issuer, 2 = TMEM allocator, 3 = G^T store issuer
-// (TMA store + completion + release of g_done, off the epilogue's critical path), 4..11 = epilogue.
+// Warp roles: 0 = TMA producer, 1 = tcgen05.mma issuer, 2 / 3 = G^T store issuers of epilogue
+// warpgroup 1 / 0 (TMA store + completion + release of g_done, off the epilogue's critical path;
+// warp 2 also owns the TMEM allocation), 4..11 = epilogue (two warpgroups, half the columns each).
+//
+// Shared memory: 4 operand stages of 48 KB (the L2 -> SM latency needs that much in flight), and
+// only 34 KB for the epilogues: one 16 KB slot per epilogue warpgroup -- a [128 x 64] bf16 box of
+// G^T, or a [128 x 32] fp32 chunk of dX / dW -- plus the staged log-sum-exps / labels.
 #pragma once
 
 #include "epilogues.cuh"
@@ -26,20 +31,22 @@
 namespace arcb {
 
 constexpr int kPBN = 256;
-constexpr int kPStages = 3;
+constexpr int kPStages = 4;
 constexpr int kPABytes = kBM * kBK * 2;
 constexpr int kPStageBytes = kPABytes + kPBN * kBK * 2;  // 48 KB
-constexpr int kPEpiSmem =
-    (EpiBwdG<false>::kSmemBytes > kChunkOutSmem ? EpiBwdG<false>::kSmemBytes : kChunkOutSmem);  // union
-constexpr int kPNumBars = 2 * kPStages + 4 + 2;
+constexpr int kPSlotBytes = kBM * 128;                   // 16 KB: [128 rows x 128 B], one per epilogue warpgroup
+constexpr int kPRowsOff = 2 * kPSlotBytes;               // staged lse2 / labels: 2 warpgroups x 128 x (4 + 4) B
+constexpr int kPEpiSmem = kPRowsOff + 256 * 8;
+constexpr int kPNumBars = 2 * kPStages + 4 + 4;          // + slot_full[2], slot_free[2]
 constexpr int kPBarOff = kPStages * kPStageBytes + kPEpiSmem;
-constexpr int kPSmemTotal = kPBarOff + kPNumBars * 8 + 16 + 1024;
+constexpr int kPSmemTotal = kPBarOff + kPNumBars * 8 + 16;  // no slack: the dynamic smem base is 1024 B aligned
 static_assert(kPSmemTotal <= 232448, "persistent backward kernel exceeds the shared memory budget");
 
 enum : int { kItemG = 0, kItemX = 1, kItemW = 2 };
 
 struct BwdPlan {
   int n_chunks, chunk_rows;  // chunk_rows % 128 == 0
+  int nbuf;                  // scratch buffers of chunk_rows rows each (2 or 3); chunk k uses buffer k % nbuf
   int Cs, B, Bp, D, Dp;
   int g_tiles_n;             // Bp / 256
   int g_kb;                  // Dp / 64
@@ -48,6 +55,7 @@ struct BwdPlan {
   int w_tiles_n, w_kb;       // ceil(D / 256), ceil(B / 64)
   unsigned int* g_done;      // [n_chunks], zeroed before the launch
   unsigned int* xw_done;     // [n_chunks], zeroed before the launch
+  int kind_mask;             // debug: bit k set = tiles of kind k run (7 = all); anything else gives wrong results
 };
 
 struct BwdArgs {
@@ -201,16 +209,19 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
                       const __grid_constant__ CUtensorMap tmDx,      // dxhat [B, D] f32 box 32 x 128
                       const __grid_constant__ CUtensorMap tmDw,      // dW    [Cs, D] f32 box 32 x 128
                       const BwdPlan pl, const BwdArgs ar) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0u) {  // the 128 B swizzle needs 1024 B aligned tiles; no slack is reserved
+    if (threadIdx.x == 0 && atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) g_wait_timeout[1] = 0xa11u;
+    return;
+  }
   uint8_t* epi_smem = smem + kPStages * kPStageBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kPBarOff);
   uint64_t* full = bars;
   uint64_t* empty = bars + kPStages;
   uint64_t* tfull = bars + 2 * kPStages;
   uint64_t* tempty = bars + 2 * kPStages + 2;
-  uint64_t* stage_full = bars + 2 * kPStages + 4;  // epilogue -> store issuer: G^T tile is in smem
-  uint64_t* stage_free = bars + 2 * kPStages + 5;  // store issuer -> epilogue: tile has been read
+  uint64_t* slot_full = bars + 2 * kPStages + 4;  // [2] epilogue warpgroup -> its store issuer: box is in smem
+  uint64_t* slot_free = bars + 2 * kPStages + 6;  // [2] store issuer -> warpgroup: box has been read
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kPNumBars);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
@@ -236,8 +247,10 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], kEpiThreads / 32);
     }
-    mbar_init(stage_full, kEpiThreads / 32);
-    mbar_init(stage_free, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&slot_full[i], kWgThreads / 32);
+      mbar_init(&slot_free[i], 1);
+    }
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -258,13 +271,13 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       int stage = 0;
       uint32_t phase = 0;
       while (w.next(pl, it)) {
-        if (it.kb0 >= it.kb1) continue;
-        if (it.kind != kItemG) {  // G^T of this chunk must be complete and visible
-          wait_counter(pl.g_done + it.chunk, static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
+        if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
+        if (it.kind != kItemG && (pl.kind_mask & 1)) {  // G^T of this chunk must be complete and visible
+          wait_counter(pl.g_done + it.chunk, 2u * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
           fence_proxy_async_all();
         }
         const int c0 = it.chunk * pl.chunk_rows;                // first class of the chunk in the shard
-        const int buf_row = (it.chunk & 1) * pl.chunk_rows;     // first row of the chunk's scratch buffer
+        const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;  // first row of the chunk's scratch buffer
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
           mbar_arrive_expect_tx(&full[stage], kPStageBytes);
@@ -304,7 +317,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       int acc = 0;
       uint32_t acc_phase = 0;
       while (w.next(pl, it)) {
-        if (it.kb0 >= it.kb1) continue;
+        if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
         const bool a_mn = it.kind == kItemX;
         const bool b_mn = it.kind != kItemG;
         const uint32_t idesc = make_idesc_bf16(kBM, kPBN, a_mn, b_mn);
@@ -335,32 +348,33 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         if (acc == 0) acc_phase ^= 1u;
       }
     }
-  } else if (warp == 3) {
+  } else if (warp == 2 || warp == 3) {
     if (lane == 0) {
-      // --------------------------- G^T store issuer -----------------------------
+      // ---------------- G^T store issuer of epilogue warpgroup (3 - warp) ----------------
+      const int wg = 3 - warp;
+      uint8_t* slot = epi_smem + wg * kPSlotBytes;
       ItemWalker w;
       w.init(pl);
       Item it;
-      uint32_t g_n = 0;
+      uint32_t n_box = 0;  // boxes this issuer has sent so far (two per G tile)
       while (w.next(pl, it)) {
-        if (it.kind != kItemG || it.kb0 >= it.kb1) continue;
-        mbar_wait(stage_full, g_n & 1u, 0x600u);
-        if (it.chunk >= 2) {  // the X / W tiles that read this scratch buffer two chunks ago must be done
-          const int kp = it.chunk - 2;
-          wait_counter(pl.xw_done + kp, static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
-          fence_proxy_async_all();
+        if (it.kind != kItemG || it.kb0 >= it.kb1 || !(pl.kind_mask & 1)) continue;
+        const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;
+        for (int bx = 0; bx < 2; ++bx, ++n_box) {
+          mbar_wait(&slot_full[wg], n_box & 1u, 0x600u + wg);
+          if (bx == 0 && it.chunk >= pl.nbuf && (pl.kind_mask & 6) == 6) {  // the X / W tiles that last read this scratch buffer must be done
+            const int kp = it.chunk - pl.nbuf;
+            wait_counter(pl.xw_done + kp, static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
+            fence_proxy_async_all();
+          }
+          tma_store_2d(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + it.m_blk * kBM);
+          tma_store_commit();
+          tma_store_wait_read0();
+          mbar_arrive(&slot_free[wg]);  // the warpgroup may overwrite its slot
         }
-        const int buf_row = (it.chunk & 1) * pl.chunk_rows;
-#pragma unroll
-        for (int bx = 0; bx < kPBN / 64; ++bx)
-          tma_store_2d(&tmGtSt, epi_smem + bx * (kBM * 128), it.n_blk * kPBN + bx * 64, buf_row + it.m_blk * kBM);
-        tma_store_commit();
-        tma_store_wait_read0();
-        mbar_arrive(stage_free);  // the epilogue may overwrite the staging tile
-        tma_store_wait_all0();    // writes (and, through the barrier chain, the t_j atomics) are done
+        tma_store_wait_all0();  // both boxes are written (and, through the barrier chain, the t_j atomics are done)
         __threadfence();
-        atomicAdd(pl.g_done + it.chunk, 1u);
-        ++g_n;
+        atomicAdd(pl.g_done + it.chunk, 1u);  // each G tile counts twice: once per warpgroup
       }
     }
   } else if (warp >= 4) {
@@ -368,18 +382,23 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     const int quad = warp & 3;
     const int row_in_tile = quad * 32 + lane;
     const int epi_tid = static_cast<int>(threadIdx.x) - (kGemmThreads - kEpiThreads);
+    const int wg = epi_tid >> 7;
+    const int wg_tid = epi_tid & 127;
+    uint8_t* slot = epi_smem + wg * kPSlotBytes;
+    float* lse_s = reinterpret_cast<float*>(epi_smem + kPRowsOff) + wg * 128;       // this warpgroup's 128 samples
+    int* lbl_s = reinterpret_cast<int*>(epi_smem + kPRowsOff + 256 * 4) + wg * 128;
     ItemWalker w;
     w.init(pl);
     Item it;
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t g_count = 0;
+    uint32_t n_box = 0;  // G^T boxes this warpgroup has handed to its store issuer
     int prev_kind = -1;
     EpiOutState ost;
     ost.it = 0;
     const float gscale = EXT ? 0.f : __ldg(ar.gscale);
     while (w.next(pl, it)) {
-      if (it.kb0 >= it.kb1) continue;
+      if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
       // per-tile row data is fetched before waiting for the accumulator, so its latency is hidden
       float lse_v = 0.f;
       int lbl_v = -1;
@@ -394,11 +413,15 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         __threadfence();
         atomicAdd(pl.xw_done + it.chunk, 1u);
       }
-      // the G^T staging tile and the X / W chunk buffers share the same shared memory
+      // the slot is used through two different mechanisms (mbarrier hand-off to the store issuer for
+      // G tiles, bulk-group waits for X / W chunks): drain the previous one when the kind changes
       if (prev_kind != -1 && (it.kind == kItemG) != (prev_kind == kItemG)) {
-        if (prev_kind == kItemG) mbar_wait(stage_free, (g_count & 1u) ^ 1u, 0x800u);
-        else if ((epi_tid & 127) == 0) tma_store_wait_read<0>();
-        named_bar_sync(1, kEpiThreads);
+        if (prev_kind == kItemG) {
+          mbar_wait(&slot_free[wg], (n_box & 1u) ^ 1u, 0x800u + wg);
+        } else {
+          if (wg_tid == 0) tma_store_wait_read<0>();
+          named_bar_sync(2 + wg, kWgThreads);
+        }
       }
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * kPBN) + (static_cast<uint32_t>(quad * 32) << 16);
       TileCoord tc;
@@ -409,9 +432,6 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       const int c0 = it.chunk * pl.chunk_rows;
       const int rows = plan_rows(pl, it.chunk);
       if (it.kind == kItemG) {
-        mbar_wait(stage_free, (g_count & 1u) ^ 1u, 0x900u);  // previous G tile has left the staging tile
-        EpiBwdG<EXT>::stage_rows(epi_smem, epi_tid, lse_v, lbl_v);
-        named_bar_sync(1, kEpiThreads);
         typename EpiBwdG<EXT>::Params p;
         p.lse2 = ar.lse2;
         p.gscale = ar.gscale;
@@ -428,19 +448,62 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         p.grad_out = EXT ? ar.grad_out + c0 : nullptr;
         p.ldgo = ar.ldgo;
         p.s_ext = ar.s_ext;
-        EpiBwdG<EXT>::template body<kPBN>(p, gscale, tc, taddr, row_in_tile, epi_tid, epi_smem);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[acc]);
-        fence_proxy_async_smem();  // staging tile -> visible to the TMA engine
-        __syncwarp();
-        if (lane == 0) mbar_arrive(stage_full);
-        ++g_count;
+        // stage this warpgroup's 128 log-sum-exps / labels (the previous tile's readers are all past
+        // their last chunk: they arrived on slot_full, which this thread observes through slot_free below,
+        // but a plain warpgroup barrier is cheaper and sufficient)
+        named_bar_sync(2 + wg, kWgThreads);
+        if (!EXT) lse_s[wg_tid] = lse_v;
+        lbl_s[wg_tid] = lbl_v;
+        named_bar_sync(2 + wg, kWgThreads);
+        const int row_local = it.m_blk * kBM + row_in_tile;
+        const int cls = c0 + row_local;
+        const int tile_cls0 = c0 + it.m_blk * kBM;
+        const bool row_ok = row_local < rows;
+        float tsum = 0.f;
+        const uint32_t srow = smem_u32(slot) + row_in_tile * 128;
+        const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
+#pragma unroll 1
+        for (int bx = 0; bx < 2; ++bx, ++n_box) {
+          // the store issuer has finished reading the previous box out of this slot
+          mbar_wait(&slot_free[wg], (n_box & 1u) ^ 1u, 0x900u + wg);
+#pragma unroll 1
+          for (int h = 0; h < 2; ++h) {
+            const int cl = bx * 64 + h * 32;      // column inside this warpgroup's half
+            const int c = wg * 128 + cl;          // column inside the tile
+            const int col0 = it.n_blk * kPBN + c;
+            float v[32];
+            tmem_ld32(taddr + c, v);
+            float g[32];
+            EpiBwdG<EXT>::chunk_math(p, gscale, lse_s + cl, lbl_s[cl + lane], col0, cls, tile_cls0, row_ok, row_local,
+                                     v, g);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) tsum = fmaf(g[j], v[j], tsum);
+            const uint32_t q0 = static_cast<uint32_t>(h * 4);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t a = srow + (((q0 + q) ^ sw) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a),
+                           "r"(pack_bf16x2(g[q * 8 + 0], g[q * 8 + 1])), "r"(pack_bf16x2(g[q * 8 + 2], g[q * 8 + 3])),
+                           "r"(pack_bf16x2(g[q * 8 + 4], g[q * 8 + 5])), "r"(pack_bf16x2(g[q * 8 + 6], g[q * 8 + 7]))
+                           : "memory");
+            }
+          }
+          if (bx == 1) {  // all TMEM reads of this tile are done; t_j must precede the last hand-off
+            tc_fence_before();
+            if (row_ok) atomicAdd(ar.tproj + cls, tsum);
+          }
+          fence_proxy_async_smem();  // box -> visible to the TMA engine
+          __syncwarp();
+          if (lane == 0) {
+            if (bx == 1) mbar_arrive(&tempty[acc]);
+            mbar_arrive(&slot_full[wg]);
+          }
+        }
       } else if (it.kind == kItemX) {
         EpiRedAdd::Params p;
         p.M = pl.B;
         p.N = pl.D;
-        EpiRedAdd::template consume<kPBN>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
+        EpiRedAdd::template consume<kPBN, 1>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[acc]);
@@ -455,7 +518,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         p.D = pl.D;
         p.Dp = pl.Dp;
         p.use_tma = ar.dw_tma;
-        EpiDW::template consume<kPBN>(p, ost, tc, tmDw, taddr, row_in_tile, epi_tid, epi_smem);
+        EpiDW::template consume<kPBN, 1>(p, ost, tc, tmDw, taddr, row_in_tile, epi_tid, epi_smem);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[acc]);
@@ -464,7 +527,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
     }
-    if ((epi_tid & 127) == 0) tma_store_wait_all0();
+    if (wg_tid == 0) tma_store_wait_all0();
   }
 
   tc_fence_before();

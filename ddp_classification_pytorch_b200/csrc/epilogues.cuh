@@ -34,13 +34,14 @@ constexpr int kWgThreads = 128;
 constexpr int kChunkBufBytes = kBM * 128;
 constexpr int kChunkOutSmem = 2 * 2 * kChunkBufBytes;
 
-template <bool REDUCE>
+template <bool REDUCE, int NBUF = 2>
 __device__ __forceinline__ void chunk_out_tma(const CUtensorMap& tm, uint8_t* epi_smem, int wg, int wg_tid,
                                               int row_in_tile, int iter, const float (&r)[32], int c_inner,
                                               int c_outer) {
-  uint8_t* buf = epi_smem + (wg * 2 + (iter & 1)) * kChunkBufBytes;
-  // the store that used this buffer two chunks ago must have finished reading it
-  if (wg_tid == 0) tma_store_wait_read<1>();
+  static_assert(NBUF == 1 || NBUF == 2, "one or two chunk buffers per warpgroup");
+  uint8_t* buf = epi_smem + (wg * NBUF + (NBUF == 2 ? (iter & 1) : 0)) * kChunkBufBytes;
+  // the store that last used this buffer (NBUF chunks ago) must have finished reading it
+  if (wg_tid == 0) tma_store_wait_read<NBUF - 1>();
   named_bar_sync(2 + wg, kWgThreads);
   const uint32_t base = smem_u32(buf) + row_in_tile * 128;
   const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
@@ -280,6 +281,55 @@ struct EpiBwdG {
     named_bar_sync(1, kEpiThreads);
     body<BN>(p, st.gscale, tc, taddr, row_in_tile, epi_tid, smem);
   }
+  // One 32-sample chunk of one class row: v = recomputed cosines (in/out: the label column gets the
+  // exact fp32 cosine), g = dLoss/dcos.  lse_c -> the 32 staged log-sum-exps, my_lbl = the staged
+  // label of sample col0 + lane.  All 32 lanes of the warp must call this together.
+  __device__ static __forceinline__ void chunk_math(const Params& p, float gscale, const float* lse_c, int my_lbl,
+                                                    int col0, int cls, int tile_cls0, bool row_ok, int row_local,
+                                                    float (&v)[32], float (&g)[32]) {
+    if constexpr (!EXT) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 l4 = *reinterpret_cast<const float4*>(lse_c + j);
+        g[j + 0] = ex2_approx(fmaf(v[j + 0], p.s2, -l4.x)) * gscale;
+        g[j + 1] = ex2_approx(fmaf(v[j + 1], p.s2, -l4.y)) * gscale;
+        g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * gscale;
+        g[j + 3] = ex2_approx(fmaf(v[j + 3], p.s2, -l4.w)) * gscale;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int i = col0 + j;
+        float gj = 0.f;
+        if (row_ok && i < p.B) gj = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext;
+        g[j] = gj;
+      }
+    }
+    // label columns of this chunk that fall into this tile's 128 classes (warp-uniform, rare)
+    unsigned hit = __ballot_sync(0xffffffffu, static_cast<unsigned>(my_lbl - tile_cls0) < static_cast<unsigned>(kBM));
+    while (hit) {
+      const int j = __ffs(hit) - 1;
+      hit &= hit - 1;
+      const int tl = __shfl_sync(0xffffffffu, my_lbl, j);
+      if (tl == cls) {  // the one thread that owns the label's class row
+        const int i = col0 + j;
+        const float ct = __ldg(p.cos_t + i);
+        const float dp = __ldg(p.dphi + i);
+        float gt;
+        if constexpr (!EXT) {
+          gt = gscale * (ex2_approx(__ldg(p.zt2 + i) - lse_c[j]) - 1.f) * dp;
+        } else {
+          gt = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext * dp;
+        }
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj)
+          if (jj == j) {
+            g[jj] = gt;
+            v[jj] = ct;
+          }
+      }
+    }
+  }
   // The tile proper: needs the staging tile free and stage_rows() visible to all epilogue threads.
   template <int BN>
   __device__ static void body(const Params& p, float gscale, const TileCoord& tc, uint32_t taddr, int row_in_tile,
@@ -300,49 +350,7 @@ struct EpiBwdG {
       float v[32];
       tmem_ld32(taddr + c, v);
       float g[32];
-      if constexpr (!EXT) {
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 l4 = *reinterpret_cast<const float4*>(lse_s + c + j);
-          g[j + 0] = ex2_approx(fmaf(v[j + 0], p.s2, -l4.x)) * gscale;
-          g[j + 1] = ex2_approx(fmaf(v[j + 1], p.s2, -l4.y)) * gscale;
-          g[j + 2] = ex2_approx(fmaf(v[j + 2], p.s2, -l4.z)) * gscale;
-          g[j + 3] = ex2_approx(fmaf(v[j + 3], p.s2, -l4.w)) * gscale;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int i = col0 + j;
-          float gj = 0.f;
-          if (row_ok && i < p.B) gj = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext;
-          g[j] = gj;
-        }
-      }
-      // label columns of this chunk that fall into this tile's 128 classes (warp-uniform, rare)
-      const int my_lbl = lbl_s[c + lane];
-      unsigned hit = __ballot_sync(0xffffffffu, static_cast<unsigned>(my_lbl - tile_cls0) < static_cast<unsigned>(kBM));
-      while (hit) {
-        const int j = __ffs(hit) - 1;
-        hit &= hit - 1;
-        const int tl = __shfl_sync(0xffffffffu, my_lbl, j);
-        if (tl == cls) {  // the one thread that owns the label's class row
-          const int i = col0 + j;
-          const float ct = __ldg(p.cos_t + i);
-          const float dp = __ldg(p.dphi + i);
-          float gt;
-          if constexpr (!EXT) {
-            gt = gscale * (ex2_approx(__ldg(p.zt2 + i) - lse_s[c + j]) - 1.f) * dp;
-          } else {
-            gt = __ldg(p.grad_out + static_cast<int64_t>(i) * p.ldgo + row_local) * p.s_ext * dp;
-          }
-#pragma unroll
-          for (int jj = 0; jj < 32; ++jj)
-            if (jj == j) {
-              g[jj] = gt;
-              v[jj] = ct;
-            }
-        }
-      }
+      chunk_math(p, gscale, lse_s + c, lbl_s[c + lane], col0, cls, tile_cls0, row_ok, row_local, v, g);
 #pragma unroll
       for (int j = 0; j < 32; ++j) tsum = fmaf(g[j], v[j], tsum);
       // 32 bf16 = 64 B = four 16 B chunks of this row inside box (c / 64)
@@ -388,7 +396,7 @@ struct EpiRedAdd {
   __device__ static void drain(int epi_tid) {
     if ((epi_tid & 127) == 0) tma_store_wait_all0();
   }
-  template <int BN>
+  template <int BN, int NBUF = 2>
   __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
                                  int row_in_tile, int epi_tid, uint8_t* smem) {
     const int wg = epi_tid >> 7;
@@ -397,7 +405,7 @@ struct EpiRedAdd {
       if (col0 >= p.N) break;
       float v[32];
       tmem_ld32(taddr + c, v);
-      chunk_out_tma<true>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, v, col0, tc.m_blk * kBM);
+      chunk_out_tma<true, NBUF>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, v, col0, tc.m_blk * kBM);
     }
   }
   template <int BN>
@@ -426,7 +434,7 @@ struct EpiDW {
   __device__ static void drain(int epi_tid) {
     if ((epi_tid & 127) == 0) tma_store_wait_all0();
   }
-  template <int BN>
+  template <int BN, int NBUF = 2>
   __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
                                  int row_in_tile, int epi_tid, uint8_t* smem) {
     const int wg = epi_tid >> 7;
@@ -470,7 +478,7 @@ struct EpiDW {
         }
       }
       if (p.use_tma) {
-        chunk_out_tma<false>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, r, col0, p.row_off + tc.m_blk * kBM);
+        chunk_out_tma<false, NBUF>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, r, col0, p.row_off + tc.m_blk * kBM);
       } else if (valid) {
         float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;
 #pragma unroll

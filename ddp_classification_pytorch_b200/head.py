@@ -26,8 +26,8 @@ from torch.nn import Parameter
 
 from . import _lib
 
-# classes per backward chunk: the persistent backward keeps TWO chunks of bf16 dLoss/dcos in flight
-# (B=1024: 2 x 19.4 MB), which together with the matching w_hat rows stays inside the 126 MB L2;
+# classes per backward chunk: the persistent backward keeps THREE chunks of bf16 dLoss/dcos in flight
+# (B=1024: 3 x 19.4 MB), which together with the matching w_hat rows stays inside the 126 MB L2;
 # 128 * 74 rows give 296 / 148 / 144 tiles per chunk for the three GEMMs on 148 SMs.
 DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 128 * 74))
 
@@ -81,7 +81,7 @@ def _alloc_ws(B, Cs, D, device):
 def _scratch_for(B, Cs, device, chunk_classes):
     L = _lib.lib()
     chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
-    nbytes = L.arcb_scratch_bytes(B, 2 * chunk)  # two buffers (double-buffered persistent backward)
+    nbytes = L.arcb_scratch_bytes(B, 3 * chunk)  # three buffers (multi-buffered persistent backward)
     return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
 

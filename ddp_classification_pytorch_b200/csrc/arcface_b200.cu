@@ -11,6 +11,7 @@
 #include <stdarg.h>
 #include <stdlib.h>
 #include <atomic>
+#include <mutex>
 #include <stdio.h>
 #include <string.h>
 
@@ -282,6 +283,32 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   return ARCB_OK;
 }
 
+// Built-in forward workspace for arcb_shard_forward_static: a fixed block of device memory that is
+// part of the loaded library image, so that entry point never has to ask anybody for memory.
+// NOTE: in host code the name below is only a handle for the runtime, not a device address; the
+// address a kernel can use comes from cudaGetSymbolAddress (static_ws_address()).
+constexpr int64_t kStaticWsBytes = ARCB_STATIC_WS_BYTES;
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+
+// Device address of g_static_ws on the CURRENT device; looked up once per device and cached.
+int static_ws_address(void** out) {
+  static std::mutex mu;
+  static void* addr[64] = {nullptr};
+  int dev = -1;
+  ARCB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(ARCB_ERR_INVALID, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_ws);
+    if (e != cudaSuccess || !p)
+      return fail(ARCB_ERR_CUDA, "cudaGetSymbolAddress(built-in workspace) on device %d: %s", dev, cudaGetErrorString(e));
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return ARCB_OK;
+}
+
 std::atomic<int> g_bwd_mode{-1};  // -1: from the environment (default persistent), 0: per-chunk launches, 1: persistent
 bool use_persistent_backward() {
   int mode = g_bwd_mode.load(std::memory_order_relaxed);
@@ -435,6 +462,28 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
   }
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;
+}
+
+// Forward for hosts that must not allocate: identical to arcb_shard_forward, except that the
+// workspace is the library's own fixed device block instead of a caller buffer.
+int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
+                              int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
+                              int easy_margin, float* stats, void* stream) {
+  int rc = check_dims(B, Cs, D);
+  if (rc) return rc;
+  const int64_t need = carve(nullptr, B, Cs, D).total;
+  if (need > kStaticWsBytes)
+    return fail(ARCB_ERR_WORKSPACE,
+                "arcb_shard_forward_static: B=%lld, Cs=%lld, D=%lld needs %lld bytes of workspace but the built-in "
+                "block holds %lld; use arcb_shard_forward with a caller-owned workspace for this size",
+                (long long)B, (long long)Cs, (long long)D, (long long)need, (long long)kStaticWsBytes);
+  void* ws = nullptr;
+  rc = static_ws_address(&ws);  // first call on a device resolves the address (not a kernel launch, no allocation)
+  if (rc) return rc;
+  // Nothing in the forward workspace has to start from zero: every region is fully rewritten
+  // (normalised operands incl. their padding, per-sample target data, per-tile partials) before it is read.
+  return arcb_shard_forward(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, kStaticWsBytes,
+                            stats, stream);
 }
 
 int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,

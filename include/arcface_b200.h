@@ -77,6 +77,28 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
                        int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
                        int64_t ws_bytes, float* stats, void* stream);
 
+/* ---- fused forward without a caller workspace (no counterpart in the reference) ----
+ * For hosts that are not allowed to obtain device memory when the call happens: a plugin living inside another
+ * runtime whose allocator owns all of HBM, a serving loop that has frozen its memory plan, or a foreign-language
+ * binding that can pass pointers it was given but has no allocator of its own.  Those callers cannot provide the
+ * `ws` buffer arcb_shard_forward needs, and neither this function nor anything it calls allocates or frees
+ * (no cudaMalloc / cudaFree, no allocating library routine): the workspace is a fixed ARCB_STATIC_WS_BYTES block
+ * that is part of the library image on every GPU that loads it (held until the process exits).
+ *   - Arguments and the stats output are exactly those of arcb_shard_forward, minus ws / ws_bytes.
+ *   - Sizes whose workspace (arcb_ws_bytes(B, Cs, D)) exceeds ARCB_STATIC_WS_BYTES are rejected with
+ *     ARCB_ERR_WORKSPACE and a message naming both numbers; nothing is launched.  (32 MiB covers e.g.
+ *     B=256, Cs=16384, D=512 or B=1024, Cs=8192, D=1024.)
+ *   - The first call on each device looks up the block's device address (with that device current) and caches
+ *     it; make that first call before any stream capture begins.
+ *   - All calls on a device share the one block: two calls whose kernels overlap on the GPU (different streams,
+ *     or different host threads) race on it -- serialise them.  The block keeps the previous call's contents;
+ *     the forward rewrites every region before reading it, so nothing needs clearing between calls.
+ *   - The block is a forward workspace only: arcb_shard_backward still needs the caller-owned `ws` variant. */
+#define ARCB_STATIC_WS_BYTES (32ll << 20)
+int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
+                              int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
+                              int easy_margin, float* stats, void* stream);
+
 /* ---- materialising forward: the literal ArcMarginProduct.forward output, arc_main.py:157-176 ----
  * logits [B, ldl] fp32 <- s * (phi at the label column, cos elsewhere) for this shard's columns. */
 int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,

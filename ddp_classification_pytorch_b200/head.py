@@ -12,7 +12,10 @@ differentiable w.r.t. ``input`` and ``weight``).  Added, non-breaking surface:
   (backward) cross NVLink through ``torch.distributed``.
 
 PyTorch is used here for device memory, streams and collectives only; all arithmetic runs in the
-hand-written CUDA kernels, reached through the C ABI with raw pointers.  There is no CPU path.
+hand-written CUDA kernels, reached through the C ABI with raw pointers.  There is no CPU path:
+the only engine shipped is :class:`CudaEngine`, which refuses CPU tensors and a missing library.
+(The autograd functions talk to the kernels through that small engine interface so that the
+collective plumbing can be exercised by CPU ``gloo`` tests with a checker engine of their own.)
 """
 from __future__ import annotations
 
@@ -40,11 +43,10 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
-def _prep_inputs(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor):
+def _canonical_inputs(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor):
+    """Shape / dtype normalisation shared by every engine (label handling as arc_main.py:169)."""
     if x.dim() != 2:
         raise IndexError(f"input must be 2-D [B, in_features], got {tuple(x.shape)}")  # F.normalize(dim=1)
-    if not x.is_cuda or not w.is_cuda:
-        raise RuntimeError("ArcMarginProduct (B200) requires CUDA tensors: there is no CPU path")
     if x.shape[1] != w.shape[1]:
         raise RuntimeError(f"input has {x.shape[1]} features, weight expects {w.shape[1]}")
     xc = x.detach()
@@ -55,7 +57,7 @@ def _prep_inputs(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor):
     if wc.dtype != torch.float32:
         wc = wc.float()
     wc = wc.contiguous()
-    lab = label.detach().reshape(-1)  # label.view(-1, 1).long()  (arc_main.py:169)
+    lab = label.detach().reshape(-1)  # label.view(-1, 1).long()
     if lab.dtype != torch.int64:
         lab = lab.long()
     lab = lab.to(x.device).contiguous()
@@ -64,25 +66,89 @@ def _prep_inputs(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor):
     return xc, wc, lab
 
 
-class _ShardCtx:
-    """Buffers that live from a forward call to its backward."""
+class CudaEngine:
+    """Every method is one call into libarcface_b200.so (include/arcface_b200.h)."""
 
-    __slots__ = ("B", "Cs", "D", "Dp", "ws", "ws_bytes", "lse", "zt", "group")
+    def prepare(self, x, w, label):
+        if x.dim() != 2:
+            raise IndexError(f"input must be 2-D [B, in_features], got {tuple(x.shape)}")
+        if not x.is_cuda or not w.is_cuda:
+            raise RuntimeError("ArcMarginProduct (B200) requires CUDA tensors: there is no CPU path")
+        _lib.lib()  # raises if the extension has not been built
+        return _canonical_inputs(x, w, label)
+
+    @staticmethod
+    def _alloc_ws(B, Cs, D, device):
+        nbytes = _lib.lib().arcb_ws_bytes(B, Cs, D)
+        if nbytes <= 0:
+            raise RuntimeError("arcb_ws_bytes rejected the sizes")
+        return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+    @staticmethod
+    def _scratch_for(B, Cs, device, chunk_classes):
+        chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
+        nbytes = _lib.lib().arcb_scratch_bytes(B, 3 * chunk)  # three buffers (multi-buffered persistent backward)
+        return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+    def shard_forward(self, xc, wc, lab, cfg):
+        """-> (stats [B,4], state kept for backward)."""
+        L = _lib.lib()
+        B, D = xc.shape
+        Cs = wc.shape[0]
+        ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
+        stats = torch.empty(B, 4, dtype=torch.float32, device=xc.device)
+        _lib.check(L.arcb_shard_forward(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
+                                        cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), _stream()),
+                   "arcb_shard_forward")
+        return stats, (B, Cs, D, ws, ws_bytes)
+
+    def shard_logits(self, xc, wc, lab, cfg):
+        L = _lib.lib()
+        B, D = xc.shape
+        Cs = wc.shape[0]
+        ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
+        out = torch.empty(B, Cs, dtype=torch.float32, device=xc.device)
+        _lib.check(L.arcb_shard_logits(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
+                                       cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(out), Cs,
+                                       _stream()), "arcb_shard_logits")
+        return out, (B, Cs, D, ws, ws_bytes)
+
+    def merge_loss(self, gathered, P, B):
+        """stats [P,B,4] -> (lse [B], target_logit [B], loss scalar)."""
+        L = _lib.lib()
+        dev = gathered.device
+        lse = torch.empty(B, dtype=torch.float32, device=dev)
+        zt = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_merge_loss(_ptr(gathered), P, B, _ptr(lse), _ptr(zt), _ptr(loss), _stream()),
+                   "arcb_merge_loss")
+        return lse, zt, loss
+
+    def shard_backward(self, state, cfg, lse=None, zt=None, grad_loss=None, grad_logits=None):
+        """-> (dw [Cs,D], dxhat partial [B,Dp])."""
+        L = _lib.lib()
+        B, Cs, D, ws, ws_bytes = state
+        dev = ws.device
+        Dp = L.arcb_padded_dim(D)
+        scratch, scratch_bytes = self._scratch_for(B, Cs, dev, cfg["chunk_classes"])
+        dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
+        dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),
+                                         _ptr(grad_logits), Cs if grad_logits is not None else 0, _ptr(scratch),
+                                         scratch_bytes, _ptr(dw), _ptr(dxhat), _stream()), "arcb_shard_backward")
+        return dw, dxhat
+
+    def input_grad(self, xc, dxhat):
+        L = _lib.lib()
+        B, D = xc.shape
+        dx = torch.empty(B, D, dtype=torch.float32, device=xc.device)
+        _lib.check(L.arcb_l2norm_rows_bwd(_ptr(xc), D, _ptr(dxhat), dxhat.shape[1], B, D, _ptr(dx), D, _stream()),
+                   "arcb_l2norm_rows_bwd")
+        return dx
 
 
-def _alloc_ws(B, Cs, D, device):
-    L = _lib.lib()
-    nbytes = L.arcb_ws_bytes(B, Cs, D)
-    if nbytes <= 0:
-        raise RuntimeError("arcb_ws_bytes rejected the sizes")
-    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
-
-
-def _scratch_for(B, Cs, device, chunk_classes):
-    L = _lib.lib()
-    chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
-    nbytes = L.arcb_scratch_bytes(B, 3 * chunk)  # three buffers (multi-buffered persistent backward)
-    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+def _world(group):
+    return 1 if group is None else torch.distributed.get_world_size(group)
 
 
 class _FusedLossFn(torch.autograd.Function):
@@ -90,54 +156,32 @@ class _FusedLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, label, cfg):
-        L = _lib.lib()
-        xc, wc, lab = _prep_inputs(x, w, label)
-        B, D = xc.shape
-        Cs = wc.shape[0]
-        dev = xc.device
-        ws, ws_bytes = _alloc_ws(B, Cs, D, dev)
-        stats = torch.empty(B, 4, dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_shard_forward(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"],
-                                        cfg["s"], cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes,
-                                        _ptr(stats), _stream()), "arcb_shard_forward")
+        eng = cfg["engine"]
+        xc, wc, lab = eng.prepare(x, w, label)
+        B = xc.shape[0]
+        stats, state = eng.shard_forward(xc, wc, lab, cfg)
         group = cfg["group"]
-        if group is not None and torch.distributed.get_world_size(group) > 1:
-            P = torch.distributed.get_world_size(group)
-            gathered = torch.empty(P, B, 4, dtype=torch.float32, device=dev)
+        P = _world(group)
+        if P > 1:  # the only forward exchange: one [B, 4] record per rank
+            gathered = torch.empty(P * B, stats.shape[1], dtype=stats.dtype, device=stats.device)  # = [P, B, 4]
             torch.distributed.all_gather_into_tensor(gathered, stats, group=group)
         else:
-            P, gathered = 1, stats
-        lse = torch.empty(B, dtype=torch.float32, device=dev)
-        zt = torch.empty(B, dtype=torch.float32, device=dev)
-        loss = torch.empty((), dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_merge_loss(_ptr(gathered), P, B, _ptr(lse), _ptr(zt), _ptr(loss), _stream()),
-                   "arcb_merge_loss")
+            gathered = stats
+        lse, zt, loss = eng.merge_loss(gathered, P, B)
         ctx.save_for_backward(xc)
-        ctx.shard = (B, Cs, D, ws, ws_bytes, lse, zt, group, cfg["s"], cfg["chunk_classes"])
-        ctx.w_meta = (w.dtype, x.dtype)
+        ctx.held = (eng, state, lse, zt, cfg, w.dtype, x.dtype)
         cfg["aux_out"].update(lse=lse, target_logit=zt, stats=stats)
         return loss
 
     @staticmethod
     def backward(ctx, grad_loss):
-        L = _lib.lib()
         (xc,) = ctx.saved_tensors
-        B, Cs, D, ws, ws_bytes, lse, zt, group, s, chunk_classes = ctx.shard
-        dev = xc.device
-        Dp = L.arcb_padded_dim(D)
+        eng, state, lse, zt, cfg, w_dtype, x_dtype = ctx.held
         g = grad_loss.detach().to(torch.float32).contiguous()
-        scratch, scratch_bytes = _scratch_for(B, Cs, dev, chunk_classes)
-        dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
-        dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_shard_backward(B, Cs, D, s, _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(g), None, 0,
-                                         _ptr(scratch), scratch_bytes, _ptr(dw), _ptr(dxhat), _stream()),
-                   "arcb_shard_backward")
-        if group is not None and torch.distributed.get_world_size(group) > 1:
-            torch.distributed.all_reduce(dxhat, group=group)  # sum of the class shards' partials
-        dx = torch.empty(B, D, dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_l2norm_rows_bwd(_ptr(xc), D, _ptr(dxhat), Dp, B, D, _ptr(dx), D, _stream()),
-                   "arcb_l2norm_rows_bwd")
-        w_dtype, x_dtype = ctx.w_meta
+        dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt, grad_loss=g)
+        if _world(cfg["group"]) > 1:  # the only backward exchange: sum of the class shards' dX_hat partials
+            torch.distributed.all_reduce(dxhat, group=cfg["group"])
+        dx = eng.input_grad(xc, dxhat)
         return dx.to(x_dtype), dw.to(w_dtype), None, None
 
 
@@ -146,41 +190,22 @@ class _LogitsFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, label, cfg):
-        L = _lib.lib()
-        xc, wc, lab = _prep_inputs(x, w, label)
-        B, D = xc.shape
-        Cs = wc.shape[0]
-        dev = xc.device
-        ws, ws_bytes = _alloc_ws(B, Cs, D, dev)
-        out = torch.empty(B, Cs, dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_shard_logits(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
-                                       cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(out), Cs,
-                                       _stream()), "arcb_shard_logits")
+        eng = cfg["engine"]
+        xc, wc, lab = eng.prepare(x, w, label)
+        out, state = eng.shard_logits(xc, wc, lab, cfg)
         ctx.save_for_backward(xc)
-        ctx.shard = (B, Cs, D, ws, ws_bytes, cfg["group"], cfg["s"], cfg["chunk_classes"])
-        ctx.w_meta = (w.dtype, x.dtype)
+        ctx.held = (eng, state, cfg, w.dtype, x.dtype)
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
-        L = _lib.lib()
         (xc,) = ctx.saved_tensors
-        B, Cs, D, ws, ws_bytes, group, s, chunk_classes = ctx.shard
-        dev = xc.device
-        Dp = L.arcb_padded_dim(D)
+        eng, state, cfg, w_dtype, x_dtype = ctx.held
         go = grad_out.detach().to(torch.float32).contiguous()
-        scratch, scratch_bytes = _scratch_for(B, Cs, dev, chunk_classes)
-        dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
-        dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_shard_backward(B, Cs, D, s, _ptr(ws), ws_bytes, None, None, None, _ptr(go), Cs,
-                                         _ptr(scratch), scratch_bytes, _ptr(dw), _ptr(dxhat), _stream()),
-                   "arcb_shard_backward")
-        if group is not None and torch.distributed.get_world_size(group) > 1:
-            torch.distributed.all_reduce(dxhat, group=group)
-        dx = torch.empty(B, D, dtype=torch.float32, device=dev)
-        _lib.check(L.arcb_l2norm_rows_bwd(_ptr(xc), D, _ptr(dxhat), Dp, B, D, _ptr(dx), D, _stream()),
-                   "arcb_l2norm_rows_bwd")
-        w_dtype, x_dtype = ctx.w_meta
+        dw, dxhat = eng.shard_backward(state, cfg, grad_logits=go)
+        if _world(cfg["group"]) > 1:
+            torch.distributed.all_reduce(dxhat, group=cfg["group"])
+        dx = eng.input_grad(xc, dxhat)
         return dx.to(x_dtype), dw.to(w_dtype), None, None
 
 
@@ -205,7 +230,7 @@ class ArcMarginProduct(nn.Module):
     """
 
     def __init__(self, in_features, out_features, s=30.0, m=0.50, easy_margin=False, *, process_group=None,
-                 chunk_classes: Optional[int] = None):
+                 chunk_classes: Optional[int] = None, _engine=None):
         super().__init__()
         self.in_features = in_features
         self.out_features = out_features
@@ -219,8 +244,8 @@ class ArcMarginProduct(nn.Module):
             world, rank = 1, 0
         self.class_lo, self.class_hi = shard_bounds(out_features, world, rank)
         self.world_size, self.rank = world, rank
-        # weight is initialised for the full matrix (xavier bound uses the global fan-out, arc_main.py:145-146)
-        # and then sliced, so that a sharded head starts from the same distribution as a replicated one.
+        # xavier_uniform_ bound of the FULL matrix (fan-out = global class count, arc_main.py:145-146), so a
+        # sharded head starts from the same distribution as a replicated one.
         rows = self.class_hi - self.class_lo
         self.weight = Parameter(torch.empty(rows, in_features, dtype=torch.float32))
         bound = math.sqrt(6.0 / (in_features + out_features))
@@ -234,6 +259,7 @@ class ArcMarginProduct(nn.Module):
         self.mm = math.sin(math.pi - m) * m
         self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES
         self.aux = {}
+        self._engine = _engine if _engine is not None else CudaEngine()
 
     def extra_repr(self):
         return (f"in_features={self.in_features}, out_features={self.out_features}, s={self.s}, m={self.m}, "
@@ -245,7 +271,7 @@ class ArcMarginProduct(nn.Module):
         return {
             "s": float(self.s), "m": float(self.m), "easy_margin": bool(self.easy_margin),
             "class_offset": int(self.class_lo), "group": self.process_group,
-            "chunk_classes": int(self.chunk_classes), "aux_out": self.aux,
+            "chunk_classes": int(self.chunk_classes), "aux_out": self.aux, "engine": self._engine,
         }
 
     def forward(self, input, label):

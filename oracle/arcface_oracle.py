@@ -222,6 +222,47 @@ def shard_forward_stats(x, w_shard, label, class_offset, s=30.0, m=0.50, easy_ma
     return mx, se, tgt
 
 
+def _normalize_backward(a_raw, d_hat):
+    """Backward of F.normalize (arc_main.py:159) for rows ``a_raw`` given d loss / d a_hat."""
+    a_raw = np.asarray(a_raw, dtype=np.float64)
+    a_hat, den = l2_normalize_rows(a_raw)
+    nrm = np.sqrt((a_raw * a_raw).sum(axis=1, keepdims=True))
+    proj = (a_hat * d_hat).sum(axis=1, keepdims=True)
+    return np.where(nrm > NORMALIZE_EPS, (d_hat - a_hat * proj) / den, d_hat / den)
+
+
+def shard_backward(x, w_shard, label, class_offset, lse, s=30.0, m=0.50, easy_margin=False, grad_scale=1.0):
+    """One class shard's share of the backward, given the GLOBAL log-sum-exp per row.
+
+    Returns (dw_shard [Cs, D] -- final, d loss / d x_hat partial [B, D] -- to be summed over shards).
+    """
+    k = margin_constants(s, m, easy_margin)
+    x = np.asarray(x, dtype=np.float64)
+    w_shard = np.asarray(w_shard, dtype=np.float64)
+    B, Cs = x.shape[0], w_shard.shape[0]
+    idx = labels_as_index(label, B)
+    xh, _ = l2_normalize_rows(x)
+    wh, _ = l2_normalize_rows(w_shard)
+    cosine = xh @ wh.T
+    local = idx - class_offset
+    owned = (local >= 0) & (local < Cs)
+    logits = cosine * k.s
+    dz = np.full_like(cosine, k.s)
+    if owned.any():
+        sub, dsub = margin_logits(cosine[owned], local[owned], k)
+        logits[owned] = sub
+        dz[owned] = dsub
+    g = np.exp(logits - np.asarray(lse, dtype=np.float64)[:, None])
+    g[np.nonzero(owned)[0], local[owned]] -= 1.0
+    dcos = g * (grad_scale / B) * dz
+    return _normalize_backward(w_shard, dcos.T @ xh), dcos @ wh
+
+
+def input_grad(x, dxh):
+    """d loss / d x from the summed d loss / d x_hat (normalisation backward of the embeddings)."""
+    return _normalize_backward(x, np.asarray(dxh, dtype=np.float64))
+
+
 def merge_shard_stats(mx, se, tgt):
     """Merge [P, B] shard records -> (lse[B], target_logit[B], loss)."""
     mx = np.asarray(mx, dtype=np.float64)

@@ -1,0 +1,99 @@
+"""Class-sharded path on CPU: world_size-2 (and 3) gloo process groups.
+
+The module's collective plumbing (shard bounds, class offsets, all_gather of the [B,4] shard
+records, merge, all_reduce of the dX_hat partials, full_weight gather) is exercised for real; the
+per-shard arithmetic -- which in the product is CUDA only -- is supplied by a checker engine built
+on the oracle.  The result must equal the un-sharded oracle.
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from ddp_classification_pytorch_b200 import ArcMarginProduct, shard_bounds
+from ddp_classification_pytorch_b200.head import _canonical_inputs
+from oracle import arcface_oracle as orc
+
+
+class OracleEngine:
+    """Engine with the interface of head.CudaEngine, computing each shard with the CPU oracle."""
+
+    def prepare(self, x, w, label):
+        return _canonical_inputs(x, w, label)
+
+    def shard_forward(self, xc, wc, lab, cfg):
+        mx, se, tgt = orc.shard_forward_stats(xc.numpy(), wc.numpy(), lab.numpy(), cfg["class_offset"], cfg["s"],
+                                              cfg["m"], cfg["easy_margin"])
+        stats = torch.tensor(np.stack([mx, se, tgt, np.zeros_like(mx)], axis=1))  # float64 record
+        return stats, (xc, wc, lab)
+
+    def merge_loss(self, gathered, P, B):
+        g = gathered.reshape(P, B, 4).numpy()
+        lse, tgt, loss = orc.merge_shard_stats(g[:, :, 0], g[:, :, 1], g[:, :, 2])
+        return torch.tensor(lse), torch.tensor(tgt), torch.tensor(loss, dtype=torch.float32)
+
+    def shard_backward(self, state, cfg, lse=None, zt=None, grad_loss=None, grad_logits=None):
+        xc, wc, lab = state
+        dw, dxh = orc.shard_backward(xc.numpy(), wc.numpy(), lab.numpy(), cfg["class_offset"], lse.numpy(), cfg["s"],
+                                     cfg["m"], cfg["easy_margin"], float(grad_loss))
+        return torch.tensor(dw), torch.tensor(dxh)
+
+    def input_grad(self, xc, dxhat):
+        return torch.tensor(orc.input_grad(xc.numpy(), dxhat.numpy()))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, B, D, C, easy, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(123)
+        w_full = (torch.rand(C, D, generator=g) * 2 - 1) * 0.1
+        x = torch.randn(B, D, generator=g)
+        y = torch.randint(0, C, (B,), generator=g)
+        head = ArcMarginProduct(D, C, s=30.0, m=0.5, easy_margin=easy, process_group=dist.group.WORLD,
+                                _engine=OracleEngine())
+        lo, hi = shard_bounds(C, world, rank)
+        assert (head.class_lo, head.class_hi) == (lo, hi) and tuple(head.weight.shape) == (hi - lo, D)
+        with torch.no_grad():
+            head.weight.copy_(w_full[lo:hi])
+        xg = x.clone().requires_grad_(True)
+        loss = head.forward_loss(xg, y)
+        (loss * 2.0).backward()
+        full = head.full_weight()
+        ref = orc.head_forward_backward(x.numpy(), w_full.numpy(), y.numpy(), 30.0, 0.5, easy, grad_scale=2.0)
+        ok = (
+            abs(loss.item() - ref["loss"]) < 1e-5 * abs(ref["loss"])
+            and np.allclose(xg.grad.numpy(), ref["dx"], rtol=1e-4, atol=1e-7)
+            and np.allclose(head.weight.grad.numpy(), ref["dw"][lo:hi], rtol=1e-4, atol=1e-7)
+            and torch.equal(full, w_full)
+            and np.allclose(head.aux["lse"].numpy(), ref["lse"], rtol=1e-6)
+        )
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,easy", [(2, False), (2, True), (3, False)])
+def test_sharded_head_equals_unsharded_oracle(world, easy):
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        out = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker, args=(r, world, port, 24, 32, 101, easy, out)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+            assert p.exitcode == 0
+        assert all(out.get(r) is True for r in range(world)), dict(out)

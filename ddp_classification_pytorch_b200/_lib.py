@@ -31,12 +31,12 @@ EXPORTED = [
     "arcb_version", "arcb_last_error", "arcb_check_watchdog", "arcb_l2norm_rows", "arcb_l2norm_rows_bwd",
     "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
-    "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static",
+    "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3",
 ]
 
 KERNEL_KINDS = [
     "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",
-    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test", "bwd_persistent",
+    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test", "bwd_persistent", "top3",
 ]
 
 _lock = threading.Lock()
@@ -101,6 +101,8 @@ def _declare(lib):
     lib.arcb_shard_logits.argtypes = fwd_args + [vp, i64, vp]
     lib.arcb_shard_forward_static.restype = i32
     lib.arcb_shard_forward_static.argtypes = fwd_args[:-2] + [vp, vp]
+    lib.arcb_shard_top3.restype = i32
+    lib.arcb_shard_top3.argtypes = [vp, i64, vp, i64, i64, i64, i64, i64, f32, vp, i64, vp, vp, vp]
     lib.arcb_merge_loss.restype = i32
     lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
     lib.arcb_shard_backward.restype = i32

@@ -502,6 +502,34 @@ int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, 
   return ARCB_OK;
 }
 
+int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, int64_t B, int64_t Cs, int64_t D,
+                    int64_t class_offset, float s, void* ws, int64_t ws_bytes, float* top_val, int64_t* top_idx,
+                    void* stream) {
+  int rc = check_dims(B, Cs, D);
+  if (rc) return rc;
+  if (!x || !w || !ws || !top_val || !top_idx) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (D * 4 > 96 * 1024) return fail(ARCB_ERR_INVALID, "arcb_shard_top3 supports D <= 24576");
+  Workspace W = carve(ws, B, Cs, D);
+  if (W.total > ws_bytes) return fail(ARCB_ERR_WORKSPACE, "workspace too small");
+  const int nparts = 2 * static_cast<int>((Cs + kBNTile - 1) / kBNTile);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (D * 4 > 48 * 1024) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      ARCB_CUDA(cudaFuncSetAttribute(topk_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      attr_set[dev] = true;
+    }
+  }
+  LaunchScope ls(ARCB_K_TOP3, st);
+  topk_rescore_kernel<<<static_cast<unsigned>(B), kTopkThreads, D * 4, st>>>(
+      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, nparts, W.Bp, (int)B, (int)D, Cs, class_offset, s,
+      top_val, top_idx);
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
 int arcb_merge_loss(const float* stats, int64_t P, int64_t B, float* lse, float* target_logit, float* loss,
                     void* stream) {
   if (!stats || !lse || !loss) return fail(ARCB_ERR_INVALID, "null pointer argument");

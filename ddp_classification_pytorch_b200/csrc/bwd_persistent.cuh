@@ -284,20 +284,25 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
           uint8_t* sa = smem + stage * kPStageBytes;
           uint8_t* sb = sa + kPABytes;
           if (it.kind == kItemG) {
-            tma_load_2d(sa, &tmWhatK, &full[stage], kb * kBK, c0 + it.m_blk * kBM);
-            tma_load_2d(sb, &tmXhatK, &full[stage], kb * kBK, it.n_blk * kPBN);
+            // w_hat rows are read again by X(k) and by the dW epilogue, x_hat by every tile: keep both in L2
+            tma_load_2d_hint(sa, &tmWhatK, &full[stage], kb * kBK, c0 + it.m_blk * kBM, kEvictLast);
+            tma_load_2d_hint(sb, &tmXhatK, &full[stage], kb * kBK, it.n_blk * kPBN, kEvictLast);
           } else if (it.kind == kItemX) {
 #pragma unroll
             for (int j = 0; j < kBM / 64; ++j)
-              tma_load_2d(sa + j * (kBK * 128), &tmGtMN, &full[stage], it.m_blk * kBM + j * 64, buf_row + kb * kBK);
+              tma_load_2d_hint(sa + j * (kBK * 128), &tmGtMN, &full[stage], it.m_blk * kBM + j * 64,
+                               buf_row + kb * kBK, kEvictLast);  // W(k) still has to read it
 #pragma unroll
             for (int j = 0; j < kPBN / 64; ++j)
-              tma_load_2d(sb + j * (kBK * 128), &tmWhatMN, &full[stage], it.n_blk * kPBN + j * 64, c0 + kb * kBK);
+              tma_load_2d_hint(sb + j * (kBK * 128), &tmWhatMN, &full[stage], it.n_blk * kPBN + j * 64, c0 + kb * kBK,
+                               kEvictNormal);
           } else {
-            tma_load_2d(sa, &tmGtK, &full[stage], kb * kBK, buf_row + it.m_blk * kBM);
+            // last reader of this part of G^T: let it leave L2 first instead of being written back later
+            tma_load_2d_hint(sa, &tmGtK, &full[stage], kb * kBK, buf_row + it.m_blk * kBM, kEvictFirst);
 #pragma unroll
             for (int j = 0; j < kPBN / 64; ++j)
-              tma_load_2d(sb + j * (kBK * 128), &tmXhatMN, &full[stage], it.n_blk * kPBN + j * 64, kb * kBK);
+              tma_load_2d_hint(sb + j * (kBK * 128), &tmXhatMN, &full[stage], it.n_blk * kPBN + j * 64, kb * kBK,
+                               kEvictLast);
           }
           if (++stage == kPStages) {
             stage = 0;
@@ -367,7 +372,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
             wait_counter(pl.xw_done + kp, static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
             fence_proxy_async_all();
           }
-          tma_store_2d(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + it.m_blk * kBM);
+          tma_store_2d_hint(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + it.m_blk * kBM, kEvictLast);
           tma_store_commit();
           tma_store_wait_read0();
           mbar_arrive(&slot_free[wg]);  // the warpgroup may overwrite its slot

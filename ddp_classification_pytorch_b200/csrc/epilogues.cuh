@@ -55,7 +55,8 @@ __device__ __forceinline__ void chunk_out_tma(const CUtensorMap& tm, uint8_t* ep
   fence_proxy_async_smem();
   named_bar_sync(2 + wg, kWgThreads);
   if (wg_tid == 0) {
-    if (REDUCE) tma_reduce_add_2d(&tm, buf, c_inner, c_outer); else tma_store_2d(&tm, buf, c_inner, c_outer);
+    // plain stores are the final fp32 dW: streamed out once, never read again by these kernels
+    if (REDUCE) tma_reduce_add_2d(&tm, buf, c_inner, c_outer); else tma_store_2d_hint(&tm, buf, c_inner, c_outer, kEvictFirst);
     tma_store_commit();
   }
 }

@@ -205,6 +205,108 @@ pack_stats_kernel(const float2* __restrict__ rec, const float* __restrict__ zt, 
   *reinterpret_cast<float4*>(stats + static_cast<int64_t>(row) * 4) = make_float4(r.x, r.y, zt[row], 0.f);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Exact top-3 / argmax of the scaled logits (consumers at arc_main.py:338-345, :377-388) without
+// the logits: the forward GEMM left, per row, the bf16-accurate maximum of every 128-class block
+// (`part`).  |cos_bf16 - cos_fp32| <= 2^-8 (two operand roundings, |x_hat||w_hat| = 1), so every
+// class that can be among the true top 3 lies in a block whose maximum is >= (third largest block
+// maximum) - 2 * 2^-8 * s2.  Those few blocks are re-scored in fp32 from the ORIGINAL operands,
+// with the margin value at the label column, and the top 3 of the re-scored logits are returned.
+// One block per row; val = logits in natural units, idx = global class ids.
+// ---------------------------------------------------------------------------------------------
+struct Top3 {
+  float v[3];
+  int i[3];
+};
+__device__ __forceinline__ void top3_insert(Top3& t, float v, int i) {
+  // order: larger value first; equal values: smaller index first (what a stable descending sort gives)
+  auto better = [](float va, int ia, float vb, int ib) { return va > vb || (va == vb && ia < ib); };
+  if (!better(v, i, t.v[2], t.i[2])) return;
+  if (better(v, i, t.v[0], t.i[0])) {
+    t.v[2] = t.v[1]; t.i[2] = t.i[1]; t.v[1] = t.v[0]; t.i[1] = t.i[0]; t.v[0] = v; t.i[0] = i;
+  } else if (better(v, i, t.v[1], t.i[1])) {
+    t.v[2] = t.v[1]; t.i[2] = t.i[1]; t.v[1] = v; t.i[1] = i;
+  } else {
+    t.v[2] = v; t.i[2] = i;
+  }
+}
+
+constexpr int kTopkThreads = 256;
+
+__global__ void __launch_bounds__(kTopkThreads)
+topk_rescore_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, int64_t ldw,
+                    const float* __restrict__ inv_nx, const float* __restrict__ inv_nw,
+                    const int* __restrict__ lbl_local, const float* __restrict__ sub, const float2* __restrict__ part,
+                    int nparts, int64_t ldp, int B, int D, int64_t Cs, int64_t class_offset, float s,
+                    float* __restrict__ top_val, int64_t* __restrict__ top_idx) {
+  extern __shared__ float xs[];  // D floats: the normalised embedding of this row
+  __shared__ Top3 red[kTopkThreads / 32];
+  __shared__ float thr_s;
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const float inx = inv_nx[row];
+  for (int e = tid; e < D; e += blockDim.x) xs[e] = x[static_cast<int64_t>(row) * ldx + e] * inx;
+
+  // (1) third largest block maximum (base-2 units u = s * log2e * cos)
+  Top3 mine;
+  for (int k = 0; k < 3; ++k) { mine.v[k] = -INFINITY; mine.i[k] = 0x7fffffff; }
+  for (int p = tid; p < nparts; p += blockDim.x) top3_insert(mine, part[p * ldp + row].x, p);
+  for (int o = 16; o > 0; o >>= 1) {
+    Top3 other;
+    for (int k = 0; k < 3; ++k) {
+      other.v[k] = __shfl_xor_sync(0xffffffffu, mine.v[k], o);
+      other.i[k] = __shfl_xor_sync(0xffffffffu, mine.i[k], o);
+    }
+    for (int k = 0; k < 3; ++k) top3_insert(mine, other.v[k], other.i[k]);
+  }
+  if (lane == 0) red[warp] = mine;
+  __syncthreads();
+  if (tid == 0) {
+    Top3 all = red[0];
+    for (int wv = 1; wv < kTopkThreads / 32; ++wv)
+      for (int k = 0; k < 3; ++k) top3_insert(all, red[wv].v[k], red[wv].i[k]);
+    // a row with fewer than 3 blocks: every block is a candidate
+    const float third = (nparts >= 3) ? all.v[2] : -INFINITY;
+    thr_s = third - 2.f * 0.00390625f * s * kLog2e;
+  }
+  __syncthreads();
+  const float thr = thr_s;
+
+  // (2) re-score every candidate block in fp32: one warp per class, lanes split the feature dimension
+  const int lbl = lbl_local[row];
+  const float sub_v = sub[row];
+  Top3 best;
+  for (int k = 0; k < 3; ++k) { best.v[k] = -INFINITY; best.i[k] = 0x7fffffff; }
+  for (int p = 0; p < nparts; ++p) {
+    if (!(part[p * ldp + row].x >= thr)) continue;  // block-uniform
+    const int c_begin = p * 128;
+    const int c_end = min(static_cast<int64_t>(c_begin + 128), Cs);
+    for (int c = c_begin + warp; c < c_end; c += kTopkThreads / 32) {
+      const float* wr = w + static_cast<int64_t>(c) * ldw;
+      float acc = 0.f;
+      for (int e = lane; e < D; e += 32) acc = fmaf(xs[e], wr[e], acc);
+      acc = warp_sum(acc);
+      if (lane == 0) {
+        const float cosv = (c == lbl) ? sub_v : acc * inv_nw[c];
+        top3_insert(best, s * cosv, c);
+      }
+    }
+  }
+  // (3) merge the warps' candidates
+  __syncthreads();
+  if (lane == 0) red[warp] = best;
+  __syncthreads();
+  if (tid == 0) {
+    Top3 all = red[0];
+    for (int wv = 1; wv < kTopkThreads / 32; ++wv)
+      for (int k = 0; k < 3; ++k) top3_insert(all, red[wv].v[k], red[wv].i[k]);
+    for (int k = 0; k < 3; ++k) {
+      top_val[row * 3 + k] = all.v[k];
+      top_idx[row * 3 + k] = (all.v[k] == -INFINITY) ? -1 : (class_offset + all.i[k]);
+    }
+  }
+}
+
 // Backward set-up: lse2[i] = lse[i] * log2(e) (+inf on padding), zt2 likewise, gscale = grad * s / B,
 // and clears the per-chunk accumulators.
 __global__ void __launch_bounds__(256)

@@ -113,6 +113,16 @@ class CudaEngine:
                                        _stream()), "arcb_shard_logits")
         return out, (B, Cs, D, ws, ws_bytes)
 
+    def shard_top3(self, xc, wc, state, cfg):
+        """-> (values [B,3] fp32 logits, indices [B,3] int64 global class ids) of this shard."""
+        L = _lib.lib()
+        B, Cs, D, ws, ws_bytes = state
+        val = torch.empty(B, 3, dtype=torch.float32, device=xc.device)
+        idx = torch.empty(B, 3, dtype=torch.int64, device=xc.device)
+        _lib.check(L.arcb_shard_top3(_ptr(xc), D, _ptr(wc), D, B, Cs, D, cfg["class_offset"], cfg["s"], _ptr(ws),
+                                     ws_bytes, _ptr(val), _ptr(idx), _stream()), "arcb_shard_top3")
+        return val, idx
+
     def merge_loss(self, gathered, P, B):
         """stats [P,B,4] -> (lse [B], target_logit [B], loss scalar)."""
         L = _lib.lib()
@@ -170,7 +180,20 @@ class _FusedLossFn(torch.autograd.Function):
         lse, zt, loss = eng.merge_loss(gathered, P, B)
         ctx.save_for_backward(xc)
         ctx.held = (eng, state, lse, zt, cfg, w.dtype, x.dtype)
-        cfg["aux_out"].update(lse=lse, target_logit=zt, stats=stats)
+        aux = cfg["aux_out"]
+        aux.update(lse=lse, target_logit=zt, stats=stats)
+        if cfg["want_top3"]:  # predictions for the accuracy counters (arc_main.py:338-345, :377-388)
+            val, idx = eng.shard_top3(xc, wc, state, cfg)
+            if P > 1:  # keep the best three of the ranks' candidates (index order on equal logits)
+                vals = torch.empty(P * B, 3, dtype=val.dtype, device=val.device)
+                idxs = torch.empty(P * B, 3, dtype=idx.dtype, device=idx.device)
+                torch.distributed.all_gather_into_tensor(vals, val, group=group)
+                torch.distributed.all_gather_into_tensor(idxs, idx, group=group)
+                vals = vals.view(P, B, 3).permute(1, 0, 2).reshape(B, 3 * P)
+                idxs = idxs.view(P, B, 3).permute(1, 0, 2).reshape(B, 3 * P)
+                order = torch.argsort(vals, dim=1, descending=True, stable=True)[:, :3]
+                val, idx = torch.gather(vals, 1, order), torch.gather(idxs, 1, order)
+            aux.update(top3=idx, top3_logits=val, argmax=idx[:, 0])
         return loss
 
     @staticmethod
@@ -272,15 +295,23 @@ class ArcMarginProduct(nn.Module):
             "s": float(self.s), "m": float(self.m), "easy_margin": bool(self.easy_margin),
             "class_offset": int(self.class_lo), "group": self.process_group,
             "chunk_classes": int(self.chunk_classes), "aux_out": self.aux, "engine": self._engine,
+            "want_top3": False,
         }
 
     def forward(self, input, label):
         """Scaled logits ``[B, classes of this rank]`` exactly as arc_main.py:157-176 returns them."""
         return _LogitsFn.apply(input, self.weight, label, self._cfg())
 
-    def forward_loss(self, input, label):
-        """``nn.CrossEntropyLoss()(self(input, label), label)`` fused (arc_main.py:326-327)."""
-        return _FusedLossFn.apply(input, self.weight, label, self._cfg())
+    def forward_loss(self, input, label, want_top3=False):
+        """``nn.CrossEntropyLoss()(self(input, label), label)`` fused (arc_main.py:326-327).
+
+        ``want_top3=True`` additionally leaves what the trainer's accuracy counters take from the logits
+        (``torch.max(out, 1)``, ``out.topk(3)``, arc_main.py:338-345) in ``.aux``: ``argmax`` [B],
+        ``top3`` [B,3] (global class ids) and ``top3_logits`` -- exact fp32 re-scores, not bf16 values.
+        """
+        cfg = self._cfg()
+        cfg["want_top3"] = bool(want_top3)
+        return _FusedLossFn.apply(input, self.weight, label, cfg)
 
     @torch.no_grad()
     def full_weight(self):

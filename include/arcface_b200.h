@@ -105,6 +105,15 @@ int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, 
                       int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
                       int64_t ws_bytes, float* logits, int64_t ldl, void* stream);
 
+/* ---- exact top-3 / argmax of the logits: torch.max(out, 1) / out.topk(3), arc_main.py:338-345, :377-388 ----
+ * Needs the workspace left by arcb_shard_forward for the same inputs.  Only the class blocks whose bf16
+ * block maximum can still reach the top 3 are re-scored, in fp32 from the original x / w (margin value at
+ * the label column).  top_val [B,3] = logits (descending), top_idx [B,3] = GLOBAL class ids (-1 if the shard
+ * has fewer than 3 classes).  Class-sharded: all_gather the [B,3] pairs and keep the best 3. */
+int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, int64_t B, int64_t Cs, int64_t D,
+                    int64_t class_offset, float s, void* ws, int64_t ws_bytes, float* top_val, int64_t* top_idx,
+                    void* stream);
+
 /* ---- merge shard records into the loss: nn.CrossEntropyLoss() mean, arc_main.py:245,:327 ----
  * stats [P, B, 4] (P shard records, e.g. after an all_gather; P = 1 unsharded)
  * -> lse [B], target_logit [B] (may be NULL), loss [1] = mean(lse - target_logit). */
@@ -151,7 +160,8 @@ enum {
   ARCB_K_LOGITS_GEMM = 11,/* materialising forward                   */
   ARCB_K_GEMM_TEST = 12,  /* arcb_gemm_bf16                          */
   ARCB_K_BWD_PERSISTENT = 13, /* whole backward of a shard, one launch */
-  ARCB_K_COUNT = 14
+  ARCB_K_TOP3 = 14,       /* exact top-3 re-score                    */
+  ARCB_K_COUNT = 15
 };
 int64_t arcb_launch_count(void);
 int arcb_profile_enable(int on);

@@ -156,3 +156,51 @@ def test_persistent_and_per_chunk_backward_agree(chunk):
     ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, False)
     assert cosine_similarity(grads[0][0].cpu().numpy(), ref["dx"]) >= GRAD_COS
     assert cosine_similarity(grads[0][1].cpu().numpy(), ref["dw"]) >= GRAD_COS
+
+
+def _check_top3(head_aux, ref_logits, s):
+    """argmax / top-3 must be IDENTICAL to the fp32 reference wherever the reference itself is unambiguous
+    (neighbouring logits further apart than fp32 summation-order noise)."""
+    ref_logits = np.asarray(ref_logits, dtype=np.float64)
+    order = np.argsort(-ref_logits, axis=1, kind="stable")
+    k = min(4, ref_logits.shape[1])
+    top = np.take_along_axis(ref_logits, order[:, :k], axis=1)
+    gaps = top[:, :-1] - top[:, 1:]
+    clear = (gaps > 2e-5 * s).all(axis=1)
+    assert clear.mean() > 0.9
+    got = head_aux["top3"].cpu().numpy()
+    want = order[:, : got.shape[1]]
+    n = min(3, ref_logits.shape[1])
+    assert (got[clear][:, :n] == want[clear][:, :n]).all()
+    assert (head_aux["argmax"].cpu().numpy()[clear] == want[clear][:, 0]).all()
+    np.testing.assert_allclose(head_aux["top3_logits"].cpu().numpy()[clear][:, :n], top[clear][:, :n], atol=2e-4 * s / 30,
+                               rtol=1e-5)
+
+
+def test_exact_top3_matches_reference_golden(golden):
+    g = golden
+    s = float(g["s"])
+    head = _module(g["w"], s, float(g["m"]), bool(g["easy_margin"]))
+    x = torch.tensor(g["x"], device="cuda")
+    y = torch.tensor(g["label"], device="cuda")
+    with torch.no_grad():
+        head.forward_loss(x, y, want_top3=True)
+    _sync_ok()
+    _check_top3(head.aux, g["logits"], s)
+
+
+@pytest.mark.parametrize("shape", [(512, 512, 40000), (200, 96, 3000)])
+def test_exact_top3_vs_oracle_many_classes(shape):
+    # at 40k classes ~10 % of the rows have a top-1/top-2 gap below bf16 resolution: the re-score must fix them
+    B, D, C = shape
+    gen = torch.Generator().manual_seed(C)
+    w = (torch.rand(C, D, generator=gen) * 2 - 1) * (6.0 / (C + D)) ** 0.5
+    x = torch.randn(B, D, generator=gen)
+    y = torch.randint(0, C, (B,), generator=gen)
+    ref = orc.head_forward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, True)
+    head = _module(w.numpy(), 30.0, 0.5, True)
+    with torch.no_grad():
+        loss = head.forward_loss(x.cuda(), y.cuda(), want_top3=True)
+    _sync_ok()
+    assert torch.isfinite(loss)
+    _check_top3(head.aux, ref, 30.0)

@@ -74,14 +74,18 @@ def _nccl_worker(rank, world, port, out):
         with torch.no_grad():
             head.weight.copy_(w[lo:hi])
         xg = x.cuda().requires_grad_(True)
-        loss = head.forward_loss(xg, y.cuda())
+        loss = head.forward_loss(xg, y.cuda(), want_top3=True)
         loss.backward()
         torch.cuda.synchronize()
         ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, True)
+        top = np.take_along_axis(ref["logits"], ref["top3"], axis=1)
+        clear = ((top[:, :-1] - top[:, 1:]) > 1e-3).all(axis=1)
         ok = (abs(loss.item() - ref["loss"]) <= 1e-3 * abs(ref["loss"])
               and cosine_similarity(xg.grad.cpu().numpy(), ref["dx"]) >= 0.999
               and cosine_similarity(head.weight.grad.cpu().numpy(), ref["dw"][lo:hi]) >= 0.999
-              and torch.equal(head.full_weight().cpu(), w))
+              and torch.equal(head.full_weight().cpu(), w)
+              and clear.mean() > 0.9
+              and np.array_equal(head.aux["top3"].cpu().numpy()[clear], ref["top3"][clear]))
         out[rank] = bool(ok)
     finally:
         dist.destroy_process_group()

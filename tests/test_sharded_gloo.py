@@ -31,6 +31,23 @@ class OracleEngine:
         stats = torch.tensor(np.stack([mx, se, tgt, np.zeros_like(mx)], axis=1))  # float64 record
         return stats, (xc, wc, lab)
 
+    def shard_top3(self, xc, wc, state, cfg):
+        # margin only where this shard owns the label
+        lo = cfg["class_offset"]
+        lab = state[2].numpy() - lo
+        cos_logits = orc.head_forward(xc.numpy(), wc.numpy(), np.clip(lab, 0, wc.shape[0] - 1), cfg["s"], cfg["m"],
+                                      cfg["easy_margin"])
+        plain = cfg["s"] * (orc.l2_normalize_rows(xc.numpy())[0] @ orc.l2_normalize_rows(wc.numpy())[0].T)
+        owned = (lab >= 0) & (lab < wc.shape[0])
+        z = np.where(owned[:, None], cos_logits, plain)
+        order = np.argsort(-z, axis=1, kind="stable")[:, :3]
+        val = np.take_along_axis(z, order, axis=1)
+        if order.shape[1] < 3:  # shard with fewer than three classes
+            pad = 3 - order.shape[1]
+            order = np.pad(order, ((0, 0), (0, pad)), constant_values=-1 - lo)
+            val = np.pad(val, ((0, 0), (0, pad)), constant_values=-np.inf)
+        return torch.tensor(val), torch.tensor(order + lo)
+
     def merge_loss(self, gathered, P, B):
         g = gathered.reshape(P, B, 4).numpy()
         lse, tgt, loss = orc.merge_shard_stats(g[:, :, 0], g[:, :, 1], g[:, :, 2])
@@ -68,7 +85,7 @@ def _worker(rank, world, port, B, D, C, easy, out):
         with torch.no_grad():
             head.weight.copy_(w_full[lo:hi])
         xg = x.clone().requires_grad_(True)
-        loss = head.forward_loss(xg, y)
+        loss = head.forward_loss(xg, y, want_top3=True)
         (loss * 2.0).backward()
         full = head.full_weight()
         ref = orc.head_forward_backward(x.numpy(), w_full.numpy(), y.numpy(), 30.0, 0.5, easy, grad_scale=2.0)
@@ -78,6 +95,8 @@ def _worker(rank, world, port, B, D, C, easy, out):
             and np.allclose(head.weight.grad.numpy(), ref["dw"][lo:hi], rtol=1e-4, atol=1e-7)
             and torch.equal(full, w_full)
             and np.allclose(head.aux["lse"].numpy(), ref["lse"], rtol=1e-6)
+            and np.array_equal(head.aux["top3"].numpy(), ref["top3"])
+            and np.array_equal(head.aux["argmax"].numpy(), ref["argmax"])
         )
         out[rank] = bool(ok)
     finally:

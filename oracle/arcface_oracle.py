@@ -310,4 +310,5 @@ class TorchPort:
         out = out * k.s
         loss = F.cross_entropy(out, label.view(-1).long())
         loss.backward()
+        self.last_logits = out.detach()
         return float(loss.detach()), x.grad, self.weight.grad

@@ -1,0 +1,110 @@
+"""BASELINE.json's full sizes on the GPU: configs[1] (B256 D2048 C1000), configs[2] (B512 D512 C100k) and
+configs[3] (B1024 D512 C1M).
+
+The CPU oracle cannot finish these in seconds, so the checker is (a) the oracle's eager fp32 torch port run
+on the same GPU (fp32 SGEMM, autograd) and (b) size-independent properties of the maths:
+  * F.normalize backward makes every gradient row orthogonal to its own input row (x_i . dX_i = 0, w_j . dW_j = 0);
+  * gradients are linear in the upstream gradient of the loss;
+  * splitting the classes into shards and merging the records changes nothing (log-sum-exp is associative);
+  * lse_i >= target logit_i, and sum_i (lse_i - target_i) / B is the loss.
+"""
+import numpy as np
+import pytest
+import torch
+
+from ddp_classification_pytorch_b200 import ArcMarginProduct, _lib, shard_bounds
+from ddp_classification_pytorch_b200.head import CudaEngine
+from oracle.arcface_oracle import TorchPort
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = {
+    "cfg2": (256, 2048, 1000),
+    "cfg3": (512, 512, 100_000),
+    "cfg4": (1024, 512, 1_000_000),
+}
+
+
+def _cos(a, b):
+    a = a.double().flatten(); b = b.double().flatten()
+    return float(a @ b / (a.norm() * b.norm()))
+
+
+def _make(B, D, C, easy):
+    g = torch.Generator(device="cuda").manual_seed(B + C)
+    bound = (6.0 / (C + D)) ** 0.5
+    w = (torch.rand(C, D, generator=g, device="cuda") * 2 - 1) * bound
+    x = torch.randn(B, D, generator=g, device="cuda")
+    y = torch.randint(0, C, (B,), generator=g, device="cuda")
+    # plant rows on both sides of the margin branches
+    for r, c in zip(range(0, B, max(1, B // 16)), [-0.99, -0.9, -0.86, -0.3, -0.01, 0.01, 0.4, 0.9] * 2):
+        wy = w[y[r]] / w[y[r]].norm()
+        n = torch.randn(D, generator=g, device="cuda"); n = n - (n @ wy) * wy; n = n / n.norm()
+        x[r] = 2.0 * (c * wy + (1 - c * c) ** 0.5 * n)
+    head = ArcMarginProduct(D, C, s=30.0, m=0.5, easy_margin=easy).cuda()
+    with torch.no_grad():
+        head.weight.copy_(w)
+    return head, x, y, w
+
+
+@pytest.mark.parametrize("name,easy", [("cfg2", False), ("cfg3", False), ("cfg3", True), ("cfg4", False)])
+def test_full_size_against_eager_fp32_port_on_gpu(name, easy):
+    B, D, C = CONFIGS[name]
+    head, x, y, w = _make(B, D, C, easy)
+    xg = x.clone().requires_grad_(True)
+    loss = head.forward_loss(xg, y, want_top3=True)
+    loss.backward()
+    _lib.check(_lib.lib().arcb_check_watchdog(torch.cuda.current_stream().cuda_stream))
+    port = TorchPort(w, 30.0, 0.5, easy)
+    ref_loss, ref_dx, ref_dw = port.step(x, y)
+    assert loss.item() == pytest.approx(ref_loss, rel=1e-3)          # north_star: loss within 1e-3 relative
+    assert _cos(xg.grad, ref_dx) >= 0.999 and _cos(head.weight.grad, ref_dw) >= 0.999   # gradient cosine >= 0.999
+    assert float(xg.grad.norm()) == pytest.approx(float(ref_dx.norm()), rel=2e-2)
+    assert float(head.weight.grad.norm()) == pytest.approx(float(ref_dw.norm()), rel=2e-2)
+    # argmax / top-3: identical wherever the fp32 logits are separated by more than SGEMM summation-order noise
+    top = port.last_logits.topk(4, dim=1)
+    clear = ((top.values[:, :-1] - top.values[:, 1:]) > 1e-3).all(dim=1)
+    assert clear.float().mean() > 0.85
+    assert torch.equal(head.aux["top3"][clear], top.indices[clear][:, :3])
+    assert torch.equal(head.aux["argmax"][clear], port.last_logits.argmax(1)[clear])
+    rows = torch.arange(B, device="cuda")
+    torch.testing.assert_close(head.aux["target_logit"], port.last_logits[rows, y], atol=2e-3, rtol=1e-5)
+
+
+@pytest.mark.parametrize("name", ["cfg3", "cfg4"])
+def test_full_size_properties(name):
+    B, D, C = CONFIGS[name]
+    head, x, y, w = _make(B, D, C, False)
+    xg = x.clone().requires_grad_(True)
+    loss = head.forward_loss(xg, y)
+    loss.backward()
+    dx1, dw1 = xg.grad.clone(), head.weight.grad.clone()
+    lse, zt = head.aux["lse"].clone(), head.aux["target_logit"].clone()
+    # cross-entropy identities
+    assert (lse >= zt).all()
+    assert float((lse.double() - zt.double()).mean()) == pytest.approx(loss.item(), rel=1e-5)
+    # F.normalize backward: gradient rows orthogonal to their input rows (relative to the two norms)
+    ox = (x * dx1).sum(1).abs() / (x.norm(dim=1) * dx1.norm(dim=1) + 1e-30)
+    assert float(ox.max()) < 1e-3
+    nz = dw1.norm(dim=1) > 0
+    ow = ((w * dw1).sum(1).abs() / (w.norm(dim=1) * dw1.norm(dim=1) + 1e-30))[nz]
+    assert float(ow.max()) < 2e-2 and float(ow.mean()) < 2e-3   # projection uses bf16 cosines: ~2^-9 relative
+    # linearity in the upstream gradient
+    head.weight.grad = None
+    xg2 = x.clone().requires_grad_(True)
+    (head.forward_loss(xg2, y) * -3.0).backward()
+    assert _cos(xg2.grad, -dx1) > 0.99999 and _cos(head.weight.grad, -dw1) > 0.99999
+    assert float(xg2.grad.norm()) == pytest.approx(3.0 * float(dx1.norm()), rel=1e-3)
+    # shards merged = unsharded
+    eng = CudaEngine()
+    recs = []
+    for r in range(4):
+        lo, hi = shard_bounds(C, 4, r)
+        cfg = {"s": 30.0, "m": 0.5, "easy_margin": False, "class_offset": lo, "chunk_classes": 9472}
+        stats, _ = eng.shard_forward(x, w[lo:hi].contiguous(), y, cfg)
+        recs.append(stats)
+    lse4, zt4, loss4 = eng.merge_loss(torch.stack(recs).contiguous(), 4, B)
+    torch.testing.assert_close(lse4, lse, rtol=1e-5, atol=1e-4)
+    torch.testing.assert_close(zt4, zt, rtol=0, atol=0)
+    assert loss4.item() == pytest.approx(loss.item(), rel=1e-5)
+    _lib.check(_lib.lib().arcb_check_watchdog(torch.cuda.current_stream().cuda_stream))

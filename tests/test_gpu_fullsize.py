@@ -94,7 +94,7 @@ def test_full_size_properties(name):
     xg2 = x.clone().requires_grad_(True)
     (head.forward_loss(xg2, y) * -3.0).backward()
     assert _cos(xg2.grad, -dx1) > 0.99999 and _cos(head.weight.grad, -dw1) > 0.99999
-    assert float(xg2.grad.norm()) == pytest.approx(3.0 * float(dx1.norm()), rel=1e-3)
+    assert float(xg2.grad.norm()) == pytest.approx(3.0 * float(dx1.norm()), rel=5e-3)  # bf16 rounding of G differs with the scale
     # shards merged = unsharded
     eng = CudaEngine()
     recs = []

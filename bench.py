@@ -145,19 +145,32 @@ def cpu_port_rate(B_rows, D, C, easy, steps, warmup, threads):
     return B_rows / dt, dt
 
 
+def size_cpu_sample(args, threads, seconds_per_step):
+    """Rows of the batch the CPU port can process in ~seconds_per_step.
+
+    One CPU step costs a + b * rows (a: normalising / differentiating the full [C, D] weight, b: the B x C
+    passes), so two probing steps give the model and the sample is sized from it (never above the batch)."""
+    r1, r2 = 16, 48
+    _, t1 = cpu_port_rate(r1, args.dim, args.classes, args.easy_margin, 1, 0, threads)
+    _, t2 = cpu_port_rate(r2, args.dim, args.classes, args.easy_margin, 1, 0, threads)
+    b = max((t2 - t1) / (r2 - r1), 1e-6)
+    a = max(t1 - b * r1, 0.0)
+    rows = int((seconds_per_step - a) / b) if seconds_per_step > a else r1
+    return max(r1, min(args.batch, rows)), a, b
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # the CPU arm runs once, on rank 0
     threads = os.cpu_count() or 1
-    rows = args.cpu_sample_rows or 16
-    # one probing step sizes the sample so that K + W steps end within a few minutes
-    _, dt = cpu_port_rate(rows, args.dim, args.classes, args.easy_margin, 1, 0, threads)
-    budget = 150.0 / max(1, args.steps + args.warmup)
-    if not args.cpu_sample_rows and dt < budget / 2:
-        rows = int(min(args.batch, max(16, rows * (budget / 2) / dt)))
+    if args.cpu_sample_rows:
+        rows = args.cpu_sample_rows
+    else:  # K + W steps (plus the two probes) should end within ~2.5 minutes
+        rows, _, _ = size_cpu_sample(args, threads, 140.0 / max(1, args.steps + args.warmup))
     rate, dt = cpu_port_rate(rows, args.dim, args.classes, args.easy_margin, args.steps, args.warmup, threads)
-    sample = f"{rows} of {args.batch} batch rows per step, full C={args.classes}, D={args.dim}; torch-CPU fp32 port of the reference head (oracle.TorchPort)"
+    sample = (f"{rows} of {args.batch} batch rows per step, full C={args.classes}, D={args.dim}; torch-CPU fp32 port of "
+              f"the reference head (oracle.TorchPort), {dt:.2f} s/step")
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
@@ -320,7 +333,7 @@ def run_b200(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            rows = args.cpu_sample_rows or 32
+            rows = args.cpu_sample_rows or min(B, 256)  # ~10-20 s of CPU work in total
             try:
                 rate, dt = cpu_port_rate(rows, D, C, args.easy_margin, 2, 1, threads)
                 line["cpu_baseline"] = {

@@ -20,6 +20,8 @@
 // kernel with different epilogues.
 #pragma once
 
+#include <stdlib.h>
+
 #include "ptx_sm100.cuh"
 
 namespace arcb {
@@ -35,6 +37,7 @@ struct GemmSched {
   int k_splits;
   int kb_total;      // number of kBK-blocks over the whole K extent
   int kb_per_split;  // ceil(kb_total / k_splits)
+  int debug_split_b; // experiment switch (ARCB_DEBUG_SPLIT_B): load a K-major B tile as four boxes
 };
 
 struct TileCoord {
@@ -128,7 +131,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               tma_load_2d(sa + j * (kBK * 128), &tmA, &full[stage], tc.m_blk * kBM + j * 64, kb * kBK);
           }
           if constexpr (!B_MN) {
-            tma_load_2d(sb, &tmB, &full[stage], kb * kBK, tc.n_blk * BN);
+            if (sc.debug_split_b) {  // experiment: same bytes as four 64-row boxes (needs a 64-row tensor-map box)
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_2d(sb + j * (64 * 128), &tmB, &full[stage], kb * kBK, tc.n_blk * BN + j * 64);
+            } else {
+              tma_load_2d(sb, &tmB, &full[stage], kb * kBK, tc.n_blk * BN);
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
@@ -251,6 +260,24 @@ inline bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType 
   return r == CUDA_SUCCESS;
 }
 
+// MN-major bf16 operand stored row-major as [k_rows, mn_extent] (mn contiguous, mn_extent % 64 == 0) seen as the
+// rank-3 tensor {64 elements, k_rows, mn_extent / 64 blocks}: ONE bulk copy of box {64, 64, nblk} lands in shared
+// memory as nblk consecutive [64 k-rows x 128 B] swizzled blocks -- the canonical MN-major SWIZZLE_128B layout.
+inline bool make_tmap_mn3(CUtensorMap* tm, const void* base, uint64_t mn_extent, uint64_t k_rows, uint64_t pitch_bytes,
+                          uint32_t nblk) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return false;
+  if ((reinterpret_cast<uintptr_t>(base) & 15u) || (pitch_bytes & 15u) || (mn_extent % 64)) return false;
+  cuuint64_t dims[3] = {64, k_rows, mn_extent / 64};
+  cuuint64_t strides[2] = {pitch_bytes, 128};
+  cuuint32_t box[3] = {64, kBK, nblk};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
 // Operand description for the launcher: a bf16 matrix in global memory.
 //   K-major : stored [mn_extent rows, k_extent cols]   (k contiguous)
 //   MN-major: stored [k_extent rows, mn_extent cols]   (m / n contiguous)
@@ -293,12 +320,18 @@ inline cudaError_t launch_gemm(const Operand& a, const Operand& b, const CUtenso
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
   CUtensorMap tmA, tmB, tmC;
   if (!make_operand_tmap<A_MN>(&tmA, a, kBM)) return cudaErrorInvalidValue;
-  if (!make_operand_tmap<B_MN>(&tmB, b, BN)) return cudaErrorInvalidValue;
+  static int dbg_split = -1;
+  if (dbg_split < 0) {
+    const char* e = getenv("ARCB_DEBUG_SPLIT_B");
+    dbg_split = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (!make_operand_tmap<B_MN>(&tmB, b, (dbg_split && !B_MN) ? 64 : BN)) return cudaErrorInvalidValue;
   if (tmC_opt) tmC = *tmC_opt; else tmC = tmA;
   GemmSched sc;
   sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
   sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
   sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
+  sc.debug_split_b = dbg_split;
   if (split_k < 1) split_k = 1;
   if (split_k > sc.kb_total) split_k = sc.kb_total;
   sc.kb_per_split = (sc.kb_total + split_k - 1) / split_k;

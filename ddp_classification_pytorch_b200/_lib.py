@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_PKG_DIR, "libarcface_b200.so")
 _SRC = os.path.join(_PKG_DIR, "csrc", "arcface_b200.cu")
 _HDRS = [
     os.path.join(_PKG_DIR, "csrc", n)
-    for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh")
+    for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "gemm2_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh")
 ] + [os.path.join(_ROOT, "include", "arcface_b200.h")]
 
 NVCC_FLAGS = [
@@ -31,7 +31,7 @@ EXPORTED = [
     "arcb_version", "arcb_last_error", "arcb_check_watchdog", "arcb_l2norm_rows", "arcb_l2norm_rows_bwd",
     "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
-    "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3",
+    "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3", "arcb_set_pair_mode",
 ]
 
 KERNEL_KINDS = [
@@ -107,6 +107,8 @@ def _declare(lib):
     lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
     lib.arcb_shard_backward.restype = i32
     lib.arcb_shard_backward.argtypes = [i64, i64, i64, f32, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp]
+    lib.arcb_set_pair_mode.restype = i32
+    lib.arcb_set_pair_mode.argtypes = [i32]
     lib.arcb_set_backward_mode.restype = i32
     lib.arcb_set_backward_mode.argtypes = [i32]
     lib.arcb_launch_count.restype = i64

@@ -17,6 +17,7 @@
 
 #include "bwd_persistent.cuh"
 #include "epilogues.cuh"
+#include "gemm2_sm100.cuh"
 #include "gemm_sm100.cuh"
 #include "rowwise.cuh"
 
@@ -194,7 +195,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
 }
 
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
-template <bool EXT>
+template <bool EXT, bool PAIR>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
                           int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st) {
   const int64_t B = W.B, Cs = W.Cs, D = W.D;
@@ -205,7 +206,8 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   pl.Cs = (int)Cs; pl.B = (int)B; pl.Bp = (int)W.Bp; pl.D = (int)D; pl.Dp = (int)W.Dp;
   pl.g_tiles_n = (int)(W.Bp / kPBN);
   pl.g_kb = (int)(W.Dp / kBK);
-  pl.x_tiles_m = (int)((B + kBM - 1) / kBM);
+  pl.tile_rows = PAIR ? 2 * kBM : kBM;
+  pl.x_tiles_m = (int)((B + pl.tile_rows - 1) / pl.tile_rows);
   pl.x_tiles_n = (int)((D + kPBN - 1) / kPBN);
   pl.w_tiles_n = pl.x_tiles_n;
   pl.w_kb = (int)((B + kBK - 1) / kBK);
@@ -214,10 +216,21 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   {
     const int kbt = (int)((chunk_rows + kBK - 1) / kBK);
     const int tiles_mn = pl.x_tiles_m * pl.x_tiles_n;
-    int want_splits = (device_sm_count() + tiles_mn - 1) / tiles_mn;
+    const int groups = device_sm_count() / (PAIR ? 2 : 1);  // CTAs or CTA pairs working in parallel
+    // enough class slices that a chunk yields a few dozen dX tiles, but not more than 4: every extra slice is
+    // another 128 KB of fp32 reduce-add traffic per tile column (measured best on B200: 4, see profiles/)
+    int want_splits = (groups + tiles_mn - 1) / tiles_mn;
+    if (want_splits > 4) want_splits = 4;
+    {
+      static int xs = -1;  // ARCB_X_SPLITS: override the number of class slices per dX tile (tuning aid)
+      if (xs < 0) {
+        const char* e = getenv("ARCB_X_SPLITS");
+        xs = e ? atoi(e) : 0;
+      }
+      if (xs > 0) want_splits = xs;
+    }
     int per = (kbt + want_splits - 1) / want_splits;
     if (per < 4) per = 4;
-    if (per > pl.w_kb && pl.w_kb >= 4) per = pl.w_kb;
     pl.x_kb_per_split = per;
   }
   pl.g_done = W.counters;
@@ -237,12 +250,13 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   bool ok = true;
   ok = ok && make_tmap_2d(&tmWhatK, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, kBK, kBM);
-  ok = ok && make_tmap_2d(&tmXhatK, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, kBK, kPBN);
+  constexpr int kBRows = PAIR ? kPBN / 2 : kPBN;  // rows / columns of the B tile one CTA stages
+  ok = ok && make_tmap_2d(&tmXhatK, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, kBK, kBRows);
   ok = ok && make_tmap_2d(&tmGtSt, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, 64, kBM);
-  ok = ok && make_tmap_2d(&tmGtMN, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, 64, kBK);
-  ok = ok && make_tmap_2d(&tmWhatMN, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, 64, kBK);
+  ok = ok && make_tmap_mn3(&tmGtMN, gt, W.Bp, nbuf * chunk_rows, W.Bp * 2, kBM / 64);
+  ok = ok && make_tmap_mn3(&tmWhatMN, W.what, W.Dp, Cs, W.Dp * 2, kBRows / 64);
   ok = ok && make_tmap_2d(&tmGtK, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, kBK, kBM);
-  ok = ok && make_tmap_2d(&tmXhatMN, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, 64, kBK);
+  ok = ok && make_tmap_mn3(&tmXhatMN, W.xhat, W.Dp, B, W.Dp * 2, kBRows / 64);
   ok = ok && make_tmap_2d(&tmDx, dxhat, f32, 4, D, B, W.Dp * 4, 32, kBM);
   if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the persistent backward could not be encoded");
   const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
@@ -254,7 +268,8 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ar.cos_t = W.cos_t; ar.tproj = W.tproj; ar.s2 = s * kLog2e; ar.grad_out = grad_logits; ar.ldgo = ldgl;
   ar.s_ext = s; ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.dw_tma = dw_tma ? 1 : 0;
 
-  auto kern = bwd_persistent_kernel<EXT>;
+  auto kern = bwd_persistent_kernel<EXT, PAIR>;
+  constexpr int kPSmemTotal = PCfg<PAIR>::kSmemTotal;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -265,18 +280,22 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   }
   long long total_items = 0;
   for (int k = 0; k < pl.n_chunks; ++k) total_items += plan_nG(pl, k) + plan_nX(pl, k) + plan_nW(pl, k);
-  int grid = device_sm_count();
-  if (grid > total_items) grid = static_cast<int>(total_items);
+  int groups = device_sm_count() / (PAIR ? 2 : 1);
+  if (groups > total_items) groups = static_cast<int>(total_items);
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
+  cfg.gridDim = dim3(groups * (PAIR ? 2 : 1));
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = kPSmemTotal;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: they wait on one another
   attr[0].val.cooperative = 1;
+  attr[1].id = cudaLaunchAttributeClusterDimension;  // PAIR: the two CTAs of a tile share a TPC
+  attr[1].val.clusterDim.x = 2;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = PAIR ? 2 : 1;
   LaunchScope ls(ARCB_K_BWD_PERSISTENT, st);
   ARCB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw, pl,
                                ar));
@@ -308,6 +327,21 @@ int static_ws_address(void** out) {
   *out = addr[dev];
   return ARCB_OK;
 }
+
+// CTA pairs (cta_group::2): 0 = nowhere, 1 = persistent backward only (default: measured best), 2 = every GEMM.
+// -1 = not yet read from the environment (ARCB_PAIR).
+std::atomic<int> g_pair_mode{-1};
+int pair_mode() {
+  int mode = g_pair_mode.load(std::memory_order_relaxed);
+  if (mode < 0) {
+    const char* e = getenv("ARCB_PAIR");
+    mode = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+    g_pair_mode.store(mode, std::memory_order_relaxed);
+  }
+  return mode;
+}
+bool use_pair_gemm() { return pair_mode() == 2; }      // forward / unit-test GEMMs
+bool use_pair_backward() { return pair_mode() >= 1; }  // persistent backward
 
 std::atomic<int> g_bwd_mode{-1};  // -1: from the environment (default persistent), 0: per-chunk launches, 1: persistent
 bool use_persistent_backward() {
@@ -341,6 +375,12 @@ int arcb_check_watchdog(void* stream) {
 }
 
 int64_t arcb_padded_dim(int64_t D) { return round_up(D, 64); }
+
+int arcb_set_pair_mode(int mode) {
+  if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "pair mode must be 0, 1 or 2");
+  g_pair_mode.store(mode, std::memory_order_relaxed);
+  return ARCB_OK;
+}
 
 int arcb_set_backward_mode(int persistent) {
   g_bwd_mode.store(persistent ? 1 : 0, std::memory_order_relaxed);
@@ -412,6 +452,17 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e;
   LaunchScope ls(ARCB_K_GEMM_TEST, st);
+  if (use_pair_gemm()) {
+    // an MN-major operand is addressed in whole 64-element blocks: its (zero padded) leading dimension is the extent
+    if ((a_mn && (lda % 64 || lda < M)) || (b_mn && (ldb % 64 || ldb < N)))
+      return fail(ARCB_ERR_INVALID, "pair GEMM: an MN-major operand needs a leading dimension that is a multiple of 64");
+    if (a_mn) a.mn_extent = lda;
+    if (b_mn) b.mn_extent = ldb;
+    if (!a_mn && !b_mn) e = launch_gemm_pair<EpiStore, 256, 6, false, false>(a, b, nullptr, M, N, K, split_k, ep, st);
+    else if (a_mn && !b_mn) e = launch_gemm_pair<EpiStore, 256, 6, true, false>(a, b, nullptr, M, N, K, split_k, ep, st);
+    else if (!a_mn && b_mn) e = launch_gemm_pair<EpiStore, 256, 6, false, true>(a, b, nullptr, M, N, K, split_k, ep, st);
+    else e = launch_gemm_pair<EpiStore, 256, 6, true, true>(a, b, nullptr, M, N, K, split_k, ep, st);
+  } else
   if (!a_mn && !b_mn) e = launch_gemm<EpiStore, 256, 4, false, false>(a, b, nullptr, M, N, K, split_k, ep, st);
   else if (a_mn && !b_mn) e = launch_gemm<EpiStore, 256, 4, true, false>(a, b, nullptr, M, N, K, split_k, ep, st);
   else if (!a_mn && b_mn) e = launch_gemm<EpiStore, 256, 4, false, true>(a, b, nullptr, M, N, K, split_k, ep, st);
@@ -448,7 +499,8 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
       const char* e3 = getenv("ARCB_FWD_STAGES");
       fwd_stages = (e3 && e3[0] == '3') ? 3 : 4;
     }
-    if (fwd_stages == 3) e = launch_gemm<EpiFwdStats, kBNTile, 3, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    if (use_pair_gemm()) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    else if (fwd_stages == 3) e = launch_gemm<EpiFwdStats, kBNTile, 3, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
     else e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
@@ -582,10 +634,17 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       nbuf = 2;
       pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
     }
+    if (use_pair_backward()) {  // a pair's tile has 256 rows: chunks (= scratch buffers) must be whole tiles
+      int64_t pc2 = pchunk / 256 * 256;
+      if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
+      if (pc2 >= 256)
+        return ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
+                   : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+    }
     if (pchunk >= 128) {
       if (pchunk > round_up(Cs, 128)) pchunk = round_up(Cs, 128);
-      return ext ? launch_bwd_persistent<true>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st)
-                 : launch_bwd_persistent<false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st);
+      return ext ? launch_bwd_persistent<true, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st)
+                 : launch_bwd_persistent<false, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st);
     }
   }
 

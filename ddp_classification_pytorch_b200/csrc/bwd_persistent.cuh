@@ -24,6 +24,14 @@
 // Shared memory: 4 operand stages of 48 KB (the L2 -> SM latency needs that much in flight), and
 // only 34 KB for the epilogues: one 16 KB slot per epilogue warpgroup -- a [128 x 64] bf16 box of
 // G^T, or a [128 x 32] fp32 chunk of dX / dW -- plus the staged log-sum-exps / labels.
+//
+// Two builds of the same kernel (template parameter PAIR):
+//   PAIR = false  one CTA per 128 x 256 tile (cta_group::1), 4 stages of 48 KB
+//   PAIR = true   a cluster of two CTAs per 256 x 256 tile (cta_group::2, see gemm2_sm100.cuh): each CTA
+//                 stages its own 128 rows of A and half of B, 6 stages of 32 KB; the backward tiles are
+//                 shared-memory-bandwidth bound (operand traffic + epilogue staging), and the pair cuts the
+//                 operand traffic per SM by a third.  Tiles, counters and epilogues are per CTA as before;
+//                 only the leader issues MMAs.
 #pragma once
 
 #include "epilogues.cuh"
@@ -31,26 +39,33 @@
 namespace arcb {
 
 constexpr int kPBN = 256;
-constexpr int kPStages = 4;
 constexpr int kPABytes = kBM * kBK * 2;
-constexpr int kPStageBytes = kPABytes + kPBN * kBK * 2;  // 48 KB
+template <bool PAIR>
+struct PCfg {
+  static constexpr int kStages = PAIR ? 6 : 4;
+  static constexpr int kBBytes = (PAIR ? kPBN / 2 : kPBN) * kBK * 2;
+  static constexpr int kStageBytes = kPABytes + kBBytes;  // 32 KB / 48 KB
+  static constexpr int kNumBars = 2 * kStages + 4 + 4;    // + slot_full[2], slot_free[2]
+  static constexpr int kBarOff = kStages * kStageBytes + (2 * kBM * 128 + 256 * 8);
+  static constexpr int kSmemTotal = kBarOff + kNumBars * 8 + 16;  // no slack: the dynamic smem base is 1024 B aligned
+  static constexpr int kCtas = PAIR ? 2 : 1;              // CTAs that work on one tile
+};
 constexpr int kPSlotBytes = kBM * 128;                   // 16 KB: [128 rows x 128 B], one per epilogue warpgroup
 constexpr int kPRowsOff = 2 * kPSlotBytes;               // staged lse2 / labels: 2 warpgroups x 128 x (4 + 4) B
 constexpr int kPEpiSmem = kPRowsOff + 256 * 8;
-constexpr int kPNumBars = 2 * kPStages + 4 + 4;          // + slot_full[2], slot_free[2]
-constexpr int kPBarOff = kPStages * kPStageBytes + kPEpiSmem;
-constexpr int kPSmemTotal = kPBarOff + kPNumBars * 8 + 16;  // no slack: the dynamic smem base is 1024 B aligned
-static_assert(kPSmemTotal <= 232448, "persistent backward kernel exceeds the shared memory budget");
+static_assert(PCfg<false>::kSmemTotal <= 232448 && PCfg<true>::kSmemTotal <= 232448,
+              "persistent backward kernel exceeds the shared memory budget");
 
 enum : int { kItemG = 0, kItemX = 1, kItemW = 2 };
 
 struct BwdPlan {
   int n_chunks, chunk_rows;  // chunk_rows % 128 == 0
+  int tile_rows;             // accumulator rows of one tile: 128 (one CTA) or 256 (CTA pair)
   int nbuf;                  // scratch buffers of chunk_rows rows each (2 or 3); chunk k uses buffer k % nbuf
   int Cs, B, Bp, D, Dp;
   int g_tiles_n;             // Bp / 256
   int g_kb;                  // Dp / 64
-  int x_tiles_m, x_tiles_n;  // ceil(B / 128), ceil(D / 256)
+  int x_tiles_m, x_tiles_n;  // ceil(B / tile_rows), ceil(D / 256)
   int x_kb_per_split;        // 64-class blocks per X tile
   int w_tiles_n, w_kb;       // ceil(D / 256), ceil(B / 64)
   unsigned int* g_done;      // [n_chunks], zeroed before the launch
@@ -84,7 +99,9 @@ __host__ __device__ inline int plan_rows(const BwdPlan& pl, int k) {
   const int rest = pl.Cs - k * pl.chunk_rows;
   return rest < pl.chunk_rows ? rest : pl.chunk_rows;
 }
-__host__ __device__ inline int plan_gm(const BwdPlan& pl, int k) { return (plan_rows(pl, k) + kBM - 1) / kBM; }
+__host__ __device__ inline int plan_gm(const BwdPlan& pl, int k) {
+  return (plan_rows(pl, k) + pl.tile_rows - 1) / pl.tile_rows;
+}
 __host__ __device__ inline int plan_nG(const BwdPlan& pl, int k) { return plan_gm(pl, k) * pl.g_tiles_n; }
 __host__ __device__ inline int plan_xsplits(const BwdPlan& pl, int k) {
   const int kbt = (plan_rows(pl, k) + kBK - 1) / kBK;
@@ -116,14 +133,16 @@ __device__ __forceinline__ int phase_items(const BwdPlan& pl, int p) {
   return is_g ? plan_nG(pl, k) : plan_nX(pl, k) + plan_nW(pl, k);
 }
 
-// Every role of a CTA walks the same sub-sequence of the global list: tiles blockIdx.x, +gridDim.x, ...
+// Every role of a CTA (or CTA pair) walks the same sub-sequence of the global list: tiles first, first + step, ...
 struct ItemWalker {
   int phase, phase_begin, phase_size, next_it;
-  __device__ void init(const BwdPlan& pl) {
+  int stride;
+  __device__ void init(const BwdPlan& pl, int first, int step) {
     phase = 0;
     phase_begin = 0;
     phase_size = phase_items(pl, 0);
-    next_it = blockIdx.x;
+    next_it = first;
+    stride = step;
   }
   __device__ bool next(const BwdPlan& pl, Item& it) {
     const int nph = 2 * pl.n_chunks;
@@ -165,7 +184,7 @@ struct ItemWalker {
         it.kb1 = pl.w_kb;
       }
     }
-    next_it += gridDim.x;
+    next_it += stride;
     return true;
   }
 };
@@ -197,7 +216,40 @@ __device__ __forceinline__ void wait_counter(const unsigned int* ctr, unsigned i
   }
 }
 
-template <bool EXT>
+// TMEM stage drained: in PAIR mode both CTAs' epilogue warps report to the leader, whose MMA issuer waits
+template <bool PAIR>
+__device__ __forceinline__ void arrive_tempty(uint64_t* bar) {
+  if constexpr (PAIR) mbar_arrive_cluster(mapa_u32(smem_u32(bar), 0)); else mbar_arrive(bar);
+}
+
+// operand loads: `bar_addr` is the shared::cluster address of the full barrier (the pair leader's in PAIR mode)
+template <bool PAIR>
+__device__ __forceinline__ void ld2(void* dst, const CUtensorMap* tm, uint32_t bar_addr, int c0, int c1, uint64_t pol) {
+  if constexpr (PAIR) {
+    tma_load_2d_pair(dst, tm, bar_addr, c0, c1, pol);
+  } else {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_addr), "r"(c0), "r"(c1), "l"(pol)
+        : "memory");
+  }
+}
+template <bool PAIR>
+__device__ __forceinline__ void ld3(void* dst, const CUtensorMap* tm, uint32_t bar_addr, int c0, int c1, int c2,
+                                    uint64_t pol) {
+  if constexpr (PAIR) {
+    tma_load_3d_pair(dst, tm, bar_addr, c0, c1, c2, pol);
+  } else {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar_addr), "r"(c0), "r"(c1), "r"(c2), "l"(pol)
+        : "memory");
+  }
+}
+
+template <bool EXT, bool PAIR>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [Cs, Dp]   box 64 x 128  (A of G)
                       const __grid_constant__ CUtensorMap tmXhatK,   // x_hat [B, Dp]    box 64 x 256  (B of G)
@@ -214,15 +266,22 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     if (threadIdx.x == 0 && atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) g_wait_timeout[1] = 0xa11u;
     return;
   }
+  using C = PCfg<PAIR>;
+  constexpr int kPStages = C::kStages;
+  constexpr int kPStageBytes = C::kStageBytes;
   uint8_t* epi_smem = smem + kPStages * kPStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kPBarOff);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kBarOff);
   uint64_t* full = bars;
   uint64_t* empty = bars + kPStages;
   uint64_t* tfull = bars + 2 * kPStages;
   uint64_t* tempty = bars + 2 * kPStages + 2;
   uint64_t* slot_full = bars + 2 * kPStages + 4;  // [2] epilogue warpgroup -> its store issuer: box is in smem
   uint64_t* slot_free = bars + 2 * kPStages + 6;  // [2] store issuer -> warpgroup: box has been read
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kPNumBars);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + C::kNumBars);
+  const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;   // position inside the CTA pair
+  const bool leader = rank == 0;
+  const int walk_first = static_cast<int>(blockIdx.x) / C::kCtas;   // tile group of this CTA
+  const int walk_step = static_cast<int>(gridDim.x) / C::kCtas;
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = static_cast<int>(lane_id());
@@ -240,12 +299,12 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kPStages; ++i) {
-      mbar_init(&full[i], 1);
+      mbar_init(&full[i], C::kCtas);  // pair: leader producer (+tx bytes of both CTAs) and follower producer
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], kEpiThreads / 32);
+      mbar_init(&tempty[i], C::kCtas * (kEpiThreads / 32));  // pair: both CTAs' epilogue warps, on the leader
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&slot_full[i], kWgThreads / 32);
@@ -254,11 +313,16 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, 2 * kPBN);
-    tmem_relinquish();
+    if constexpr (PAIR) {
+      tmem_alloc_pair(tmem_slot, 2 * kPBN);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_slot, 2 * kPBN);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -266,44 +330,41 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     if (lane == 0) {
       // ------------------------------ TMA producer ------------------------------
       ItemWalker w;
-      w.init(pl);
+      w.init(pl, walk_first, walk_step);
       Item it;
       int stage = 0;
       uint32_t phase = 0;
       while (w.next(pl, it)) {
         if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
         if (it.kind != kItemG && (pl.kind_mask & 1)) {  // G^T of this chunk must be complete and visible
-          wait_counter(pl.g_done + it.chunk, 2u * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
+          wait_counter(pl.g_done + it.chunk, 2u * C::kCtas * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
           fence_proxy_async_all();
         }
+        const int mblk = it.m_blk * C::kCtas + rank;            // this CTA's 128-row block of the tile
         const int c0 = it.chunk * pl.chunk_rows;                // first class of the chunk in the shard
         const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;  // first row of the chunk's scratch buffer
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
-          mbar_arrive_expect_tx(&full[stage], kPStageBytes);
+          // pair: both CTAs' bytes are counted on the leader's barrier (count 2: leader +tx, follower plain)
+          const uint32_t full_addr = PAIR ? mapa_u32(smem_u32(&full[stage]), 0) : smem_u32(&full[stage]);
+          if (leader) mbar_arrive_expect_tx(&full[stage], C::kCtas * kPStageBytes);
           uint8_t* sa = smem + stage * kPStageBytes;
           uint8_t* sb = sa + kPABytes;
+          const int half = rank * (kPBN / 2);  // this CTA's half of the B tile (pair), else 0
           if (it.kind == kItemG) {
             // w_hat rows are read again by X(k) and by the dW epilogue, x_hat by every tile: keep both in L2
-            tma_load_2d_hint(sa, &tmWhatK, &full[stage], kb * kBK, c0 + it.m_blk * kBM, kEvictLast);
-            tma_load_2d_hint(sb, &tmXhatK, &full[stage], kb * kBK, it.n_blk * kPBN, kEvictLast);
+            ld2<PAIR>(sa, &tmWhatK, full_addr, kb * kBK, c0 + mblk * kBM, kEvictLast);
+            ld2<PAIR>(sb, &tmXhatK, full_addr, kb * kBK, it.n_blk * kPBN + half, kEvictLast);
           } else if (it.kind == kItemX) {
-#pragma unroll
-            for (int j = 0; j < kBM / 64; ++j)
-              tma_load_2d_hint(sa + j * (kBK * 128), &tmGtMN, &full[stage], it.m_blk * kBM + j * 64,
-                               buf_row + kb * kBK, kEvictLast);  // W(k) still has to read it
-#pragma unroll
-            for (int j = 0; j < kPBN / 64; ++j)
-              tma_load_2d_hint(sb + j * (kBK * 128), &tmWhatMN, &full[stage], it.n_blk * kPBN + j * 64, c0 + kb * kBK,
-                               kEvictNormal);
+            // A = G (class index slowest): 2 blocks of 64 samples; B = w_hat: blocks of 64 features; W(k) re-reads G^T
+            ld3<PAIR>(sa, &tmGtMN, full_addr, 0, buf_row + kb * kBK, mblk * (kBM / 64), kEvictLast);
+            ld3<PAIR>(sb, &tmWhatMN, full_addr, 0, c0 + kb * kBK, (it.n_blk * kPBN + half) / 64, kEvictNormal);
           } else {
             // last reader of this part of G^T: let it leave L2 first instead of being written back later
-            tma_load_2d_hint(sa, &tmGtK, &full[stage], kb * kBK, buf_row + it.m_blk * kBM, kEvictFirst);
-#pragma unroll
-            for (int j = 0; j < kPBN / 64; ++j)
-              tma_load_2d_hint(sb + j * (kBK * 128), &tmXhatMN, &full[stage], it.n_blk * kPBN + j * 64, kb * kBK,
-                               kEvictLast);
+            ld2<PAIR>(sa, &tmGtK, full_addr, kb * kBK, buf_row + mblk * kBM, kEvictFirst);
+            ld3<PAIR>(sb, &tmXhatMN, full_addr, 0, kb * kBK, (it.n_blk * kPBN + half) / 64, kEvictLast);
           }
+          if (PAIR && !leader) mbar_arrive_cluster(full_addr);
           if (++stage == kPStages) {
             stage = 0;
             phase ^= 1u;
@@ -312,10 +373,10 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ------------------------------ MMA issuer --------------------------------
+    if (lane == 0 && leader) {
+      // ------------------------------ MMA issuer (pair: leader only) --------------------------------
       ItemWalker w;
-      w.init(pl);
+      w.init(pl, walk_first, walk_step);
       Item it;
       int stage = 0;
       uint32_t phase = 0;
@@ -325,7 +386,12 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
         const bool a_mn = it.kind == kItemX;
         const bool b_mn = it.kind != kItemG;
-        const uint32_t idesc = make_idesc_bf16(kBM, kPBN, a_mn, b_mn);
+        const uint32_t idesc = make_idesc_bf16(C::kCtas * kBM, kPBN, a_mn, b_mn);
+        // descriptor of k-slice 0 at smem offset 0; per slice only the (16-byte granular) start address moves
+        const uint64_t da0 = a_mn ? make_smem_desc(0, kBK * 128, 1024) : make_smem_desc(0, 16, 1024);
+        const uint64_t db0 = b_mn ? make_smem_desc(0, kBK * 128, 1024) : make_smem_desc(0, 16, 1024);
+        const uint32_t a_step = a_mn ? (2048u >> 4) : (32u >> 4);
+        const uint32_t b_step = b_mn ? (2048u >> 4) : (32u >> 4);
         mbar_wait(&tempty[acc], acc_phase ^ 1u, 0x200u + acc);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kPBN);
@@ -333,22 +399,21 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
           mbar_wait(&full[stage], phase, 0x300u + stage);
           tc_fence_after();
           const uint32_t a_base = smem_u32(smem + stage * kPStageBytes);
-          const uint32_t b_base = a_base + kPABytes;
+          const uint64_t da = da0 + (a_base >> 4);
+          const uint64_t db = db0 + ((a_base + kPABytes) >> 4);
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {
-            const uint64_t da = a_mn ? make_smem_desc(a_base + k * 2048, kBK * 128, 1024)
-                                     : make_smem_desc(a_base + k * 32, 16, 1024);
-            const uint64_t db = b_mn ? make_smem_desc(b_base + k * 2048, kBK * 128, 1024)
-                                     : make_smem_desc(b_base + k * 32, 16, 1024);
-            tc_mma_bf16(tmem_d, da, db, idesc, (kb > it.kb0 || k > 0) ? 1u : 0u);
+            const uint32_t accum = (kb > it.kb0 || k > 0) ? 1u : 0u;
+            if constexpr (PAIR) tc_mma_bf16_pair(tmem_d, da + k * a_step, db + k * b_step, idesc, accum);
+            else tc_mma_bf16(tmem_d, da + k * a_step, db + k * b_step, idesc, accum);
           }
-          tc_commit(&empty[stage]);
+          if constexpr (PAIR) tc_commit_pair(&empty[stage], 0x3); else tc_commit(&empty[stage]);
           if (++stage == kPStages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        tc_commit(&tfull[acc]);
+        if constexpr (PAIR) tc_commit_pair(&tfull[acc], 0x3); else tc_commit(&tfull[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
@@ -359,20 +424,21 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       const int wg = 3 - warp;
       uint8_t* slot = epi_smem + wg * kPSlotBytes;
       ItemWalker w;
-      w.init(pl);
+      w.init(pl, walk_first, walk_step);
       Item it;
       uint32_t n_box = 0;  // boxes this issuer has sent so far (two per G tile)
       while (w.next(pl, it)) {
         if (it.kind != kItemG || it.kb0 >= it.kb1 || !(pl.kind_mask & 1)) continue;
         const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;
+        const int mblk = it.m_blk * C::kCtas + rank;
         for (int bx = 0; bx < 2; ++bx, ++n_box) {
           mbar_wait(&slot_full[wg], n_box & 1u, 0x600u + wg);
           if (bx == 0 && it.chunk >= pl.nbuf && (pl.kind_mask & 6) == 6) {  // the X / W tiles that last read this scratch buffer must be done
             const int kp = it.chunk - pl.nbuf;
-            wait_counter(pl.xw_done + kp, static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
+            wait_counter(pl.xw_done + kp, C::kCtas * static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
             fence_proxy_async_all();
           }
-          tma_store_2d_hint(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + it.m_blk * kBM, kEvictLast);
+          tma_store_2d_hint(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + mblk * kBM, kEvictLast);
           tma_store_commit();
           tma_store_wait_read0();
           mbar_arrive(&slot_free[wg]);  // the warpgroup may overwrite its slot
@@ -393,7 +459,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     float* lse_s = reinterpret_cast<float*>(epi_smem + kPRowsOff) + wg * 128;       // this warpgroup's 128 samples
     int* lbl_s = reinterpret_cast<int*>(epi_smem + kPRowsOff + 256 * 4) + wg * 128;
     ItemWalker w;
-    w.init(pl);
+    w.init(pl, walk_first, walk_step);
     Item it;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -430,7 +496,8 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       }
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * kPBN) + (static_cast<uint32_t>(quad * 32) << 16);
       TileCoord tc;
-      tc.m_blk = it.m_blk;
+      const int mblk = it.m_blk * C::kCtas + rank;  // this CTA's 128 accumulator rows of the tile
+      tc.m_blk = mblk;
       tc.n_blk = it.n_blk;
       tc.kb0 = it.kb0;
       tc.kb1 = it.kb1;
@@ -460,9 +527,9 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         if (!EXT) lse_s[wg_tid] = lse_v;
         lbl_s[wg_tid] = lbl_v;
         named_bar_sync(2 + wg, kWgThreads);
-        const int row_local = it.m_blk * kBM + row_in_tile;
+        const int row_local = mblk * kBM + row_in_tile;
         const int cls = c0 + row_local;
-        const int tile_cls0 = c0 + it.m_blk * kBM;
+        const int tile_cls0 = c0 + mblk * kBM;
         const bool row_ok = row_local < rows;
         float tsum = 0.f;
         const uint32_t srow = smem_u32(slot) + row_in_tile * 128;
@@ -500,7 +567,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
           fence_proxy_async_smem();  // box -> visible to the TMA engine
           __syncwarp();
           if (lane == 0) {
-            if (bx == 1) mbar_arrive(&tempty[acc]);
+            if (bx == 1) arrive_tempty<PAIR>(&tempty[acc]);
             mbar_arrive(&slot_full[wg]);
           }
         }
@@ -511,7 +578,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         EpiRedAdd::template consume<kPBN, 1>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[acc]);
+        if (lane == 0) arrive_tempty<PAIR>(&tempty[acc]);
       } else {
         EpiDW::Params p;
         p.dw = ar.dw;
@@ -526,7 +593,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         EpiDW::template consume<kPBN, 1>(p, ost, tc, tmDw, taddr, row_in_tile, epi_tid, epi_smem);
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[acc]);
+        if (lane == 0) arrive_tempty<PAIR>(&tempty[acc]);
       }
       prev_kind = it.kind;
       acc ^= 1;
@@ -536,10 +603,10 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();  // pair: the peer may still signal our barriers
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 2 * kPBN);
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, 2 * kPBN); else tmem_dealloc(tmem_base, 2 * kPBN);
   }
 }
 

@@ -132,6 +132,11 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
                         const float* target_logit, const float* grad_loss, const float* grad_logits, int64_t ldgl,
                         void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, void* stream);
 
+/* Where CTA pairs (cta_group::2: 256 x 256 tile per pair of SMs, B operand shared by the pair) are used:
+ * 0 = nowhere (one CTA per 128 x 256 tile), 1 (default) = persistent backward only, 2 = every GEMM.
+ * Same results in all modes; the switch exists for A/B measurements and tests. */
+int arcb_set_pair_mode(int mode);
+
 /* Backward schedule: 1 (default) = one persistent cooperative kernel per shard, 0 = one launch
  * per GEMM and class chunk.  Both produce the same gradients (A/B testing, profiling). */
 int arcb_set_backward_mode(int persistent);

@@ -14,9 +14,9 @@ def _run(M, N, K, a_mn, b_mn, split_k, seed=0):
     A = torch.randn(M, K, generator=g).to(dev).bfloat16()
     B = torch.randn(N, K, generator=g).to(dev).bfloat16()
     ref = A.float() @ B.float().t()
-    def pad8(t):  # leading dimension must be a multiple of 8 elements (16 bytes)
+    def pad8(t):  # leading dimension: multiple of 64 elements (covers the 16-byte rule and whole MN blocks)
         r, c = t.shape
-        cp = (c + 7) // 8 * 8
+        cp = (c + 63) // 64 * 64
         buf = torch.zeros(r, cp, dtype=t.dtype, device=dev)
         buf[:, :c] = t
         return buf

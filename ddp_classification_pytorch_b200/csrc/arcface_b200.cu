@@ -195,13 +195,22 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
 }
 
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
-template <bool EXT, bool PAIR>
+template <bool EXT, bool PAIR, bool TRACE = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
-                          int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st) {
+                          int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st,
+                          unsigned long long* trace = nullptr) {
   const int64_t B = W.B, Cs = W.Cs, D = W.D;
   BwdPlan pl;
   pl.chunk_rows = static_cast<int>(chunk_rows);
   pl.nbuf = nbuf;
+  {
+    static int lag = 0;  // ARCB_LAG: tuning aid; nbuf >= lag + 2 keeps buffer-reuse waits a phase away
+    if (!lag) {
+      const char* e = getenv("ARCB_LAG");
+      lag = (e && e[0] >= '1' && e[0] <= '4') ? e[0] - '0' : 2;
+    }
+    pl.lag = lag < nbuf ? lag : (nbuf > 1 ? nbuf - 1 : 1);
+  }
   pl.n_chunks = static_cast<int>((Cs + chunk_rows - 1) / chunk_rows);
   pl.Cs = (int)Cs; pl.B = (int)B; pl.Bp = (int)W.Bp; pl.D = (int)D; pl.Dp = (int)W.Dp;
   pl.g_tiles_n = (int)(W.Bp / kPBN);
@@ -267,8 +276,9 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ar.lse2 = W.lse2; ar.gscale = W.gscale; ar.lbl_local = W.lbl_local; ar.zt2 = W.zt2; ar.dphi = W.dphi;
   ar.cos_t = W.cos_t; ar.tproj = W.tproj; ar.s2 = s * kLog2e; ar.grad_out = grad_logits; ar.ldgo = ldgl;
   ar.s_ext = s; ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.dw_tma = dw_tma ? 1 : 0;
+  ar.trace = trace;
 
-  auto kern = bwd_persistent_kernel<EXT, PAIR>;
+  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE>;
   constexpr int kPSmemTotal = PCfg<PAIR>::kSmemTotal;
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -622,17 +632,35 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   ARCB_CUDA(cudaMemsetAsync(dxhat, 0, B * W.Dp * 4, st));
 
   if (use_persistent_backward()) {
-    // multi-buffered scratch: kScratchBufs buffers of `pchunk` classes each (two if it is small)
+    // multi-buffered scratch: 4 buffers of `pchunk` classes each (fewer if the scratch is small)
     static int want_bufs = 0;
     if (!want_bufs) {
       const char* e = getenv("ARCB_SCRATCH_BUFS");
-      want_bufs = (e && e[0] == '2') ? 2 : 3;
+      want_bufs = (e && e[0] >= '2' && e[0] <= '6') ? e[0] - '0' : 4;
     }
     int nbuf = want_bufs;
     int64_t pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
-    if (pchunk < 128) {
-      nbuf = 2;
+    while (pchunk < 256 && nbuf > 2) {
+      --nbuf;
       pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
+    }
+    // debug trace (ARCB_TRACE=1, fused path only): the last 1 MiB of the scratch receives per-tile clock stamps
+    static int want_trace = -1;
+    if (want_trace < 0) {
+      const char* e = getenv("ARCB_TRACE");
+      want_trace = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (want_trace && !ext && scratch_bytes > (4ll << 20)) {
+      const int64_t usable = scratch_bytes - (1ll << 20);
+      unsigned long long* trace = reinterpret_cast<unsigned long long*>(static_cast<char*>(scratch) + usable);
+      ARCB_CUDA(cudaMemsetAsync(trace, 0, 1ll << 20, st));
+      int64_t pc = usable / (W.Bp * 2) / nbuf / 256 * 256;
+      if (pc > round_up(Cs, 256)) pc = round_up(Cs, 256);
+      if (pc >= 256) {
+        if (use_pair_backward())
+          return launch_bwd_persistent<false, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, trace);
+        return launch_bwd_persistent<false, false, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, trace);
+      }
     }
     if (use_pair_backward()) {  // a pair's tile has 256 rows: chunks (= scratch buffers) must be whole tiles
       int64_t pc2 = pchunk / 256 * 256;

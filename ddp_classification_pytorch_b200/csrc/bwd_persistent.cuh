@@ -9,9 +9,8 @@
 //         fp32 bulk reduce-add)
 //   W(k)  dW[chunk, D] = inv_norm * (G^T[chunk, B] * x_hat[B, D] - t * w_hat)
 //
-// All CTAs walk ONE global tile list  G0, G1, XW0, G2, XW1, ..., G(n-1), XW(n-2), XW(n-1)
-// round-robin; the look-ahead of one G phase means a CTA that reaches XW(k) almost never has to
-// wait.  Dependencies are two arrays of global counters:
+// All CTAs walk ONE global tile list round-robin: phase p = the G tiles of chunk p interleaved with the
+// X / W tiles of chunk p - 2 (see ItemWalker).  Dependencies are two arrays of global counters:
 //   g_done[k]   half-tiles of G(k) whose stores have completed  -> gates the loads of X(k)/W(k)
 //   xw_done[k]  X/W tiles of chunk k that finished reading G^T  -> gates the stores of G(k+nbuf)
 // Every wait targets a tile that is EARLIER in the list and all CTAs are co-resident (cooperative
@@ -42,17 +41,19 @@ constexpr int kPBN = 256;
 constexpr int kPABytes = kBM * kBK * 2;
 template <bool PAIR>
 struct PCfg {
-  static constexpr int kStages = PAIR ? 6 : 4;
+  static constexpr int kStages = PAIR ? 5 : 4;
   static constexpr int kBBytes = (PAIR ? kPBN / 2 : kPBN) * kBK * 2;
   static constexpr int kStageBytes = kPABytes + kBBytes;  // 32 KB / 48 KB
-  static constexpr int kNumBars = 2 * kStages + 4 + 4;    // + slot_full[2], slot_free[2]
-  static constexpr int kBarOff = kStages * kStageBytes + (2 * kBM * 128 + 256 * 8);
+  // epilogue slots per warpgroup: with two, a warpgroup never waits inside a tile for the bulk store of its
+  // previous G^T box / dX / dW chunk to finish reading shared memory (the pair's smaller stages pay for it)
+  static constexpr int kBufs = PAIR ? 2 : 1;
+  static constexpr int kRowsOff = 2 * kBufs * kBM * 128;   // staged lse2 / labels behind the slots
+  static constexpr int kNumBars = 2 * kStages + 4 + 4 * kBufs;  // + slot_full / slot_free [2 warpgroups][kBufs]
+  static constexpr int kBarOff = kStages * kStageBytes + kRowsOff + 256 * 8;
   static constexpr int kSmemTotal = kBarOff + kNumBars * 8 + 16;  // no slack: the dynamic smem base is 1024 B aligned
   static constexpr int kCtas = PAIR ? 2 : 1;              // CTAs that work on one tile
 };
 constexpr int kPSlotBytes = kBM * 128;                   // 16 KB: [128 rows x 128 B], one per epilogue warpgroup
-constexpr int kPRowsOff = 2 * kPSlotBytes;               // staged lse2 / labels: 2 warpgroups x 128 x (4 + 4) B
-constexpr int kPEpiSmem = kPRowsOff + 256 * 8;
 static_assert(PCfg<false>::kSmemTotal <= 232448 && PCfg<true>::kSmemTotal <= 232448,
               "persistent backward kernel exceeds the shared memory budget");
 
@@ -61,6 +62,7 @@ enum : int { kItemG = 0, kItemX = 1, kItemW = 2 };
 struct BwdPlan {
   int n_chunks, chunk_rows;  // chunk_rows % 128 == 0
   int tile_rows;             // accumulator rows of one tile: 128 (one CTA) or 256 (CTA pair)
+  int lag;                   // phases between the G tiles of a chunk and its X / W tiles (default 2)
   int nbuf;                  // scratch buffers of chunk_rows rows each (2 or 3); chunk k uses buffer k % nbuf
   int Cs, B, Bp, D, Dp;
   int g_tiles_n;             // Bp / 256
@@ -89,7 +91,17 @@ struct BwdArgs {
   const __nv_bfloat16* what;
   const float* inv_nw;
   int dw_tma;
+  unsigned long long* trace;  // TRACE builds only: [8 CTAs][kTraceItems][kTraceWords] clock64 stamps
 };
+
+constexpr int kTraceItems = 1024;
+constexpr int kTraceWords = 12;
+template <bool TRACE>
+__device__ __forceinline__ unsigned long long* trace_slot(const BwdArgs& ar, int item_no) {
+  if constexpr (!TRACE) return nullptr;
+  if (!ar.trace || blockIdx.x >= 8 || item_no >= kTraceItems) return nullptr;
+  return ar.trace + (static_cast<size_t>(blockIdx.x) * kTraceItems + item_no) * kTraceWords;
+}
 
 struct Item {
   int kind, chunk, m_blk, n_blk, kb0, kb1;
@@ -112,25 +124,26 @@ __host__ __device__ inline int plan_nX(const BwdPlan& pl, int k) {
 }
 __host__ __device__ inline int plan_nW(const BwdPlan& pl, int k) { return plan_gm(pl, k) * pl.w_tiles_n; }
 
-// phase p of the global list -> (is it a G phase, which chunk)
-__device__ __forceinline__ void phase_kind(const BwdPlan& pl, int p, bool& is_g, int& k) {
-  if (p == 0) {
-    is_g = true;
-    k = 0;
-  } else if (p & 1) {
-    k = (p + 1) >> 1;
-    is_g = k < pl.n_chunks;
-    if (!is_g) k = pl.n_chunks - 1;
-  } else {
-    is_g = false;
-    k = (p >> 1) - 1;
-  }
+// The global list is a sequence of n_chunks + lag phases; phase p holds the G tiles of chunk p (if any) mixed
+// PROPORTIONALLY with the X / W tiles of chunk p - lag (if any), and X with W likewise.  Mixing matters: if all
+// CTAs reached the dW tiles together, the burst of fp32 dW stores (~3 TB/s) would saturate HBM writes and
+// stall those epilogues; spread over the whole phase the same bytes need ~0.7 TB/s.  With a lag of two phases
+// the G tiles an X / W tile depends on were all issued a full phase earlier (and, with 4 scratch buffers, so
+// were the X / W tiles whose buffer a G tile overwrites), so a CTA rarely waits on a counter.
+// (the lag is pl.lag, default 2)
+__device__ __forceinline__ int phase_nG(const BwdPlan& pl, int p) { return p < pl.n_chunks ? plan_nG(pl, p) : 0; }
+__device__ __forceinline__ int phase_nXW(const BwdPlan& pl, int p) {
+  return (p >= pl.lag && p - pl.lag < pl.n_chunks) ? plan_nX(pl, p - pl.lag) + plan_nW(pl, p - pl.lag) : 0;
 }
-__device__ __forceinline__ int phase_items(const BwdPlan& pl, int p) {
-  bool is_g;
-  int k;
-  phase_kind(pl, p, is_g, k);
-  return is_g ? plan_nG(pl, k) : plan_nX(pl, k) + plan_nW(pl, k);
+__device__ __forceinline__ int phase_items(const BwdPlan& pl, int p) { return phase_nG(pl, p) + phase_nXW(pl, p); }
+
+// j-th of `total` slots, of which `n_b` belong to stream B spread evenly: is slot j a B slot, and which one?
+__device__ __forceinline__ bool pick_b(int j, int n_b, int total, int& idx_b, int& idx_a) {
+  const int before = static_cast<int>((static_cast<long long>(j) * n_b) / total);
+  const int after = static_cast<int>((static_cast<long long>(j + 1) * n_b) / total);
+  idx_b = before;
+  idx_a = j - before;
+  return after > before;
 }
 
 // Every role of a CTA (or CTA pair) walks the same sub-sequence of the global list: tiles first, first + step, ...
@@ -145,41 +158,44 @@ struct ItemWalker {
     stride = step;
   }
   __device__ bool next(const BwdPlan& pl, Item& it) {
-    const int nph = 2 * pl.n_chunks;
+    const int nph = pl.n_chunks + pl.lag;
     while (phase < nph && next_it >= phase_begin + phase_size) {
       phase_begin += phase_size;
       ++phase;
       if (phase < nph) phase_size = phase_items(pl, phase);
     }
     if (phase >= nph) return false;
-    bool is_g;
-    int k;
-    phase_kind(pl, phase, is_g, k);
-    int j = next_it - phase_begin;
-    it.chunk = k;
-    const int gm = plan_gm(pl, k);
-    if (is_g) {
+    const int j = next_it - phase_begin;
+    const int n_xw = phase_nXW(pl, phase);
+    int i_xw, i_g;
+    if (!pick_b(j, n_xw, phase_size, i_xw, i_g)) {  // a G tile of chunk `phase`
+      const int k = phase;
+      const int gm = plan_gm(pl, k);
       it.kind = kItemG;
-      it.m_blk = j % gm;
-      it.n_blk = j / gm;
+      it.chunk = k;
+      it.m_blk = i_g % gm;
+      it.n_blk = i_g / gm;
       it.kb0 = 0;
       it.kb1 = pl.g_kb;
-    } else {
+    } else {  // an X or W tile of chunk `phase - lag`
+      const int k = phase - pl.lag;
+      const int gm = plan_gm(pl, k);
       const int nx = plan_nX(pl, k);
-      if (j < nx) {
+      it.chunk = k;
+      int i_x, i_w;
+      if (pick_b(i_xw, nx, n_xw, i_x, i_w)) {
         it.kind = kItemX;
-        it.m_blk = j % pl.x_tiles_m;
-        const int r = j / pl.x_tiles_m;
+        it.m_blk = i_x % pl.x_tiles_m;
+        const int r = i_x / pl.x_tiles_m;
         it.n_blk = r % pl.x_tiles_n;
         const int ks = r / pl.x_tiles_n;
         const int kbt = (plan_rows(pl, k) + kBK - 1) / kBK;
         it.kb0 = ks * pl.x_kb_per_split;
         it.kb1 = min(it.kb0 + pl.x_kb_per_split, kbt);
       } else {
-        j -= nx;
         it.kind = kItemW;
-        it.m_blk = j % gm;
-        it.n_blk = j / gm;
+        it.m_blk = i_w % gm;
+        it.n_blk = i_w / gm;
         it.kb0 = 0;
         it.kb1 = pl.w_kb;
       }
@@ -249,7 +265,7 @@ __device__ __forceinline__ void ld3(void* dst, const CUtensorMap* tm, uint32_t b
   }
 }
 
-template <bool EXT, bool PAIR>
+template <bool EXT, bool PAIR, bool TRACE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [Cs, Dp]   box 64 x 128  (A of G)
                       const __grid_constant__ CUtensorMap tmXhatK,   // x_hat [B, Dp]    box 64 x 256  (B of G)
@@ -275,8 +291,9 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   uint64_t* empty = bars + kPStages;
   uint64_t* tfull = bars + 2 * kPStages;
   uint64_t* tempty = bars + 2 * kPStages + 2;
-  uint64_t* slot_full = bars + 2 * kPStages + 4;  // [2] epilogue warpgroup -> its store issuer: box is in smem
-  uint64_t* slot_free = bars + 2 * kPStages + 6;  // [2] store issuer -> warpgroup: box has been read
+  constexpr int kBufs = C::kBufs;
+  uint64_t* slot_full = bars + 2 * kPStages + 4;              // [wg][buf] warpgroup -> its store issuer: box is in smem
+  uint64_t* slot_free = bars + 2 * kPStages + 4 + 2 * kBufs;  // [wg][buf] store issuer -> warpgroup: box has been read
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + C::kNumBars);
   const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;   // position inside the CTA pair
   const bool leader = rank == 0;
@@ -306,7 +323,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], C::kCtas * (kEpiThreads / 32));  // pair: both CTAs' epilogue warps, on the leader
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 2 * kBufs; ++i) {
       mbar_init(&slot_full[i], kWgThreads / 32);
       mbar_init(&slot_free[i], 1);
     }
@@ -334,17 +351,32 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       Item it;
       int stage = 0;
       uint32_t phase = 0;
+      int item_no = -1;
       while (w.next(pl, it)) {
         if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
+        ++item_no;
+        unsigned long long* tr = trace_slot<TRACE>(ar, item_no);
+        long long w_empty = 0;
+        const long long t_flag = TRACE ? clock64() : 0;
         if (it.kind != kItemG && (pl.kind_mask & 1)) {  // G^T of this chunk must be complete and visible
           wait_counter(pl.g_done + it.chunk, 2u * C::kCtas * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
           fence_proxy_async_all();
+        }
+        if (tr) {
+          tr[8] = clock64() - t_flag;
+          tr[10] = clock64();
         }
         const int mblk = it.m_blk * C::kCtas + rank;            // this CTA's 128-row block of the tile
         const int c0 = it.chunk * pl.chunk_rows;                // first class of the chunk in the shard
         const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;  // first row of the chunk's scratch buffer
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
+          if (tr) {
+            const long long t0 = clock64();
+            mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
+            w_empty += clock64() - t0;
+          } else {
+            mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
+          }
           // pair: both CTAs' bytes are counted on the leader's barrier (count 2: leader +tx, follower plain)
           const uint32_t full_addr = PAIR ? mapa_u32(smem_u32(&full[stage]), 0) : smem_u32(&full[stage]);
           if (leader) mbar_arrive_expect_tx(&full[stage], C::kCtas * kPStageBytes);
@@ -370,6 +402,10 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
             phase ^= 1u;
           }
         }
+        if (tr) {
+          tr[7] = w_empty;
+          tr[11] = clock64();
+        }
       }
     }
   } else if (warp == 1) {
@@ -382,8 +418,13 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      int item_no = -1;
       while (w.next(pl, it)) {
         if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
+        ++item_no;
+        unsigned long long* tr = trace_slot<TRACE>(ar, item_no);
+        long long w_full = 0;
+        if (tr) tr[0] = clock64();
         const bool a_mn = it.kind == kItemX;
         const bool b_mn = it.kind != kItemG;
         const uint32_t idesc = make_idesc_bf16(C::kCtas * kBM, kPBN, a_mn, b_mn);
@@ -394,9 +435,16 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         const uint32_t b_step = b_mn ? (2048u >> 4) : (32u >> 4);
         mbar_wait(&tempty[acc], acc_phase ^ 1u, 0x200u + acc);
         tc_fence_after();
+        if (tr) tr[1] = clock64();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kPBN);
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
-          mbar_wait(&full[stage], phase, 0x300u + stage);
+          if (tr) {
+            const long long t0 = clock64();
+            mbar_wait(&full[stage], phase, 0x300u + stage);
+            w_full += clock64() - t0;
+          } else {
+            mbar_wait(&full[stage], phase, 0x300u + stage);
+          }
           tc_fence_after();
           const uint32_t a_base = smem_u32(smem + stage * kPStageBytes);
           const uint64_t da = da0 + (a_base >> 4);
@@ -414,6 +462,10 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
           }
         }
         if constexpr (PAIR) tc_commit_pair(&tfull[acc], 0x3); else tc_commit(&tfull[acc]);
+        if (tr) {
+          tr[2] = clock64();
+          tr[3] = w_full;
+        }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
@@ -422,17 +474,18 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     if (lane == 0) {
       // ---------------- G^T store issuer of epilogue warpgroup (3 - warp) ----------------
       const int wg = 3 - warp;
-      uint8_t* slot = epi_smem + wg * kPSlotBytes;
       ItemWalker w;
       w.init(pl, walk_first, walk_step);
       Item it;
-      uint32_t n_box = 0;  // boxes this issuer has sent so far (two per G tile)
+      uint32_t n_box = 0;  // boxes this issuer has sent so far (two per G tile); box n lives in buffer n % kBufs
       while (w.next(pl, it)) {
         if (it.kind != kItemG || it.kb0 >= it.kb1 || !(pl.kind_mask & 1)) continue;
         const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;
         const int mblk = it.m_blk * C::kCtas + rank;
         for (int bx = 0; bx < 2; ++bx, ++n_box) {
-          mbar_wait(&slot_full[wg], n_box & 1u, 0x600u + wg);
+          const uint32_t buf = n_box % kBufs, use = n_box / kBufs;
+          uint8_t* slot = epi_smem + (wg * kBufs + buf) * kPSlotBytes;
+          mbar_wait(&slot_full[wg * kBufs + buf], use & 1u, 0x600u + wg);
           if (bx == 0 && it.chunk >= pl.nbuf && (pl.kind_mask & 6) == 6) {  // the X / W tiles that last read this scratch buffer must be done
             const int kp = it.chunk - pl.nbuf;
             wait_counter(pl.xw_done + kp, C::kCtas * static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
@@ -441,7 +494,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
           tma_store_2d_hint(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + mblk * kBM, kEvictLast);
           tma_store_commit();
           tma_store_wait_read0();
-          mbar_arrive(&slot_free[wg]);  // the warpgroup may overwrite its slot
+          mbar_arrive(&slot_free[wg * kBufs + buf]);  // the warpgroup may overwrite this buffer
         }
         tma_store_wait_all0();  // both boxes are written (and, through the barrier chain, the t_j atomics are done)
         __threadfence();
@@ -455,9 +508,8 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     const int epi_tid = static_cast<int>(threadIdx.x) - (kGemmThreads - kEpiThreads);
     const int wg = epi_tid >> 7;
     const int wg_tid = epi_tid & 127;
-    uint8_t* slot = epi_smem + wg * kPSlotBytes;
-    float* lse_s = reinterpret_cast<float*>(epi_smem + kPRowsOff) + wg * 128;       // this warpgroup's 128 samples
-    int* lbl_s = reinterpret_cast<int*>(epi_smem + kPRowsOff + 256 * 4) + wg * 128;
+    float* lse_s = reinterpret_cast<float*>(epi_smem + C::kRowsOff) + wg * 128;  // this warpgroup's 128 samples
+    int* lbl_s = reinterpret_cast<int*>(epi_smem + C::kRowsOff + 256 * 4) + wg * 128;
     ItemWalker w;
     w.init(pl, walk_first, walk_step);
     Item it;
@@ -468,17 +520,47 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     EpiOutState ost;
     ost.it = 0;
     const float gscale = EXT ? 0.f : __ldg(ar.gscale);
+    int item_no = -1;
     while (w.next(pl, it)) {
       if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
+      ++item_no;
+      unsigned long long* tr = (epi_tid == 0) ? trace_slot<TRACE>(ar, item_no) : nullptr;
+      if (tr) {
+        tr[4] = clock64();
+        tr[9] = it.kind;
+      }
       // per-tile row data is fetched before waiting for the accumulator, so its latency is hidden
       float lse_v = 0.f;
       int lbl_v = -1;
+      EpiDW::Params pw;
+      EpiDW::RowData rdw;
       if (it.kind == kItemG) {
         if (!EXT) lse_v = __ldg(ar.lse2 + it.n_blk * kPBN + epi_tid);
         lbl_v = __ldg(ar.lbl_local + it.n_blk * kPBN + epi_tid);
+      } else if (it.kind == kItemW) {
+        // (t_j of this chunk is final: the producer of this tile only loads operands once g_done[chunk] is
+        //  complete, but the epilogue may run ahead of it -- so wait for the same counter here)
+        pw.dw = ar.dw;
+        pw.what = ar.what;
+        pw.t = ar.tproj;
+        pw.inv_norm = ar.inv_nw;
+        pw.row_off = it.chunk * pl.chunk_rows;
+        pw.rows_valid = plan_rows(pl, it.chunk);
+        pw.D = pl.D;
+        pw.Dp = pl.Dp;
+        pw.use_tma = ar.dw_tma;
+        if (pl.kind_mask & 1)
+          wait_counter(pl.g_done + it.chunk, 2u * C::kCtas * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x510u);
+        TileCoord tcw;
+        tcw.m_blk = it.m_blk * C::kCtas + rank;
+        tcw.n_blk = it.n_blk;
+        tcw.kb0 = it.kb0;
+        tcw.kb1 = it.kb1;
+        rdw = EpiDW::template prefetch<kPBN>(pw, tcw, row_in_tile, epi_tid);
       }
       mbar_wait(&tfull[acc], acc_phase, 0x400u + acc);
       tc_fence_after();
+      if (tr) tr[5] = clock64();
       if (it.kind != kItemG && epi_tid == 0) {  // this tile has finished reading its G^T chunk
         fence_proxy_async_all();
         __threadfence();
@@ -487,8 +569,10 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       // the slot is used through two different mechanisms (mbarrier hand-off to the store issuer for
       // G tiles, bulk-group waits for X / W chunks): drain the previous one when the kind changes
       if (prev_kind != -1 && (it.kind == kItemG) != (prev_kind == kItemG)) {
-        if (prev_kind == kItemG) {
-          mbar_wait(&slot_free[wg], (n_box & 1u) ^ 1u, 0x800u + wg);
+        if (prev_kind == kItemG) {  // every buffer's last G^T box has been read by its bulk store
+          const uint32_t uses = n_box / kBufs;  // n_box is even: the same number of boxes went through each buffer
+#pragma unroll
+          for (int b = 0; b < kBufs; ++b) mbar_wait(&slot_free[wg * kBufs + b], (uses & 1u) ^ 1u, 0x800u + wg);
         } else {
           if (wg_tid == 0) tma_store_wait_read<0>();
           named_bar_sync(2 + wg, kWgThreads);
@@ -532,12 +616,13 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         const int tile_cls0 = c0 + mblk * kBM;
         const bool row_ok = row_local < rows;
         float tsum = 0.f;
-        const uint32_t srow = smem_u32(slot) + row_in_tile * 128;
         const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
 #pragma unroll 1
         for (int bx = 0; bx < 2; ++bx, ++n_box) {
-          // the store issuer has finished reading the previous box out of this slot
-          mbar_wait(&slot_free[wg], (n_box & 1u) ^ 1u, 0x900u + wg);
+          // the bulk store of the box that last used this buffer has finished reading it
+          const uint32_t buf = n_box % kBufs, use = n_box / kBufs;
+          mbar_wait(&slot_free[wg * kBufs + buf], (use & 1u) ^ 1u, 0x900u + wg);
+          const uint32_t srow = smem_u32(epi_smem + (wg * kBufs + buf) * kPSlotBytes) + row_in_tile * 128;
 #pragma unroll 1
           for (int h = 0; h < 2; ++h) {
             const int cl = bx * 64 + h * 32;      // column inside this warpgroup's half
@@ -568,33 +653,24 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
           __syncwarp();
           if (lane == 0) {
             if (bx == 1) arrive_tempty<PAIR>(&tempty[acc]);
-            mbar_arrive(&slot_full[wg]);
+            mbar_arrive(&slot_full[wg * kBufs + buf]);
           }
         }
       } else if (it.kind == kItemX) {
         EpiRedAdd::Params p;
         p.M = pl.B;
         p.N = pl.D;
-        EpiRedAdd::template consume<kPBN, 1>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
+        EpiRedAdd::template consume<kPBN, kBufs>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) arrive_tempty<PAIR>(&tempty[acc]);
       } else {
-        EpiDW::Params p;
-        p.dw = ar.dw;
-        p.what = ar.what;
-        p.t = ar.tproj;
-        p.inv_norm = ar.inv_nw;
-        p.row_off = c0;
-        p.rows_valid = rows;
-        p.D = pl.D;
-        p.Dp = pl.Dp;
-        p.use_tma = ar.dw_tma;
-        EpiDW::template consume<kPBN, 1>(p, ost, tc, tmDw, taddr, row_in_tile, epi_tid, epi_smem);
+        EpiDW::template consume_with<kPBN, kBufs>(pw, ost, tc, tmDw, taddr, row_in_tile, epi_tid, epi_smem, rdw);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) arrive_tempty<PAIR>(&tempty[acc]);
       }
+      if (tr) tr[6] = clock64();
       prev_kind = it.kind;
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;

@@ -435,25 +435,55 @@ struct EpiDW {
   __device__ static void drain(int epi_tid) {
     if ((epi_tid & 127) == 0) tma_store_wait_all0();
   }
-  template <int BN, int NBUF = 2>
-  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
-                                 int row_in_tile, int epi_tid, uint8_t* smem) {
+  // Per-row data of a tile that does not depend on the accumulator: fetched BEFORE the epilogue waits for the
+  // MMAs of the tile, so the global-load latency (inv_norm, t_j, first chunk of w_hat) is off the critical path.
+  struct RowData {
+    float tj, inv;
+    uint4 w0[4];
+  };
+  template <int BN>
+  __device__ static RowData prefetch(const Params& p, const TileCoord& tc, int row_in_tile, int epi_tid) {
+    RowData rd;
     const int wg = epi_tid >> 7;
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const bool valid = row_local < p.rows_valid;
     const int cls = p.row_off + row_local;
-    float tj = 0.f, inv = 0.f;
+    rd.tj = 0.f;
+    rd.inv = 0.f;
     if (valid) {
-      inv = __ldg(p.inv_norm + cls);
-      tj = (inv < 0.5e12f) ? __ldcg(p.t + cls) : 0.f;  // clamped rows take no projection (t is written in-kernel: coherent load)
+      rd.inv = __ldg(p.inv_norm + cls);
+      rd.tj = __ldcg(p.t + cls);  // written by G tiles of this launch: coherent load
     }
+    const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
+    const int c_begin = wg * (BN / 2);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) rd.w0[q] = make_uint4(0u, 0u, 0u, 0u);
+    if (tc.n_blk * BN + c_begin < p.D) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) rd.w0[q] = __ldg(reinterpret_cast<const uint4*>(wrow + tc.n_blk * BN + c_begin) + q);
+    }
+    return rd;
+  }
+  template <int BN, int NBUF = 2>
+  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t* smem) {
+    const RowData rd = prefetch<BN>(p, tc, row_in_tile, epi_tid);
+    consume_with<BN, NBUF>(p, st, tc, tmC, taddr, row_in_tile, epi_tid, smem, rd);
+  }
+  template <int BN, int NBUF = 2>
+  __device__ static void consume_with(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC,
+                                      uint32_t taddr, int row_in_tile, int epi_tid, uint8_t* smem, const RowData& rd) {
+    const int wg = epi_tid >> 7;
+    const int row_local = tc.m_blk * kBM + row_in_tile;
+    const bool valid = row_local < p.rows_valid;
+    const int cls = p.row_off + row_local;
+    const float inv = rd.inv;
+    const float tj = (inv < 0.5e12f) ? rd.tj : 0.f;  // clamped rows take no projection
     const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
     const int c_begin = wg * (BN / 2), c_end = (wg + 1) * (BN / 2);
     uint4 wnext[4];
-    if (tc.n_blk * BN + c_begin < p.D) {
 #pragma unroll
-      for (int q = 0; q < 4; ++q) wnext[q] = __ldg(reinterpret_cast<const uint4*>(wrow + tc.n_blk * BN + c_begin) + q);
-    }
+    for (int q = 0; q < 4; ++q) wnext[q] = rd.w0[q];
     for (int c = c_begin; c < c_end; c += 32) {
       const int col0 = tc.n_blk * BN + c;
       if (col0 >= p.D) break;

@@ -29,10 +29,10 @@ from torch.nn import Parameter
 
 from . import _lib
 
-# classes per backward chunk: the persistent backward keeps THREE chunks of bf16 dLoss/dcos in flight
-# (B=1024: 3 x 19.4 MB), which together with the matching w_hat rows stays inside the 126 MB L2;
-# 128 * 74 rows give 296 / 148 / 144 tiles per chunk for the three GEMMs on 148 SMs.
-DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 128 * 74))
+# classes per backward chunk: the persistent backward keeps FOUR chunks of bf16 dLoss/dcos in flight
+# (B=1024: 4 x 19.4 MB), which together with the matching w_hat rows stays inside the 126 MB L2;
+# 256 * 37 rows = 37 tile rows per CTA pair and chunk (measured best among 4.8k .. 19k on B200).
+DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 256 * 37))
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -87,7 +87,7 @@ class CudaEngine:
     @staticmethod
     def _scratch_for(B, Cs, device, chunk_classes):
         chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
-        nbytes = _lib.lib().arcb_scratch_bytes(B, 3 * chunk)  # three buffers (multi-buffered persistent backward)
+        nbytes = _lib.lib().arcb_scratch_bytes(B, int(os.environ.get("ARCB_SCRATCH_BUFS", 4)) * chunk)  # four buffers by default
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
     def shard_forward(self, xc, wc, lab, cfg):

@@ -166,8 +166,8 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     if args.cpu_sample_rows:
         rows = args.cpu_sample_rows
-    else:  # K + W steps (plus the two probes) should end within ~2.5 minutes
-        rows, _, _ = size_cpu_sample(args, threads, 140.0 / max(1, args.steps + args.warmup))
+    else:  # K + W steps (plus the two probes) should end within ~2 minutes
+        rows, _, _ = size_cpu_sample(args, threads, 100.0 / max(1, args.steps + args.warmup))
     rate, dt = cpu_port_rate(rows, args.dim, args.classes, args.easy_margin, args.steps, args.warmup, threads)
     sample = (f"{rows} of {args.batch} batch rows per step, full C={args.classes}, D={args.dim}; torch-CPU fp32 port of "
               f"the reference head (oracle.TorchPort), {dt:.2f} s/step")

@@ -194,6 +194,8 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   return ARCB_OK;
 }
 
+constexpr int kLaunchRefused = 1;  // internal: the cooperative launch was refused, try the next schedule
+
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
 template <bool EXT, bool PAIR, bool TRACE = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
@@ -307,8 +309,15 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   cfg.attrs = attr;
   cfg.numAttrs = PAIR ? 2 : 1;
   LaunchScope ls(ARCB_K_BWD_PERSISTENT, st);
-  ARCB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw, pl,
-                               ar));
+  const cudaError_t le =
+      cudaLaunchKernelEx(&cfg, kern, tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw, pl, ar);
+  if (le != cudaSuccess) {
+    // e.g. the device cannot keep the whole grid co-resident right now (shared GPU, MPS limits): nothing has
+    // been enqueued, so the caller may fall back to another schedule
+    (void)cudaGetLastError();
+    fail(ARCB_ERR_CUDA, "persistent backward launch refused: %s", cudaGetErrorString(le));
+    return kLaunchRefused;
+  }
   return ARCB_OK;
 }
 
@@ -665,15 +674,19 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
     if (use_pair_backward()) {  // a pair's tile has 256 rows: chunks (= scratch buffers) must be whole tiles
       int64_t pc2 = pchunk / 256 * 256;
       if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
-      if (pc2 >= 256)
-        return ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
-                   : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+      if (pc2 >= 256) {
+        rc = ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
+                 : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+        if (rc != kLaunchRefused) return rc;
+      }
     }
     if (pchunk >= 128) {
       if (pchunk > round_up(Cs, 128)) pchunk = round_up(Cs, 128);
-      return ext ? launch_bwd_persistent<true, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st)
-                 : launch_bwd_persistent<false, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st);
+      rc = ext ? launch_bwd_persistent<true, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st)
+               : launch_bwd_persistent<false, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st);
+      if (rc != kLaunchRefused) return rc;
     }
+    // refused twice: one launch per GEMM and chunk needs no co-residency (memsets above are still valid)
   }
 
   const int sms = device_sm_count();

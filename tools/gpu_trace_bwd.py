@@ -41,3 +41,11 @@ for cta in (0, 2):
               f"epilogue wait tfull {epi_wait:7.0f} work {epi_work:6.0f} | producer item {prod_total:7.0f} (wait empty {prod_empty:6.0f}, flag {prod_flag:6.0f})")
     # steady-state sample of consecutive tiles
     print("   first 12 tiles: kind, mma_start, mma_end-start, epi_work:", [(names[int(r[9])], int(r[0]-t[0,0]), int(r[2]-r[0]), int(r[6]-r[5])) for r in t[20:32]])
+
+print("per-CTA totals (kcycles): producer flag wait | producer empty wait | MMA full wait | MMA tempty wait | epilogue tfull wait | epilogue work | span")
+for cta in range(8):
+    t = tr[cta]; n = int((t[:, 6] > 0).sum()); t = t[:n]
+    if n == 0: continue
+    span = (t[-1, 6] - t[0, 4]) / 1e3
+    print(f"  CTA {cta}: n={n:4d} flag {t[:,8].sum()/1e3:7.0f} | empty {t[:,7].sum()/1e3:7.0f} | full {t[:,3].sum()/1e3:7.0f} | "
+          f"tempty {(t[:,1]-t[:,0]).clip(min=0).sum()/1e3:7.0f} | tfull {(t[:,5]-t[:,4]).sum()/1e3:7.0f} | work {(t[:,6]-t[:,5]).sum()/1e3:7.0f} | span {span:7.0f}")

@@ -270,7 +270,12 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ok = ok && make_tmap_mn3(&tmXhatMN, W.xhat, W.Dp, B, W.Dp * 2, kBRows / 64);
   ok = ok && make_tmap_2d(&tmDx, dxhat, f32, 4, D, B, W.Dp * 4, 32, kBM);
   if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the persistent backward could not be encoded");
-  const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
+  static int dw_direct = -1;  // ARCB_DW_DIRECT=1: dW rows are stored straight from registers (tuning aid)
+  if (dw_direct < 0) {
+    const char* e = getenv("ARCB_DW_DIRECT");
+    dw_direct = (e && e[0] == '1') ? 1 : 0;
+  }
+  const bool dw_tma = !dw_direct && (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
                       make_tmap_2d(&tmDw, dw, f32, 4, D, Cs, D * 4, 32, kBM);
   if (!dw_tma) tmDw = tmDx;
 

@@ -511,10 +511,19 @@ struct EpiDW {
       if (p.use_tma) {
         chunk_out_tma<false, NBUF>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, r, col0, p.row_off + tc.m_blk * kBM);
       } else if (valid) {
+        // straight from registers: each thread owns 128 contiguous bytes of its dW row (no shared-memory round trip)
         float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;
+        if ((p.D & 3) == 0 && col0 + 32 <= p.D) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (col0 + j < p.D) o[j] = r[j];
+          for (int j = 0; j < 32; j += 4)
+            asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(r[j]), "f"(r[j + 1]),
+                         "f"(r[j + 2]), "f"(r[j + 3])
+                         : "memory");
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < p.D) o[j] = r[j];
+        }
       }
     }
   }

@@ -18,7 +18,8 @@ LIB_PATH = os.path.join(_PKG_DIR, "libarcface_b200.so")
 _SRC = os.path.join(_PKG_DIR, "csrc", "arcface_b200.cu")
 _HDRS = [
     os.path.join(_PKG_DIR, "csrc", n)
-    for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "gemm2_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh")
+    for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "gemm2_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh",
+              "optim_rows.cuh")
 ] + [os.path.join(_ROOT, "include", "arcface_b200.h")]
 
 NVCC_FLAGS = [
@@ -32,11 +33,12 @@ EXPORTED = [
     "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
     "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3", "arcb_set_pair_mode",
+    "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
 ]
 
 KERNEL_KINDS = [
     "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",
-    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test", "bwd_persistent", "top3",
+    "dw_gemm", "l2norm_bwd", "logits_gemm", "gemm_test", "bwd_persistent", "top3", "optim",
 ]
 
 _lock = threading.Lock()
@@ -75,7 +77,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 def _declare(lib):
     c = ctypes
-    vp, i64, i32, f32 = c.c_void_p, c.c_int64, c.c_int, c.c_float
+    vp, i64, i32, f32, f64 = c.c_void_p, c.c_int64, c.c_int, c.c_float, c.c_double
     lib.arcb_version.restype = i32
     lib.arcb_version.argtypes = []
     lib.arcb_last_error.restype = c.c_char_p
@@ -97,6 +99,14 @@ def _declare(lib):
     fwd_args = [vp, i64, vp, i64, vp, i64, i64, i64, i64, f32, f32, i32, vp, i64]
     lib.arcb_shard_forward.restype = i32
     lib.arcb_shard_forward.argtypes = fwd_args + [vp, vp]
+    lib.arcb_shard_forward_prenorm.restype = i32
+    lib.arcb_shard_forward_prenorm.argtypes = fwd_args + [vp, vp]
+    lib.arcb_ws_weight_slots.restype = i32
+    lib.arcb_ws_weight_slots.argtypes = [vp, i64, i64, c.POINTER(vp), c.POINTER(vp)]
+    lib.arcb_sgd_step.restype = i32
+    lib.arcb_sgd_step.argtypes = [vp, i64, vp, i64, vp, i64, i64, i64, f64, f64, f64, f64, i32, i32, vp, i64, vp, vp]
+    lib.arcb_adam_step.restype = i32
+    lib.arcb_adam_step.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i64, f64, f64, f64, f64, f64, i64, vp, i64, vp, vp]
     lib.arcb_shard_logits.restype = i32
     lib.arcb_shard_logits.argtypes = fwd_args + [vp, i64, vp]
     lib.arcb_shard_forward_static.restype = i32

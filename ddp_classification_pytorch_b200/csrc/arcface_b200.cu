@@ -20,6 +20,7 @@
 #include "gemm2_sm100.cuh"
 #include "gemm_sm100.cuh"
 #include "rowwise.cuh"
+#include "optim_rows.cuh"
 
 using namespace arcb;
 
@@ -112,10 +113,12 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
     off += round_up(bytes, 256);
     return r;
   };
-  w.xhat = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
+  // the two weight-derived regions come first so that their offsets do not depend on the batch size
+  // (arcb_ws_weight_slots: the fused optimizer step deposits them for the next forward)
   w.what = reinterpret_cast<__nv_bfloat16*>(take(Cs * w.Dp * 2));
-  w.inv_nx = reinterpret_cast<float*>(take(w.Bp * 4));
   w.inv_nw = reinterpret_cast<float*>(take(Cs * 4));
+  w.xhat = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
+  w.inv_nx = reinterpret_cast<float*>(take(w.Bp * 4));
   w.lbl_local = reinterpret_cast<int*>(take(w.Bp * 4));
   w.sub = reinterpret_cast<float*>(take(w.Bp * 4));
   w.zt = reinterpret_cast<float*>(take(w.Bp * 4));
@@ -166,7 +169,7 @@ int launch_l2norm(const float* x, int64_t rows, int64_t D, int64_t ldx, __nv_bfl
 // Steps shared by the fused and the materialising forward: normalise, target preparation.
 int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
                    int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy, void* ws_ptr,
-                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st) {
+                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, bool w_prenormalised = false) {
   int rc = check_dims(B, Cs, D);
   if (rc) return rc;
   if (!x || !w || !labels || !ws_ptr) return fail(ARCB_ERR_INVALID, "null pointer argument");
@@ -179,8 +182,10 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
                 (long long)ws_bytes);
   rc = launch_l2norm(x, B, D, ldx, W.xhat, W.Dp, W.inv_nx, st, ARCB_K_L2NORM_X);
   if (rc) return rc;
-  rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
-  if (rc) return rc;
+  if (!w_prenormalised) {  // otherwise the workspace already holds w_hat / inv_norm of exactly this w
+    rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
+    if (rc) return rc;
+  }
   const double md = static_cast<double>(m);
   const float cos_m = static_cast<float>(cos(md)), sin_m = static_cast<float>(sin(md));
   const float th = static_cast<float>(cos(M_PI - md)), mm = static_cast<float>(sin(M_PI - md) * md);
@@ -380,6 +385,43 @@ bool use_persistent_backward() {
 
 }  // namespace
 
+namespace {
+// ---- optimizer step on the weight shard (+ the next forward's normalised copy) -- optim_rows.cuh ----
+template <class Rule>
+int launch_optim(float* w, int64_t ldw, const float* dw, int64_t ldg, float* s0, float* s1, int64_t lds,
+                        int64_t rows, int64_t D, const Rule& rule, void* w_hat, int64_t Dp, float* inv_norm,
+                        cudaStream_t st) {
+  if (!w || !dw) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (rows < 0 || D <= 0 || D > (1 << 20) || ldw < D || ldg < D || ((s0 || s1) && lds < D))
+    return fail(ARCB_ERR_INVALID, "bad sizes for the optimizer step");
+  if ((w_hat != nullptr) != (inv_norm != nullptr))
+    return fail(ARCB_ERR_INVALID, "w_hat_bf16 and inv_norm_w must be given together (or both NULL)");
+  if (w_hat && (Dp < D || Dp % 64)) return fail(ARCB_ERR_INVALID, "Dp must be arcb_padded_dim(D)");
+  if (rows == 0) return ARCB_OK;
+  LaunchScope ls(ARCB_K_OPTIM, st);
+  int64_t blocks = (rows + 7) / 8;
+  if (blocks > 148 * 64) blocks = 148 * 64;  // grid-stride beyond that
+  const int64_t Dpad = w_hat ? Dp : round_up(D, 64);
+  auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool vec = (D % 4 == 0) && (ldw % 4 == 0) && (ldg % 4 == 0) && (lds % 4 == 0 || (!s0 && !s1)) && al16(w) &&
+                   al16(dw) && al16(s0) && al16(s1);
+  const int g = static_cast<int>(blocks);
+  __nv_bfloat16* wh = static_cast<__nv_bfloat16*>(w_hat);
+#define ARCB_OPT(NV) \
+  optim_rows_kernel<NV, Rule><<<g, 256, 0, st>>>(w, ldw, dw, ldg, s0, s1, lds, rows, (int)D, rule, wh, (int)Dpad, inv_norm)
+  if (vec && Dpad <= 128) ARCB_OPT(1);
+  else if (vec && Dpad <= 256) ARCB_OPT(2);
+  else if (vec && Dpad <= 512) ARCB_OPT(4);
+  else if (vec && Dpad <= 1024) ARCB_OPT(8);
+  else if (vec && Dpad <= 2048) ARCB_OPT(16);
+  else ARCB_OPT(0);
+#undef ARCB_OPT
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
+}  // namespace
+
 extern "C" {
 
 int arcb_version(void) { return 100; }
@@ -505,13 +547,15 @@ int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes) {
   return round_up(chunk_classes, 128) * round_up(B, kBNTile) * 2;
 }
 
-int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
-                       int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
-                       int64_t ws_bytes, float* stats, void* stream) {
+static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
+                              int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
+                              int easy_margin, void* ws, int64_t ws_bytes, float* stats, void* stream,
+                              bool w_prenormalised) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (!stats) return fail(ARCB_ERR_INVALID, "null stats pointer");
   Workspace W;
-  int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st);
+  int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
+                          w_prenormalised);
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
@@ -538,6 +582,64 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
   }
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;
+}
+
+int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                       int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                       int64_t ws_bytes, float* stats, void* stream) {
+  return shard_forward_impl(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, stats,
+                            stream, false);
+}
+
+int arcb_shard_forward_prenorm(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
+                               int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
+                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, void* stream) {
+  return shard_forward_impl(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, stats,
+                            stream, true);
+}
+
+int arcb_ws_weight_slots(void* ws, int64_t Cs, int64_t D, void** w_hat_bf16, float** inv_norm_w) {
+  if (!ws || !w_hat_bf16 || !inv_norm_w) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (Cs <= 0 || D <= 0) return fail(ARCB_ERR_INVALID, "Cs and D must be positive");
+  if (reinterpret_cast<uintptr_t>(ws) & 255) return fail(ARCB_ERR_INVALID, "workspace must be 256-byte aligned");
+  Workspace W = carve(ws, 1, Cs, D);  // the two weight regions lead the layout: same place for every B
+  *w_hat_bf16 = W.what;
+  *inv_norm_w = W.inv_nw;
+  return ARCB_OK;
+}
+
+int arcb_sgd_step(float* w, int64_t ldw, const float* dw, int64_t ldg, float* momentum_buf, int64_t ldb, int64_t rows,
+                  int64_t D, double lr, double momentum, double dampening, double weight_decay, int nesterov,
+                  int first_step, void* w_hat_bf16, int64_t Dp, float* inv_norm_w, void* stream) {
+  if (momentum != 0.0 && !momentum_buf) return fail(ARCB_ERR_INVALID, "momentum != 0 needs a momentum buffer");
+  if (nesterov && (momentum <= 0.0 || dampening != 0.0))
+    return fail(ARCB_ERR_INVALID, "Nesterov momentum requires a momentum and zero dampening");
+  // hyper-parameters arrive as doubles (Python floats) and are rounded to fp32 once, after any arithmetic on
+  // them -- the way torch hands its scalars to its kernels
+  SgdRule r;
+  r.lr = static_cast<float>(lr); r.momentum = static_cast<float>(momentum);
+  r.one_minus_damp = static_cast<float>(1.0 - dampening); r.wd = static_cast<float>(weight_decay);
+  r.nesterov = nesterov ? 1 : 0; r.first = first_step ? 1 : 0; r.has_buf = (momentum != 0.0) ? 1 : 0;
+  return launch_optim(w, ldw, dw, ldg, r.has_buf ? momentum_buf : nullptr, nullptr, ldb, rows, D, r, w_hat_bf16, Dp,
+                      inv_norm_w, static_cast<cudaStream_t>(stream));
+}
+
+int arcb_adam_step(float* w, int64_t ldw, const float* dw, int64_t ldg, float* exp_avg, float* exp_avg_sq, int64_t lds,
+                   int64_t rows, int64_t D, double lr, double beta1, double beta2, double eps, double weight_decay,
+                   int64_t step, void* w_hat_bf16, int64_t Dp, float* inv_norm_w, void* stream) {
+  if (!exp_avg || !exp_avg_sq) return fail(ARCB_ERR_INVALID, "null optimizer state");
+  if (step < 1) return fail(ARCB_ERR_INVALID, "step counts from 1 (got %lld)", (long long)step);
+  if (!(beta1 >= 0.0 && beta1 < 1.0 && beta2 >= 0.0 && beta2 < 1.0)) return fail(ARCB_ERR_INVALID, "betas out of [0, 1)");
+  const double bc1 = 1.0 - pow(beta1, static_cast<double>(step));
+  const double bc2 = 1.0 - pow(beta2, static_cast<double>(step));
+  AdamRule r;
+  r.one_minus_b1 = static_cast<float>(1.0 - beta1); r.b2 = static_cast<float>(beta2);
+  r.one_minus_b2 = static_cast<float>(1.0 - beta2); r.eps = static_cast<float>(eps);
+  r.wd = static_cast<float>(weight_decay);
+  r.step_size = static_cast<float>(lr / bc1);
+  r.bc2_sqrt = static_cast<float>(sqrt(bc2));
+  return launch_optim(w, ldw, dw, ldg, exp_avg, exp_avg_sq, lds, rows, D, r, w_hat_bf16, Dp, inv_norm_w,
+                      static_cast<cudaStream_t>(stream));
 }
 
 // Forward for hosts that must not allocate: identical to arcb_shard_forward, except that the

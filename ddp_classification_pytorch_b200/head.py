@@ -66,6 +66,59 @@ def _canonical_inputs(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor):
     return xc, wc, lab
 
 
+class _WeightCache:
+    """A forward workspace that outlives the call, so that the normalised weight in it can be reused.
+
+    ``F.normalize(self.weight)`` (arc_main.py:159) is recomputed by the reference on every call.  With this
+    cache the head keeps ONE workspace; its weight slots (w_hat bf16 + 1/norm) stay valid while the parameter
+    is unchanged -- ``valid`` holds the (data_ptr, tensor version) they were computed from -- and the fused
+    optimizer step (optim.py) refreshes them in the same pass that updates the weight.  A workspace that an
+    un-backpropagated graph still needs is ``busy``: the next forward then takes a fresh, uncached workspace.
+    """
+
+    def __init__(self):
+        self.ws = None
+        self.ws_bytes = 0
+        self.key = None
+        self.valid = None
+        self.busy = 0
+        self.generation = 0
+
+    def workspace(self, B, Cs, D, device):
+        need = _lib.lib().arcb_ws_bytes(B, Cs, D)
+        if need <= 0:
+            raise RuntimeError("arcb_ws_bytes rejected the sizes")
+        if self.ws is None or self.key != (Cs, D, device) or need > self.ws_bytes:
+            self.ws = torch.empty(need, dtype=torch.uint8, device=device)
+            self.ws_bytes, self.key, self.valid = need, (Cs, D, device), None
+        return self.ws, self.ws_bytes
+
+    def slots(self):
+        """Device addresses (w_hat bf16, inv_norm fp32) inside the cached workspace."""
+        import ctypes
+        Cs, D, _ = self.key
+        a, b = ctypes.c_void_p(), ctypes.c_void_p()
+        _lib.check(_lib.lib().arcb_ws_weight_slots(self.ws.data_ptr(), Cs, D, ctypes.byref(a), ctypes.byref(b)),
+                   "arcb_ws_weight_slots")
+        return a.value, b.value
+
+
+class _Lease:
+    """Marks a cached workspace as needed by a pending backward; released by that backward or on collection."""
+
+    def __init__(self, cache):
+        self.cache = cache
+        self.live = True
+        cache.busy += 1
+
+    def release(self):
+        if self.live:
+            self.live = False
+            self.cache.busy -= 1
+
+    __del__ = release
+
+
 class CudaEngine:
     """Every method is one call into libarcface_b200.so (include/arcface_b200.h)."""
 
@@ -95,12 +148,25 @@ class CudaEngine:
         L = _lib.lib()
         B, D = xc.shape
         Cs = wc.shape[0]
-        ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
         stats = torch.empty(B, 4, dtype=torch.float32, device=xc.device)
-        _lib.check(L.arcb_shard_forward(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
-                                        cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), _stream()),
-                   "arcb_shard_forward")
-        return stats, (B, Cs, D, ws, ws_bytes)
+        cache = cfg.get("wcache")
+        tag = cfg.get("w_tag")  # (data_ptr, version) of the parameter itself
+        fn, gen = L.arcb_shard_forward, 0
+        if cache is not None and cache.busy == 0 and tag is not None and tag[0] == wc.data_ptr():
+            ws, ws_bytes = cache.workspace(B, Cs, D, xc.device)
+            if cache.valid == tag:  # w_hat / inv_norm in the workspace belong to exactly this weight
+                fn = L.arcb_shard_forward_prenorm
+            cache.valid = None  # until the call below has been enqueued
+        else:
+            cache = None
+            ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
+        _lib.check(fn(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"], cfg["m"],
+                      int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), _stream()), "arcb_shard_forward")
+        if cache is not None:
+            cache.valid = tag
+            cache.generation += 1
+            gen = cache.generation
+        return stats, (B, Cs, D, ws, ws_bytes, cache, gen)
 
     def shard_logits(self, xc, wc, lab, cfg):
         L = _lib.lib()
@@ -111,12 +177,12 @@ class CudaEngine:
         _lib.check(L.arcb_shard_logits(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
                                        cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(out), Cs,
                                        _stream()), "arcb_shard_logits")
-        return out, (B, Cs, D, ws, ws_bytes)
+        return out, (B, Cs, D, ws, ws_bytes, None, 0)
 
     def shard_top3(self, xc, wc, state, cfg):
         """-> (values [B,3] fp32 logits, indices [B,3] int64 global class ids) of this shard."""
         L = _lib.lib()
-        B, Cs, D, ws, ws_bytes = state
+        B, Cs, D, ws, ws_bytes = state[:5]
         val = torch.empty(B, 3, dtype=torch.float32, device=xc.device)
         idx = torch.empty(B, 3, dtype=torch.int64, device=xc.device)
         _lib.check(L.arcb_shard_top3(_ptr(xc), D, _ptr(wc), D, B, Cs, D, cfg["class_offset"], cfg["s"], _ptr(ws),
@@ -137,7 +203,12 @@ class CudaEngine:
     def shard_backward(self, state, cfg, lse=None, zt=None, grad_loss=None, grad_logits=None):
         """-> (dw [Cs,D], dxhat partial [B,Dp])."""
         L = _lib.lib()
-        B, Cs, D, ws, ws_bytes = state
+        B, Cs, D, ws, ws_bytes = state[:5]
+        cache, gen = state[5], state[6]
+        if cache is not None and cache.generation != gen:
+            raise RuntimeError("ArcMarginProduct (B200): the cached workspace of this forward was reused by a later "
+                               "forward before its backward ran (second backward through a retained graph?); "
+                               "construct the head with cache_normalized_weight=False for that pattern")
         dev = ws.device
         Dp = L.arcb_padded_dim(D)
         scratch, scratch_bytes = self._scratch_for(B, Cs, dev, cfg["chunk_classes"])
@@ -169,7 +240,12 @@ class _FusedLossFn(torch.autograd.Function):
         eng = cfg["engine"]
         xc, wc, lab = eng.prepare(x, w, label)
         B = xc.shape[0]
+        if cfg.get("wcache") is not None:
+            cfg = dict(cfg, w_tag=(w.data_ptr(), w._version))
         stats, state = eng.shard_forward(xc, wc, lab, cfg)
+        lease = None
+        if len(state) > 5 and state[5] is not None and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]):
+            lease = _Lease(state[5])  # the workspace now belongs to this graph until its backward has run
         group = cfg["group"]
         P = _world(group)
         if P > 1:  # the only forward exchange: one [B, 4] record per rank
@@ -180,6 +256,7 @@ class _FusedLossFn(torch.autograd.Function):
         lse, zt, loss = eng.merge_loss(gathered, P, B)
         ctx.save_for_backward(xc)
         ctx.held = (eng, state, lse, zt, cfg, w.dtype, x.dtype)
+        ctx.lease = lease
         aux = cfg["aux_out"]
         aux.update(lse=lse, target_logit=zt, stats=stats)
         if cfg["want_top3"]:  # predictions for the accuracy counters (arc_main.py:338-345, :377-388)
@@ -205,6 +282,8 @@ class _FusedLossFn(torch.autograd.Function):
         if _world(cfg["group"]) > 1:  # the only backward exchange: sum of the class shards' dX_hat partials
             torch.distributed.all_reduce(dxhat, group=cfg["group"])
         dx = eng.input_grad(xc, dxhat)
+        if ctx.lease is not None:
+            ctx.lease.release()
         return dx.to(x_dtype), dw.to(w_dtype), None, None
 
 
@@ -250,10 +329,11 @@ class ArcMarginProduct(nn.Module):
         easy_margin: use the ``cos > 0`` fallback instead of ``th`` / ``mm``
         process_group (keyword-only): shard the classes over this ``torch.distributed`` group;
             ``weight`` then holds only this rank's rows and ``forward`` returns only its columns.
+        cache_normalized_weight (keyword-only): see :meth:`cache_normalized_weight`.
     """
 
     def __init__(self, in_features, out_features, s=30.0, m=0.50, easy_margin=False, *, process_group=None,
-                 chunk_classes: Optional[int] = None, _engine=None):
+                 chunk_classes: Optional[int] = None, cache_normalized_weight: bool = False, _engine=None):
         super().__init__()
         self.in_features = in_features
         self.out_features = out_features
@@ -283,6 +363,18 @@ class ArcMarginProduct(nn.Module):
         self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES
         self.aux = {}
         self._engine = _engine if _engine is not None else CudaEngine()
+        self._wcache = _WeightCache() if cache_normalized_weight else None
+
+    def cache_normalized_weight(self, enable: bool = True):
+        """Keep the forward workspace between calls so that ``F.normalize(self.weight)`` (arc_main.py:159) is only
+        recomputed after the weight has changed (``forward_loss`` path).  Switched on by the fused optimizers in
+        ``optim.py``, which refresh the normalised copy while they update the weight; also saves the pass in a
+        validation loop (arc_main.py:357-404), where the weight is constant."""
+        if enable and self._wcache is None:
+            self._wcache = _WeightCache()
+        elif not enable:
+            self._wcache = None
+        return self
 
     def extra_repr(self):
         return (f"in_features={self.in_features}, out_features={self.out_features}, s={self.s}, m={self.m}, "
@@ -295,7 +387,7 @@ class ArcMarginProduct(nn.Module):
             "s": float(self.s), "m": float(self.m), "easy_margin": bool(self.easy_margin),
             "class_offset": int(self.class_lo), "group": self.process_group,
             "chunk_classes": int(self.chunk_classes), "aux_out": self.aux, "engine": self._engine,
-            "want_top3": False,
+            "want_top3": False, "wcache": self._wcache,
         }
 
     def forward(self, input, label):

@@ -99,6 +99,40 @@ int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64
                               int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
                               int easy_margin, float* stats, void* stream);
 
+/* ---- forward on a weight whose normalised copy is already in the workspace ----
+ * Same arguments, outputs and arithmetic as arcb_shard_forward, but the F.normalize(self.weight) pass
+ * (arc_main.py:159, weight half) is skipped: `ws` must already hold w_hat / inv_norm of exactly this `w` in its
+ * weight slots -- put there by arcb_sgd_step / arcb_adam_step (below), or left by an earlier forward on the same
+ * workspace while `w` has not changed since (validation loop, arc_main.py:357-404: the weight is constant). */
+int arcb_shard_forward_prenorm(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
+                               int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
+                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, void* stream);
+
+/* Where a workspace keeps the normalised weight: w_hat [Cs, arcb_padded_dim(D)] bf16 and inv_norm_w [Cs] fp32.
+ * The two regions lead the workspace layout, so the addresses do not depend on the batch size. */
+int arcb_ws_weight_slots(void* ws, int64_t Cs, int64_t D, void** w_hat_bf16, float** inv_norm_w);
+
+/* ---- optimizer step on the weight shard, fused with the next step's F.normalize(weight) ----
+ * Replaces optimizer.step() (arc_main.py:330) for the head's parameter group: torch.optim.SGD(lr, weight_decay=5e-4,
+ * momentum=0.9) (arc_main.py:252-253) and torch.optim.Adam(lr) (arc_main.py:249-250), with the update rules of
+ * torch/optim/sgd.py and torch/optim/adam.py (single-tensor form, amsgrad / maximize off).  w, dw and the state
+ * tensors are [rows, D] fp32 with their own leading dimensions; w and the state are updated IN PLACE.
+ * If w_hat_bf16 / inv_norm_w are given (both or neither; e.g. from arcb_ws_weight_slots of the workspace the next
+ * forward will use) the unit rows of the UPDATED weight are written there in the same pass, so that
+ * arcb_shard_forward_prenorm can skip its normalisation kernel: one read of w per training step instead of two.
+ *   SGD : g = dw + weight_decay * w;  buf = g on the first step, else momentum * buf + (1 - dampening) * g;
+ *         g = g + momentum * buf if nesterov else buf;  w -= lr * g.   momentum == 0: momentum_buf may be NULL.
+ *   Adam: g = dw + weight_decay * w;  m += (1 - beta1)(g - m);  v = beta2 v + (1 - beta2) g^2;
+ *         w -= lr / (1 - beta1^step) * m / (sqrt(v) / sqrt(1 - beta2^step) + eps);   step counts from 1.
+ * Hyper-parameters are doubles (as Python / torch hold them); 1 - beta, 1 - dampening and the bias corrections are
+ * formed in double and rounded to fp32 once; the per-element arithmetic is fp32. */
+int arcb_sgd_step(float* w, int64_t ldw, const float* dw, int64_t ldg, float* momentum_buf, int64_t ldb, int64_t rows,
+                  int64_t D, double lr, double momentum, double dampening, double weight_decay, int nesterov,
+                  int first_step, void* w_hat_bf16, int64_t Dp, float* inv_norm_w, void* stream);
+int arcb_adam_step(float* w, int64_t ldw, const float* dw, int64_t ldg, float* exp_avg, float* exp_avg_sq, int64_t lds,
+                   int64_t rows, int64_t D, double lr, double beta1, double beta2, double eps, double weight_decay,
+                   int64_t step, void* w_hat_bf16, int64_t Dp, float* inv_norm_w, void* stream);
+
 /* ---- materialising forward: the literal ArcMarginProduct.forward output, arc_main.py:157-176 ----
  * logits [B, ldl] fp32 <- s * (phi at the label column, cos elsewhere) for this shard's columns. */
 int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
@@ -166,7 +200,8 @@ enum {
   ARCB_K_GEMM_TEST = 12,  /* arcb_gemm_bf16                          */
   ARCB_K_BWD_PERSISTENT = 13, /* whole backward of a shard, one launch */
   ARCB_K_TOP3 = 14,       /* exact top-3 re-score                    */
-  ARCB_K_COUNT = 15
+  ARCB_K_OPTIM = 15,      /* optimizer step + next step's normalise  */
+  ARCB_K_COUNT = 16
 };
 int64_t arcb_launch_count(void);
 int arcb_profile_enable(int on);

@@ -34,6 +34,7 @@ EXPORTED = [
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
     "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3", "arcb_set_pair_mode",
     "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
+    "arcb_suggest_chunk_classes",
 ]
 
 KERNEL_KINDS = [
@@ -94,6 +95,8 @@ def _declare(lib):
     lib.arcb_gemm_bf16.argtypes = [vp, i32, vp, i32, i64, i64, i64, i64, i64, vp, i64, i32, vp]
     lib.arcb_ws_bytes.restype = i64
     lib.arcb_ws_bytes.argtypes = [i64, i64, i64]
+    lib.arcb_suggest_chunk_classes.restype = i64
+    lib.arcb_suggest_chunk_classes.argtypes = [i64, i64, i64]
     lib.arcb_scratch_bytes.restype = i64
     lib.arcb_scratch_bytes.argtypes = [i64, i64]
     fwd_args = [vp, i64, vp, i64, vp, i64, i64, i64, i64, f32, f32, i32, vp, i64]

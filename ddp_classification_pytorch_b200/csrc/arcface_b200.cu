@@ -97,6 +97,8 @@ struct Workspace {
   float* gscale;         // [1]
   float* tproj;          // [Cs]
   unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
+  int4* items;             // [items_cap][2] tile list of the persistent backward (bwd_items_kernel)
+  int64_t items_cap;
   int64_t total;
 };
 
@@ -131,7 +133,14 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
   w.zt2 = reinterpret_cast<float*>(take(w.Bp * 4));
   w.gscale = reinterpret_cast<float*>(take(4));
   w.tproj = reinterpret_cast<float*>(take(Cs * 4));
-  w.counters = reinterpret_cast<unsigned int*>(take(2 * ((Cs + 127) / 128) * 4));
+  w.counters = reinterpret_cast<unsigned int*>(take((2 * ((Cs + 127) / 128) + 4) * 4));  // + the feed's claim counter
+  {
+    // upper bound of the backward's tile count for any chunking (chunks are multiples of 128 classes, a dX tile
+    // covers at least 4 blocks of 64 classes): recompute + dW tiles, then dX tiles incl. per-chunk rounding
+    const int64_t T = (Cs + 127) / 128, dn = (D + 255) / 256;
+    w.items_cap = T * (w.Bp / kBNTile + dn) + ((B + 127) / 128) * dn * (2 * T + 1);
+    w.items = reinterpret_cast<int4*>(take(w.items_cap * 32));
+  }
   w.total = off;
   return w;
 }
@@ -202,7 +211,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
 constexpr int kLaunchRefused = 1;  // internal: the cooperative launch was refused, try the next schedule
 
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
-template <bool EXT, bool PAIR, bool TRACE = false>
+template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
                           int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st,
                           unsigned long long* trace = nullptr) {
@@ -259,8 +268,39 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     }
     pl.kind_mask = mask;
   }
+  {
+    static int dbg = -1;
+    if (dbg < 0) {
+      const char* e = getenv("ARCB_DEBUG_EPI");
+      dbg = e ? atoi(e) : 0;
+    }
+    pl.debug_epi = dbg;
+    static int rot = -1;  // ARCB_ROT: slot rotation per dealing round of the tile list (tuning aid)
+    if (rot < 0) {
+      const char* e = getenv("ARCB_ROT");
+      rot = e ? atoi(e) : 0;
+      if (rot < 0) rot = 0;
+    }
+    pl.rot = rot;
+  }
   pl.xw_done = W.counters + pl.n_chunks;
-  ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * 2 * pl.n_chunks, st));
+  pl.claim = W.counters + 2 * pl.n_chunks;
+  ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * (2 * pl.n_chunks + 1), st));
+  {
+    // the tile list: written once here, then read (one 32-byte record per tile) by every role of every CTA
+    const int nph = pl.n_chunks + pl.lag;
+    const long long total = phase_begin_of(pl, nph);
+    if (total > W.items_cap || total > 0x7fffffffll) {
+      fail(ARCB_ERR_WORKSPACE, "persistent backward: %lld tiles exceed the workspace's tile list (%lld)", total,
+           (long long)W.items_cap);
+      return kLaunchRefused;  // the per-chunk schedule needs no list
+    }
+    pl.items = W.items;
+    pl.total_items = static_cast<int>(total);
+    LaunchScope ls(ARCB_K_BWD_PREP, st);
+    bwd_items_kernel<<<nph, 128, 0, st>>>(pl, W.items);
+    ARCB_CUDA(cudaGetLastError());
+  }
 
   CUtensorMap tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw;
   const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
@@ -290,7 +330,7 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ar.s_ext = s; ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.dw_tma = dw_tma ? 1 : 0;
   ar.trace = trace;
 
-  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE>;
+  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE, DYN>;
   constexpr int kPSmemTotal = PCfg<PAIR>::kSmemTotal;
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -300,8 +340,7 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     ARCB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPSmemTotal));
     attr_set[dev] = true;
   }
-  long long total_items = 0;
-  for (int k = 0; k < pl.n_chunks; ++k) total_items += plan_nG(pl, k) + plan_nX(pl, k) + plan_nW(pl, k);
+  const long long total_items = pl.total_items;
   int groups = device_sm_count() / (PAIR ? 2 : 1);
   if (groups > total_items) groups = static_cast<int>(total_items);
   cudaLaunchConfig_t cfg = {};
@@ -371,6 +410,16 @@ int pair_mode() {
 }
 bool use_pair_gemm() { return pair_mode() == 2; }      // forward / unit-test GEMMs
 bool use_pair_backward() { return pair_mode() >= 1; }  // persistent backward
+
+// ARCB_DYN=0: CTA pairs take a fixed share of the tile list instead of claiming tiles as they go (A/B runs)
+bool use_dynamic_feed() {
+  static int dyn = -1;
+  if (dyn < 0) {
+    const char* e = getenv("ARCB_DYN");
+    dyn = (e && e[0] == '0') ? 0 : 1;
+  }
+  return dyn == 1;
+}
 
 std::atomic<int> g_bwd_mode{-1};  // -1: from the environment (default persistent), 0: per-chunk launches, 1: persistent
 bool use_persistent_backward() {
@@ -540,6 +589,38 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
 int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D) {
   if (B <= 0 || Cs <= 0 || D <= 0) return -1;
   return carve(nullptr, B, Cs, D).total;
+}
+
+// Classes per backward chunk for this problem: the persistent backward deals the tiles of a phase (one chunk's
+// recompute tiles mixed with an earlier chunk's dX / dW tiles) round-robin to the CTA pairs, so a phase whose
+// tile count sits just below a multiple of the number of pairs wastes the least; four chunks of bf16 G^T must
+// stay well inside L2, and short chunks pay too much fp32 reduce-add traffic per dX tile.
+int64_t arcb_suggest_chunk_classes(int64_t B, int64_t Cs, int64_t D) {
+  if (B <= 0 || Cs <= 0 || D <= 0) return -1;
+  const int64_t Bp = round_up(B, kBNTile);
+  const int groups = device_sm_count() / 2 > 0 ? device_sm_count() / 2 : 74;
+  const int64_t g_tiles_n = Bp / kBNTile, dn = (D + 255) / 256, x_tiles = ((B + 255) / 256) * dn;
+  const int64_t r_cap = (Cs + 255) / 256;
+  int64_t best_r = 0;
+  double best_cost = 1e30;
+  for (int64_t r = 16; r <= 64; ++r) {
+    if (4 * r * 256 * Bp * 2 > (48ll << 20) && best_r) break;  // four G^T buffers <= 48 MB of the 126 MB L2
+    int64_t want = (groups + x_tiles - 1) / x_tiles;
+    if (want > 4) want = 4;
+    int64_t per = (4 * r + want - 1) / want;
+    if (per < 4) per = 4;
+    const int64_t items = r * (g_tiles_n + dn) + x_tiles * ((4 * r + per - 1) / per);
+    if (items % groups == 0) continue;  // the dealing would never rotate: the same pairs get the dX tiles every phase
+    const int64_t rounds = (items + groups - 1) / groups;
+    const double waste = static_cast<double>(rounds * groups - items) / static_cast<double>(items);
+    const double cost = waste - 1e-4 * static_cast<double>(r);  // ties: the longer chunk
+    if (cost < best_cost) {
+      best_cost = cost;
+      best_r = r;
+    }
+  }
+  if (best_r > r_cap) best_r = r_cap;
+  return best_r * 256;
 }
 
 int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes) {
@@ -773,8 +854,12 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       int64_t pc = usable / (W.Bp * 2) / nbuf / 256 * 256;
       if (pc > round_up(Cs, 256)) pc = round_up(Cs, 256);
       if (pc >= 256) {
-        if (use_pair_backward())
+        if (use_pair_backward()) {
+          if (use_dynamic_feed())
+            return launch_bwd_persistent<false, true, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st,
+                                                                  trace);
           return launch_bwd_persistent<false, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, trace);
+        }
         return launch_bwd_persistent<false, false, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, trace);
       }
     }
@@ -782,8 +867,12 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       int64_t pc2 = pchunk / 256 * 256;
       if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
       if (pc2 >= 256) {
-        rc = ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
-                 : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+        if (use_dynamic_feed())
+          rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
+                   : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+        else
+          rc = ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
+                   : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
         if (rc != kLaunchRefused) return rc;
       }
     }

@@ -48,9 +48,11 @@ struct PCfg {
   // previous G^T box / dX / dW chunk to finish reading shared memory (the pair's smaller stages pay for it)
   static constexpr int kBufs = PAIR ? 2 : 1;
   static constexpr int kRowsOff = 2 * kBufs * kBM * 128;   // staged lse2 / labels behind the slots
-  static constexpr int kNumBars = 2 * kStages + 4 + 4 * kBufs;  // + slot_full / slot_free [2 warpgroups][kBufs]
+  static constexpr int kRing = 8;  // tile records a CTA pair may hold ahead of its slowest role (dynamic feed)
+  static constexpr int kNumBars = 2 * kStages + 4 + 4 * kBufs + 3 * kRing;  // + slot_full / slot_free [2 wg][kBufs], feed
   static constexpr int kBarOff = kStages * kStageBytes + kRowsOff + 256 * 8;
-  static constexpr int kSmemTotal = kBarOff + kNumBars * 8 + 16;  // no slack: the dynamic smem base is 1024 B aligned
+  static constexpr int kRingOff = kBarOff + kNumBars * 8 + 16;  // after the barriers and the TMEM slot; 16 B aligned
+  static constexpr int kSmemTotal = kRingOff + kRing * 32;      // no slack: the dynamic smem base is 1024 B aligned
   static constexpr int kCtas = PAIR ? 2 : 1;              // CTAs that work on one tile
 };
 constexpr int kPSlotBytes = kBM * 128;                   // 16 KB: [128 rows x 128 B], one per epilogue warpgroup
@@ -73,6 +75,11 @@ struct BwdPlan {
   unsigned int* g_done;      // [n_chunks], zeroed before the launch
   unsigned int* xw_done;     // [n_chunks], zeroed before the launch
   int kind_mask;             // debug: bit k set = tiles of kind k run (7 = all); anything else gives wrong results
+  unsigned int* claim;       // dynamic feed: next unclaimed list index (zeroed before the launch)
+  int rot;                   // slot rotation per dealing round (see ItemWalker), 0 = plain round-robin
+  int debug_epi;             // debug (ARCB_DEBUG_EPI): 1 = G epilogue skips math + smem stores, 2 = also skips the TMEM loads
+  const int4* items;         // [total_items][2] the global tile list, written by bwd_items_kernel before the launch
+  int total_items;
 };
 
 struct BwdArgs {
@@ -105,6 +112,9 @@ __device__ __forceinline__ unsigned long long* trace_slot(const BwdArgs& ar, int
 
 struct Item {
   int kind, chunk, m_blk, n_blk, kb0, kb1;
+  unsigned int target;  // X / W tile: value of g_done[chunk] that makes its G^T complete;
+                        // G tile: value of xw_done[chunk - nbuf] that frees the scratch buffer it overwrites
+  int buf;              // scratch buffer of the chunk (chunk % nbuf)
 };
 
 __host__ __device__ inline int plan_rows(const BwdPlan& pl, int k) {
@@ -146,64 +156,201 @@ __device__ __forceinline__ bool pick_b(int j, int n_b, int total, int& idx_b, in
   return after > before;
 }
 
-// Every role of a CTA (or CTA pair) walks the same sub-sequence of the global list: tiles first, first + step, ...
-struct ItemWalker {
-  int phase, phase_begin, phase_size, next_it;
-  int stride;
-  __device__ void init(const BwdPlan& pl, int first, int step) {
-    phase = 0;
-    phase_begin = 0;
-    phase_size = phase_items(pl, 0);
-    next_it = first;
-    stride = step;
-  }
-  __device__ bool next(const BwdPlan& pl, Item& it) {
-    const int nph = pl.n_chunks + pl.lag;
-    while (phase < nph && next_it >= phase_begin + phase_size) {
-      phase_begin += phase_size;
-      ++phase;
-      if (phase < nph) phase_size = phase_items(pl, phase);
-    }
-    if (phase >= nph) return false;
-    const int j = next_it - phase_begin;
-    const int n_xw = phase_nXW(pl, phase);
-    int i_xw, i_g;
-    if (!pick_b(j, n_xw, phase_size, i_xw, i_g)) {  // a G tile of chunk `phase`
-      const int k = phase;
-      const int gm = plan_gm(pl, k);
-      it.kind = kItemG;
-      it.chunk = k;
-      it.m_blk = i_g % gm;
-      it.n_blk = i_g / gm;
+// Item j of phase `phase` (the arithmetic of the global list: integer divisions, done once per item by
+// bwd_items_kernel instead of by every role of every CTA in front of every tile).
+__device__ inline void make_item(const BwdPlan& pl, int phase, int j, Item& it) {
+  const int ctas = pl.tile_rows / kBM;
+  const int phase_size = phase_items(pl, phase);
+  const int n_xw = phase_nXW(pl, phase);
+  int i_xw, i_g;
+  if (!pick_b(j, n_xw, phase_size, i_xw, i_g)) {  // a G tile of chunk `phase`
+    const int k = phase;
+    const int gm = plan_gm(pl, k);
+    it.kind = kItemG;
+    it.chunk = k;
+    it.m_blk = i_g % gm;
+    it.n_blk = i_g / gm;
+    it.kb0 = 0;
+    it.kb1 = pl.g_kb;
+    const int kp = k - pl.nbuf;
+    it.target = kp >= 0 ? static_cast<unsigned>(ctas * (plan_nX(pl, kp) + plan_nW(pl, kp))) : 0u;
+  } else {  // an X or W tile of chunk `phase - lag`
+    const int k = phase - pl.lag;
+    const int gm = plan_gm(pl, k);
+    const int nx = plan_nX(pl, k);
+    it.chunk = k;
+    int i_x, i_w;
+    if (pick_b(i_xw, nx, n_xw, i_x, i_w)) {
+      it.kind = kItemX;
+      it.m_blk = i_x % pl.x_tiles_m;
+      const int r = i_x / pl.x_tiles_m;
+      it.n_blk = r % pl.x_tiles_n;
+      const int ks = r / pl.x_tiles_n;
+      const int kbt = (plan_rows(pl, k) + kBK - 1) / kBK;
+      it.kb0 = ks * pl.x_kb_per_split;
+      it.kb1 = min(it.kb0 + pl.x_kb_per_split, kbt);
+    } else {
+      it.kind = kItemW;
+      it.m_blk = i_w % gm;
+      it.n_blk = i_w / gm;
       it.kb0 = 0;
-      it.kb1 = pl.g_kb;
-    } else {  // an X or W tile of chunk `phase - lag`
-      const int k = phase - pl.lag;
-      const int gm = plan_gm(pl, k);
-      const int nx = plan_nX(pl, k);
-      it.chunk = k;
-      int i_x, i_w;
-      if (pick_b(i_xw, nx, n_xw, i_x, i_w)) {
-        it.kind = kItemX;
-        it.m_blk = i_x % pl.x_tiles_m;
-        const int r = i_x / pl.x_tiles_m;
-        it.n_blk = r % pl.x_tiles_n;
-        const int ks = r / pl.x_tiles_n;
-        const int kbt = (plan_rows(pl, k) + kBK - 1) / kBK;
-        it.kb0 = ks * pl.x_kb_per_split;
-        it.kb1 = min(it.kb0 + pl.x_kb_per_split, kbt);
-      } else {
-        it.kind = kItemW;
-        it.m_blk = i_w % gm;
-        it.n_blk = i_w / gm;
-        it.kb0 = 0;
-        it.kb1 = pl.w_kb;
-      }
+      it.kb1 = pl.w_kb;
     }
-    next_it += stride;
+    it.target = 2u * static_cast<unsigned>(ctas * plan_nG(pl, k));
+  }
+  it.buf = it.chunk % pl.nbuf;
+}
+
+// Items in phases [0, p): every chunk but the last has the same tile counts.
+__host__ __device__ inline long long phase_begin_of(const BwdPlan& pl, int p) {
+  const int nc = pl.n_chunks;
+  auto prefix = [&](int k, bool g) -> long long {  // tiles of chunks [0, k)
+    if (k <= 0) return 0;
+    if (k > nc) k = nc;
+    const long long full = g ? plan_nG(pl, 0) : plan_nX(pl, 0) + plan_nW(pl, 0);
+    if (k < nc) return full * k;
+    const long long tail = g ? plan_nG(pl, nc - 1) : plan_nX(pl, nc - 1) + plan_nW(pl, nc - 1);
+    return full * (nc - 1) + tail;
+  };
+  return prefix(p, true) + prefix(p - pl.lag, false);
+}
+
+// One block per phase writes that phase's items (two int4 each) into the table every role reads.
+__global__ void __launch_bounds__(128) bwd_items_kernel(const BwdPlan pl, int4* __restrict__ out) {
+  const int p = blockIdx.x;
+  const long long begin = phase_begin_of(pl, p);
+  const int n = phase_items(pl, p);
+  for (int j = threadIdx.x; j < n; j += blockDim.x) {
+    Item it;
+    make_item(pl, p, j, it);
+    out[2 * (begin + j)] = make_int4(it.kind, it.chunk, it.m_blk, it.n_blk);
+    out[2 * (begin + j) + 1] = make_int4(it.kb0, it.kb1, static_cast<int>(it.target), it.buf);
+  }
+}
+
+// Every role of a CTA (or CTA pair) walks the same sub-sequence of the global list: tiles first, first + step, ...
+// The record of the following tile is requested while the current one is being worked on.
+struct ItemWalker {
+  int round_base, slot, stride, rot_step;  // next record = round_base + slot; the slot rotates from round to round
+  int4 a, b;
+  __device__ __forceinline__ void fetch(const BwdPlan& pl) {
+    const int n = round_base + slot;
+    if (n < pl.total_items) {
+      a = __ldg(pl.items + 2 * static_cast<size_t>(n));
+      b = __ldg(pl.items + 2 * static_cast<size_t>(n) + 1);
+    }
+  }
+  __device__ __forceinline__ void init(const BwdPlan& pl, int first, int step) {
+    round_base = 0;
+    slot = first;
+    stride = step;
+    // the list is dealt in rounds of `stride` consecutive tiles; which tile of a round a CTA (pair) takes moves
+    // by a fixed odd-ish step every round, so that the periodic G / X / W pattern of the list cannot line up with
+    // the dealing and hand one CTA the expensive kind round after round (pl.rot = 0: plain round-robin)
+    rot_step = pl.rot % step;
+    fetch(pl);
+  }
+  // false once this CTA's share of the list is exhausted (the last, partial round may not reach its slot)
+  __device__ __forceinline__ bool next(const BwdPlan& pl, Item& it) {
+    while (round_base < pl.total_items && round_base + slot >= pl.total_items) advance(pl);
+    if (round_base >= pl.total_items) return false;
+    it.kind = a.x; it.chunk = a.y; it.m_blk = a.z; it.n_blk = a.w;
+    it.kb0 = b.x; it.kb1 = b.y; it.target = static_cast<unsigned>(b.z); it.buf = b.w;
+    advance(pl);
     return true;
   }
+  __device__ __forceinline__ void advance(const BwdPlan& pl) {
+    round_base += stride;
+    slot += rot_step;
+    if (slot >= stride) slot -= stride;
+    fetch(pl);
+  }
 };
+
+// Where a role gets its tiles from.
+//   static  (DYN = false): the CTA's fixed share of the list, see ItemWalker.
+//   dynamic (DYN = true, CTA pairs): one thread of the pair (the follower's otherwise idle warp 1) claims the next
+//     list index with an atomic whenever a ring slot is free, fetches the record and pushes it into the ring of
+//     BOTH CTAs (st.async counted on each CTA's feed_full barrier).  Every role reads the records in ring order and
+//     reports on the claimer's feed_empty barrier.  Tiles are still started in list order, so every dependency
+//     (a counter a tile waits for) belongs to a tile with a smaller index that some pair has already claimed and
+//     will reach without needing anything later in the list: no deadlock.  A pair that falls behind simply claims
+//     less, which is what the fixed dealing could not do.
+template <bool DYN>
+struct TileFeed {
+  ItemWalker w;            // static
+  const int4* ring;        // dynamic: this CTA's ring [kRing][2]
+  uint64_t* full;          // this CTA's feed_full[kRing]
+  uint32_t empty_remote;   // shared::cluster address of feed_empty[0] in the claimer's CTA
+  uint64_t* taken;         // claimer's CTA, producer only: feed_taken[kRing]
+  uint32_t n;
+  bool armer, collective;
+  // armer: the one thread per CTA that announces the 32 bytes of every record on feed_full (the TMA producer);
+  // collective: all 32 lanes of a warp call next() together (epilogue warps) and count as ONE reader.
+  __device__ __forceinline__ void init(const BwdPlan& pl, int first, int step, uint8_t* ring_smem, uint64_t* full_bars,
+                                       uint64_t* empty_bars, bool armer_, bool collective_,
+                                       uint64_t* taken_bars = nullptr) {
+    if constexpr (!DYN) {
+      w.init(pl, first, step);
+    } else {
+      ring = reinterpret_cast<const int4*>(ring_smem);
+      full = full_bars;
+      empty_remote = mapa_u32(smem_u32(empty_bars), 1);
+      n = 0;
+      armer = armer_;
+      collective = collective_;
+      taken = taken_bars;
+    }
+  }
+  __device__ __forceinline__ bool next(const BwdPlan& pl, Item& it) {
+    if constexpr (!DYN) {
+      return w.next(pl, it);
+    } else {
+      const uint32_t slot = n % PCfg<true>::kRing, use = n / PCfg<true>::kRing;
+      ++n;
+      if (armer) mbar_arrive_expect_tx(&full[slot], 32);
+      mbar_wait(&full[slot], use & 1u, 0xb00u + slot);
+      const int4 a = ring[2 * slot], b = ring[2 * slot + 1];
+      if (collective) __syncwarp();
+      if (!collective || lane_id() == 0) mbar_arrive_cluster(empty_remote + slot * 8);
+      if (taken) mbar_arrive(&taken[slot]);  // the pair has started on this tile: the claimer may fetch the next one
+      it.kind = a.x; it.chunk = a.y; it.m_blk = a.z; it.n_blk = a.w;
+      it.kb0 = b.x; it.kb1 = b.y; it.target = static_cast<unsigned>(b.z); it.buf = b.w;
+      return a.x >= 0;
+    }
+  }
+};
+
+// The claimer of a CTA pair (dynamic feed): runs until it has handed out the end-of-list record.
+// A tile is claimed only once the pair's producer has started on the previous one: claiming further ahead would
+// park tiles that other pairs' tiles depend on behind this pair's backlog (measured: counter waits x4).  The ring
+// is deeper than that look-ahead only because the slowest role (the epilogue) reads a record a few tiles later.
+__device__ __forceinline__ void feed_claim_loop(const BwdPlan& pl, uint8_t* ring_smem, uint64_t* full_bars,
+                                                uint64_t* empty_bars, uint64_t* taken_bars) {
+  constexpr int kRing = PCfg<true>::kRing;
+  for (uint32_t n = 0;; ++n) {
+    const uint32_t slot = n % kRing, use = n / kRing;
+    mbar_wait(&empty_bars[slot], (use & 1u) ^ 1u, 0xc00u + slot);  // every role of both CTAs has read the old record
+    if (n >= 1) {
+      const uint32_t ps = (n - 1) % kRing, pu = (n - 1) / kRing;
+      mbar_wait(&taken_bars[ps], pu & 1u, 0xd00u + ps);
+    }
+    const unsigned int idx = atomicAdd(pl.claim, 1u);
+    int4 a = make_int4(-1, 0, 0, 0), b = make_int4(0, 0, 0, 0);
+    if (idx < static_cast<unsigned int>(pl.total_items)) {
+      a = __ldg(pl.items + 2 * static_cast<size_t>(idx));
+      b = __ldg(pl.items + 2 * static_cast<size_t>(idx) + 1);
+    }
+    const uint32_t dst = smem_u32(ring_smem) + slot * 32, bar = smem_u32(&full_bars[slot]);
+#pragma unroll
+    for (uint32_t cta = 0; cta < 2; ++cta) {
+      const uint32_t d = mapa_u32(dst, cta), m = mapa_u32(bar, cta);
+      st_async_v4(d, a, m);
+      st_async_v4(d + 16, b, m);
+    }
+    if (a.x < 0) break;
+  }
+}
 
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
@@ -265,7 +412,7 @@ __device__ __forceinline__ void ld3(void* dst, const CUtensorMap* tm, uint32_t b
   }
 }
 
-template <bool EXT, bool PAIR, bool TRACE>
+template <bool EXT, bool PAIR, bool TRACE, bool DYN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [Cs, Dp]   box 64 x 128  (A of G)
                       const __grid_constant__ CUtensorMap tmXhatK,   // x_hat [B, Dp]    box 64 x 256  (B of G)
@@ -294,6 +441,11 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   constexpr int kBufs = C::kBufs;
   uint64_t* slot_full = bars + 2 * kPStages + 4;              // [wg][buf] warpgroup -> its store issuer: box is in smem
   uint64_t* slot_free = bars + 2 * kPStages + 4 + 2 * kBufs;  // [wg][buf] store issuer -> warpgroup: box has been read
+  uint64_t* feed_full = bars + 2 * kPStages + 4 + 4 * kBufs;  // dynamic feed: record n is in ring slot n % kRing
+  uint64_t* feed_empty = feed_full + C::kRing;                // ... and every role has read it (claimer's CTA only)
+  uint64_t* feed_taken = feed_empty + C::kRing;               // ... and the claimer's own producer has started on it
+  uint8_t* ring_smem = smem + C::kRingOff;
+  static_assert(!DYN || PAIR, "the dynamic feed uses the follower CTA's idle warp 1 as claimer");
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + C::kNumBars);
   const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;   // position inside the CTA pair
   const bool leader = rank == 0;
@@ -327,6 +479,12 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       mbar_init(&slot_full[i], kWgThreads / 32);
       mbar_init(&slot_free[i], 1);
     }
+    for (int i = 0; i < C::kRing; ++i) {
+      mbar_init(&feed_full[i], 1);  // the CTA's producer thread (+ the 32 record bytes)
+      // readers of a record: producer, 2 store issuers and 8 epilogue warps per CTA + the leader's MMA issuer
+      mbar_init(&feed_empty[i], 2 * (3 + kEpiThreads / 32) + 1);
+      mbar_init(&feed_taken[i], 1);
+    }
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -346,8 +504,8 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   if (warp == 0) {
     if (lane == 0) {
       // ------------------------------ TMA producer ------------------------------
-      ItemWalker w;
-      w.init(pl, walk_first, walk_step);
+      TileFeed<DYN> w;
+      w.init(pl, walk_first, walk_step, ring_smem, feed_full, feed_empty, true, false, leader ? nullptr : feed_taken);
       Item it;
       int stage = 0;
       uint32_t phase = 0;
@@ -359,7 +517,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         long long w_empty = 0;
         const long long t_flag = TRACE ? clock64() : 0;
         if (it.kind != kItemG && (pl.kind_mask & 1)) {  // G^T of this chunk must be complete and visible
-          wait_counter(pl.g_done + it.chunk, 2u * C::kCtas * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x500u);
+          wait_counter(pl.g_done + it.chunk, it.target, 0x500u);
           fence_proxy_async_all();
         }
         if (tr) {
@@ -368,7 +526,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         }
         const int mblk = it.m_blk * C::kCtas + rank;            // this CTA's 128-row block of the tile
         const int c0 = it.chunk * pl.chunk_rows;                // first class of the chunk in the shard
-        const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;  // first row of the chunk's scratch buffer
+        const int buf_row = it.buf * pl.chunk_rows;  // first row of the chunk's scratch buffer
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           if (tr) {
             const long long t0 = clock64();
@@ -411,8 +569,8 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   } else if (warp == 1) {
     if (lane == 0 && leader) {
       // ------------------------------ MMA issuer (pair: leader only) --------------------------------
-      ItemWalker w;
-      w.init(pl, walk_first, walk_step);
+      TileFeed<DYN> w;
+      w.init(pl, walk_first, walk_step, ring_smem, feed_full, feed_empty, false, false);
       Item it;
       int stage = 0;
       uint32_t phase = 0;
@@ -469,26 +627,28 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
+    } else if (DYN && lane == 0 && !leader) {
+      // ------------------------------ tile claimer of the pair (dynamic feed) ------------------------
+      feed_claim_loop(pl, ring_smem, feed_full, feed_empty, feed_taken);
     }
   } else if (warp == 2 || warp == 3) {
     if (lane == 0) {
       // ---------------- G^T store issuer of epilogue warpgroup (3 - warp) ----------------
       const int wg = 3 - warp;
-      ItemWalker w;
-      w.init(pl, walk_first, walk_step);
+      TileFeed<DYN> w;
+      w.init(pl, walk_first, walk_step, ring_smem, feed_full, feed_empty, false, false);
       Item it;
       uint32_t n_box = 0;  // boxes this issuer has sent so far (two per G tile); box n lives in buffer n % kBufs
       while (w.next(pl, it)) {
         if (it.kind != kItemG || it.kb0 >= it.kb1 || !(pl.kind_mask & 1)) continue;
-        const int buf_row = (it.chunk % pl.nbuf) * pl.chunk_rows;
+        const int buf_row = it.buf * pl.chunk_rows;
         const int mblk = it.m_blk * C::kCtas + rank;
         for (int bx = 0; bx < 2; ++bx, ++n_box) {
           const uint32_t buf = n_box % kBufs, use = n_box / kBufs;
           uint8_t* slot = epi_smem + (wg * kBufs + buf) * kPSlotBytes;
           mbar_wait(&slot_full[wg * kBufs + buf], use & 1u, 0x600u + wg);
           if (bx == 0 && it.chunk >= pl.nbuf && (pl.kind_mask & 6) == 6) {  // the X / W tiles that last read this scratch buffer must be done
-            const int kp = it.chunk - pl.nbuf;
-            wait_counter(pl.xw_done + kp, C::kCtas * static_cast<unsigned>(plan_nX(pl, kp) + plan_nW(pl, kp)), 0x700u);
+            wait_counter(pl.xw_done + (it.chunk - pl.nbuf), it.target, 0x700u);
             fence_proxy_async_all();
           }
           tma_store_2d_hint(&tmGtSt, slot, it.n_blk * kPBN + wg * 128 + bx * 64, buf_row + mblk * kBM, kEvictLast);
@@ -510,8 +670,8 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
     const int wg_tid = epi_tid & 127;
     float* lse_s = reinterpret_cast<float*>(epi_smem + C::kRowsOff) + wg * 128;  // this warpgroup's 128 samples
     int* lbl_s = reinterpret_cast<int*>(epi_smem + C::kRowsOff + 256 * 4) + wg * 128;
-    ItemWalker w;
-    w.init(pl, walk_first, walk_step);
+    TileFeed<DYN> w;
+    w.init(pl, walk_first, walk_step, ring_smem, feed_full, feed_empty, false, true);
     Item it;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -550,7 +710,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         pw.Dp = pl.Dp;
         pw.use_tma = ar.dw_tma;
         if (pl.kind_mask & 1)
-          wait_counter(pl.g_done + it.chunk, 2u * C::kCtas * static_cast<unsigned>(plan_nG(pl, it.chunk)), 0x510u);
+          wait_counter(pl.g_done + it.chunk, it.target, 0x510u);
         TileCoord tcw;
         tcw.m_blk = it.m_blk * C::kCtas + rank;
         tcw.n_blk = it.n_blk;
@@ -629,7 +789,12 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
             const int c = wg * 128 + cl;          // column inside the tile
             const int col0 = it.n_blk * kPBN + c;
             float v[32];
+            if (pl.debug_epi >= 2) continue;
             tmem_ld32(taddr + c, v);
+            if (pl.debug_epi == 1) {
+              tsum += v[0] + v[31];
+              continue;
+            }
             float g[32];
             EpiBwdG<EXT>::chunk_math(p, gscale, lse_s + cl, lbl_s[cl + lane], col0, cls, tile_cls0, row_ok, row_local,
                                      v, g);

@@ -212,6 +212,14 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// 16-byte store into the shared memory of a CTA of this cluster (possibly this one); the bytes are counted on the
+// mbarrier at `bar_cluster_addr`, which must live in the same CTA as the destination
+__device__ __forceinline__ void st_async_v4(uint32_t dst_cluster_addr, int4 v, uint32_t bar_cluster_addr) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(
+                   dst_cluster_addr),
+               "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(bar_cluster_addr)
+               : "memory");
+}
 // bulk tensor loads of a CTA pair: data lands in THIS CTA's smem, the bytes are counted on the mbarrier at
 // `bar_cluster_addr`, which may live in the peer CTA (the pair leader).
 __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* tm, uint32_t bar_cluster_addr,

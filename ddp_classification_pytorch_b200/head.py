@@ -29,10 +29,10 @@ from torch.nn import Parameter
 
 from . import _lib
 
-# classes per backward chunk: the persistent backward keeps FOUR chunks of bf16 dLoss/dcos in flight
-# (B=1024: 4 x 19.4 MB), which together with the matching w_hat rows stays inside the 126 MB L2;
-# 256 * 37 rows = 37 tile rows per CTA pair and chunk (measured best among 4.8k .. 19k on B200).
-DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 256 * 37))
+# classes per backward chunk: the persistent backward keeps FOUR chunks of bf16 dLoss/dcos in flight, which
+# together with the matching w_hat rows must stay inside the 126 MB L2.  0 = ask the library
+# (arcb_suggest_chunk_classes: e.g. 256 * 19 at B=1024, D=512); ARCB_CHUNK_CLASSES overrides it for tuning runs.
+DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 0))
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -138,7 +138,9 @@ class CudaEngine:
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
     @staticmethod
-    def _scratch_for(B, Cs, device, chunk_classes):
+    def _scratch_for(B, Cs, D, device, chunk_classes):
+        if chunk_classes <= 0:
+            chunk_classes = _lib.lib().arcb_suggest_chunk_classes(B, Cs, D)
         chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
         nbytes = _lib.lib().arcb_scratch_bytes(B, int(os.environ.get("ARCB_SCRATCH_BUFS", 4)) * chunk)  # four buffers by default
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
@@ -211,7 +213,7 @@ class CudaEngine:
                                "construct the head with cache_normalized_weight=False for that pattern")
         dev = ws.device
         Dp = L.arcb_padded_dim(D)
-        scratch, scratch_bytes = self._scratch_for(B, Cs, dev, cfg["chunk_classes"])
+        scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
         dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
         dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
         _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),
@@ -360,7 +362,7 @@ class ArcMarginProduct(nn.Module):
         self.sin_m = math.sin(m)
         self.th = math.cos(math.pi - m)
         self.mm = math.sin(math.pi - m) * m
-        self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES
+        self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES  # 0: chosen per call by the library
         self.aux = {}
         self._engine = _engine if _engine is not None else CudaEngine()
         self._wcache = _WeightCache() if cache_normalized_weight else None

@@ -69,6 +69,10 @@ int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D);
  * falls back to one kernel launch per GEMM and chunk). */
 int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes);
 
+/* Chunk length (classes, a multiple of 256) that suits the persistent backward for this problem on the current
+ * device: size the scratch as arcb_scratch_bytes(B, 4 * arcb_suggest_chunk_classes(B, Cs, D)). */
+int64_t arcb_suggest_chunk_classes(int64_t B, int64_t Cs, int64_t D);
+
 /* ---- fused forward on one class shard: arc_main.py:159-172 + the softmax statistics of :245 ----
  * x [B, D] fp32, w [Cs, D] fp32 (the shard's rows of ArcMarginProduct.weight), labels [B] int64.
  * Writes stats [B, 4] fp32 = (row max of logits * log2e, sum 2^(logit*log2e - max), target logit

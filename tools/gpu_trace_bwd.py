@@ -6,7 +6,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.ins
 import numpy as np, torch
 from ddp_classification_pytorch_b200 import _lib
 from ddp_classification_pytorch_b200.head import CudaEngine
-B, D, C = 1024, 512, int(os.environ.get("TRACE_C", 200000))
+B, D, C = int(os.environ.get("TRACE_B", 1024)), int(os.environ.get("TRACE_D", 512)), int(os.environ.get("TRACE_C", 200000))
 chunk = int(os.environ.get("ARCB_CHUNK_CLASSES", 256 * 29))
 g = torch.Generator(device="cuda").manual_seed(0)
 x = torch.randn(B, D, generator=g, device="cuda"); w = (torch.rand(C, D, generator=g, device="cuda") - 0.5) * 0.01
@@ -15,7 +15,7 @@ eng = CudaEngine(); L = _lib.lib()
 cfg = {"s": 30.0, "m": 0.5, "easy_margin": False, "class_offset": 0, "chunk_classes": chunk}
 stats, state = eng.shard_forward(x, w, y, cfg)
 lse, zt, loss = eng.merge_loss(stats, 1, B)
-Bq, Cs, Dq, ws, ws_bytes = state
+Bq, Cs, Dq, ws, ws_bytes = state[:5]
 Dp = L.arcb_padded_dim(D)
 nbytes = L.arcb_scratch_bytes(B, 4 * chunk) + (1 << 20)
 scratch = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")

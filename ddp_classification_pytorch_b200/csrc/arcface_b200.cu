@@ -178,7 +178,9 @@ int launch_l2norm(const float* x, int64_t rows, int64_t D, int64_t ldx, __nv_bfl
 // Steps shared by the fused and the materialising forward: normalise, target preparation.
 int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
                    int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy, void* ws_ptr,
-                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, bool w_prenormalised = false) {
+                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, int w_mode = 0) {
+  // w_mode: 0 = normalise the weight here, 1 = the workspace already holds w_hat / inv_norm of this weight,
+  //         2 = the forward GEMM kernel normalises it on the fly (launch_gemm_norm)
   int rc = check_dims(B, Cs, D);
   if (rc) return rc;
   if (!x || !w || !labels || !ws_ptr) return fail(ARCB_ERR_INVALID, "null pointer argument");
@@ -191,16 +193,21 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
                 (long long)ws_bytes);
   rc = launch_l2norm(x, B, D, ldx, W.xhat, W.Dp, W.inv_nx, st, ARCB_K_L2NORM_X);
   if (rc) return rc;
-  if (!w_prenormalised) {  // otherwise the workspace already holds w_hat / inv_norm of exactly this w
+  if (w_mode == 0) {
     rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
     if (rc) return rc;
+  } else if (w_mode == 2) {  // per-B-tile "rows normalised" counters of the fused kernel
+    ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * ((Cs + kBNTile - 1) / kBNTile), st));
   }
   const double md = static_cast<double>(m);
   const float cos_m = static_cast<float>(cos(md)), sin_m = static_cast<float>(sin(md));
   const float th = static_cast<float>(cos(M_PI - md)), mm = static_cast<float>(sin(M_PI - md) * md);
   const int blocks = static_cast<int>((W.Bp + 7) / 8);
   LaunchScope ls(ARCB_K_TARGET_PREP, st);
-  target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.inv_nx, W.inv_nw, (int)B, (int)W.Bp, (int)D, Cs,
+  // the target row's norm is always taken from the row itself (inv_nw = nullptr): the weight may still be being
+  // normalised (w_mode 2), and the target logit must not depend on which of the three modes produced w_hat
+  target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.inv_nx, nullptr, (int)B,
+                                             (int)W.Bp, (int)D, Cs,
                                              class_offset, s, cos_m, sin_m, th, mm, easy, W.lbl_local, W.sub, W.zt,
                                              W.dphi, W.cos_t);
   ARCB_CUDA(cudaGetLastError());
@@ -421,6 +428,19 @@ bool use_dynamic_feed() {
   return dyn == 1;
 }
 
+// F.normalize(weight) inside the forward GEMM kernel: 0 = never (separate kernel), 1 = where it pays (default),
+// 2 = whenever the shape allows it.  -1 = not yet read from the environment (ARCB_FUSE_NORM).
+std::atomic<int> g_fuse_mode{-1};
+int forward_norm_mode() {
+  int mode = g_fuse_mode.load(std::memory_order_relaxed);
+  if (mode < 0) {
+    const char* e = getenv("ARCB_FUSE_NORM");
+    mode = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+    g_fuse_mode.store(mode, std::memory_order_relaxed);
+  }
+  return mode;
+}
+
 std::atomic<int> g_bwd_mode{-1};  // -1: from the environment (default persistent), 0: per-chunk launches, 1: persistent
 bool use_persistent_backward() {
   int mode = g_bwd_mode.load(std::memory_order_relaxed);
@@ -494,6 +514,12 @@ int64_t arcb_padded_dim(int64_t D) { return round_up(D, 64); }
 int arcb_set_pair_mode(int mode) {
   if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "pair mode must be 0, 1 or 2");
   g_pair_mode.store(mode, std::memory_order_relaxed);
+  return ARCB_OK;
+}
+
+int arcb_set_forward_norm_mode(int mode) {
+  if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "forward norm mode must be 0, 1 or 2");
+  g_fuse_mode.store(mode, std::memory_order_relaxed);
   return ARCB_OK;
 }
 
@@ -635,13 +661,47 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (!stats) return fail(ARCB_ERR_INVALID, "null stats pointer");
   Workspace W;
+  // F.normalize(weight) inside the GEMM kernel (ARCB_FUSE_NORM=0 switches back to the separate kernel); needs
+  // 16-byte aligned rows like the vector path of the stand-alone kernel, D <= 2048 and the one-CTA tile shape
+  const int fuse_env = forward_norm_mode();
+  // measured on B200: the overlap pays (4-9 % of the forward) where the GEMM is long enough to hide the pass but
+  // short enough that eight extra warps per SM do not cost it more than the pass itself: 512 <= B <= 1024, many
+  // classes.  ARCB_FUSE_NORM=2 forces it for every shape (tests).
+  const bool shape_ok = fuse_env == 2 || (B >= 512 && B <= 1024 && Cs >= 65536);
+  bool fuse = fuse_env && shape_ok && !w_prenormalised && !use_pair_gemm() && (D % 4 == 0) && (ldw % 4 == 0) &&
+              D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
   int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
-                          w_prenormalised);
+                          w_prenormalised ? 1 : (fuse ? 2 : 0));
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
   cudaError_t e;
-  {
+  if (fuse) {
+    NormArgs na;
+    na.w = w; na.ldw = ldw; na.rows = Cs; na.D = (int)D; na.Dp = (int)W.Dp; na.what = W.what; na.inv_nw = W.inv_nw;
+    na.done = W.counters;
+    const int tiles_m = (int)((B + kBM - 1) / kBM);
+    const int ahead = (device_sm_count() + tiles_m - 1) / tiles_m + 2;  // a CTA's last tile is at most this far from the end
+    na.lookahead = ahead > 64 ? ahead : 64;                             // 64 B tiles of w_hat = 16 MB at D = 512
+    {
+      static int look = -1;  // ARCB_NORM_LOOK: override (tuning aid)
+      if (look < 0) {
+        const char* e1 = getenv("ARCB_NORM_LOOK");
+        look = e1 ? atoi(e1) : 0;
+      }
+      if (look > 0) na.lookahead = look > ahead ? look : ahead;
+    }
+    {
+      LaunchScope ls(ARCB_K_FWD_GEMM, st);
+      e = launch_gemm_norm<EpiFwdStats, 4>(a, b, B, Cs, W.Dp, ep, na, st);
+    }
+    if (e != cudaSuccess) {  // the grid cannot be made co-resident right now: two kernels instead
+      fuse = false;
+      rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
+      if (rc) return rc;
+    }
+  }
+  if (!fuse) {
     LaunchScope ls(ARCB_K_FWD_GEMM, st);
     static int fwd_stages = 0;
     if (!fwd_stages) {

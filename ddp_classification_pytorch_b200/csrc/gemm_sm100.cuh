@@ -23,6 +23,7 @@
 #include <stdlib.h>
 
 #include "ptx_sm100.cuh"
+#include "rowwise.cuh"
 
 namespace arcb {
 
@@ -39,6 +40,24 @@ struct GemmSched {
   int kb_per_split;  // ceil(kb_total / k_splits)
   int debug_split_b; // experiment switch (ARCB_DEBUG_SPLIT_B): load a K-major B tile as four boxes
 };
+
+// Work of the optional normaliser warps (NORM = true: warps 12..15, forward GEMM only): F.normalize(self.weight)
+// (arc_main.py:159) runs INSIDE the GEMM kernel that consumes it, so the HBM-bound pass hides behind the tensor-bound
+// one.  The rows are cut into units of 64; CTA c normalises units c, c + grid, ... (16 rows per warp) and bumps
+// done[unit / 4]; the TMA producer of a tile waits until done[n_blk] has reached 16 (all 256 rows of its B tile).
+// The normalisers never wait for anything but the pace of their own CTA's GEMM (they stay at most `lookahead`
+// B tiles ahead of it, so that w_hat is still in L2 when the bulk loads come for it): no cyclic dependency.
+struct NormArgs {
+  const float* w;
+  int64_t ldw, rows;
+  int D, Dp;
+  __nv_bfloat16* what;
+  float* inv_nw;
+  unsigned int* done;  // [tiles_n], zeroed before the launch
+  int lookahead;       // B tiles
+};
+constexpr int kNormUnitRows = 64;
+constexpr int kNormWarps = 8;  // normaliser warps per CTA (NORM kernels): 8 x 4 rows x 2 KB = 64 KB of loads in flight per SM
 
 struct TileCoord {
   int m_blk, n_blk, kb0, kb1;
@@ -66,11 +85,14 @@ struct GemmSmem {
   static constexpr int kTotal = kBarOff + kNumBars * 8 + 16 + 1024;  // +1024: manual alignment slack
 };
 
-template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN, bool NORM = false>
+__global__ void __launch_bounds__(kGemmThreads + (NORM ? 32 * kNormWarps : 0), 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const __grid_constant__ CUtensorMap tmC, const GemmSched sc, const typename Epi::Params ep) {
+                  const __grid_constant__ CUtensorMap tmC, const GemmSched sc, const typename Epi::Params ep,
+                  const NormArgs na) {
   using L = GemmSmem<Epi, BN, STAGES>;
+  static_assert(!NORM || (BN == 256 && !B_MN), "the normaliser produces K-major B tiles of 256 rows");
+  __shared__ int norm_progress;  // NORM: B tile the CTA's producer is working on (read by the normaliser warps)
   static_assert(BN == 128 || BN == 256, "accumulator double-buffer must be a power of two <= 512 columns");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -98,6 +120,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], kEpiThreads / 32);
     }
+    if (NORM) norm_progress = 0;
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -118,6 +141,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const TileCoord tc = decode_tile(sc, t);
+        if constexpr (NORM) {  // all 256 rows of this B tile must be normalised and visible to the bulk loads
+          *reinterpret_cast<volatile int*>(&norm_progress) = tc.n_blk;
+          wait_counter(na.done + tc.n_blk, static_cast<unsigned>(kNormWarps * (BN / kNormUnitRows)), 0xe00u);
+          fence_proxy_async_all();
+        }
         for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u, 0x100u + stage);
           mbar_arrive_expect_tx(&full[stage], L::kStageBytes);
@@ -188,6 +216,29 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tc_commit(&tfull[acc]);  // accumulator complete -> epilogue
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+  } else if (NORM && warp >= 4 + kEpiThreads / 32) {
+    // ------------------ normaliser warps: F.normalize(weight) for the tiles still to come ------------------
+    const int nw = warp - (4 + kEpiThreads / 32);
+    const int64_t units = (static_cast<int64_t>(sc.tiles_n) * BN) / kNormUnitRows;
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+      const int blk = static_cast<int>(u / (BN / kNormUnitRows));
+      while (blk > *reinterpret_cast<volatile int*>(&norm_progress) + na.lookahead) __nanosleep(200);
+      const int64_t row0 = u * kNormUnitRows + nw * (kNormUnitRows / kNormWarps);
+      int nrows = kNormUnitRows / kNormWarps;
+      if (row0 + nrows > na.rows) nrows = static_cast<int>(na.rows > row0 ? na.rows - row0 : 0);
+      if (nrows > 0) {
+        if (na.Dp <= 128) l2norm_rows_warp<1>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 256) l2norm_rows_warp<2>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 512) l2norm_rows_warp<4>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 1024) l2norm_rows_warp<8>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else l2norm_rows_warp<16>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+      }
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence();
+        atomicAdd(na.done + blk, 1u);
       }
     }
   } else if (warp >= 4) {
@@ -351,8 +402,57 @@ inline cudaError_t launch_gemm(const Operand& a, const Operand& b, const CUtenso
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  kern<<<grid, kGemmThreads, L::kTotal, stream>>>(tmA, tmB, tmC, sc, ep);
+  kern<<<grid, kGemmThreads, L::kTotal, stream>>>(tmA, tmB, tmC, sc, ep, NormArgs{});
   return cudaGetLastError();
+}
+
+// Forward GEMM with the weight normalisation fused in (NormArgs): K-major operands, one 256-column B tile per
+// 256 rows of the weight.  Cooperative launch: a tile may wait for rows normalised by any other CTA, so the whole
+// grid has to be resident.  cudaErrorCooperativeLaunchTooLarge & co. mean "nothing was enqueued, use the two-kernel
+// path".  na.done must have been zeroed on `stream`.
+template <class Epi, int STAGES>
+inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t M, int64_t N, int64_t K,
+                                    const typename Epi::Params& ep, NormArgs na, cudaStream_t stream) {
+  constexpr int BN = 256;
+  using L = GemmSmem<Epi, BN, STAGES>;
+  static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
+  CUtensorMap tmA, tmB;
+  if (!make_operand_tmap<false>(&tmA, a, kBM)) return cudaErrorInvalidValue;
+  if (!make_operand_tmap<false>(&tmB, b, BN)) return cudaErrorInvalidValue;
+  GemmSched sc;
+  sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
+  sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
+  sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
+  sc.debug_split_b = 0;
+  sc.kb_per_split = sc.kb_total;
+  sc.k_splits = 1;
+  const int total = sc.tiles_m * sc.tiles_n;
+  if (total <= 0) return cudaSuccess;
+  int grid = device_sm_count();
+  if (grid > total) grid = total;
+  auto kern = gemm_sm100_kernel<Epi, BN, STAGES, false, false, true>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads + 32 * kNormWarps);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmA, sc, ep, na);
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e;
 }
 
 }  // namespace arcb

@@ -74,6 +74,38 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32
   }
 }
 
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Spin until *ctr >= target (acquire, gpu scope).  Same watchdog as mbar_wait.
+__device__ __forceinline__ void wait_counter(const unsigned int* ctr, unsigned int target, uint32_t tag) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+  if (v >= target) return;
+  const long long t0 = clock64();
+  uint32_t spins = 0;
+  while (true) {
+    __nanosleep(100);
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    if (v >= target) return;
+    if ((++spins & 0xffu) == 0) {
+      if (*reinterpret_cast<volatile unsigned int*>(&g_wait_timeout[0]) != 0) return;
+      if (clock64() - t0 > 4000000000ll) {
+        if (atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) {
+          g_wait_timeout[1] = tag;
+          g_wait_timeout[2] = blockIdx.x;
+          g_wait_timeout[3] = target;
+        }
+        return;
+      }
+    }
+  }
+}
+
+// Ask L2 to fetch `bytes` (multiple of 16) starting at the 16-byte aligned global address `p`; fire and forget.
+__device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // --------------------------------- TMA --------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");

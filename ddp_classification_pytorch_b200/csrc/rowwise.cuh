@@ -80,7 +80,52 @@ __global__ void __launch_bounds__(256) l2norm_rows_kernel(const float* __restric
   }
 }
 
+// The same normalisation for `nrows` consecutive rows handled by ONE warp, RIF rows in flight so that a handful of
+// warps per SM keeps enough bytes outstanding (used by the normaliser warps inside the forward GEMM kernel).
+// Same arithmetic and summation order as l2norm_rows_kernel<NV>, hence bit-identical outputs.
+template <int NV>
+__device__ __forceinline__ void l2norm_rows_warp(const float* __restrict__ x, int64_t ldx, int64_t row0, int nrows, int D,
+                                                 __nv_bfloat16* __restrict__ out, int Dp, float* __restrict__ inv_norm,
+                                                 int lane) {
+  constexpr int RIF = NV <= 4 ? 4 : (NV <= 8 ? 2 : 1);
+  for (int r = 0; r < nrows; r += RIF) {
+    float4 v[RIF][NV];
+#pragma unroll
+    for (int j = 0; j < RIF; ++j) {
+      const float* xr = x + (row0 + r + j) * ldx;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int e = (i * 32 + lane) * 4;
+        v[j][i] = (r + j < nrows && e < D) ? ld_stream_f4(xr + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < RIF; ++j) {
+      if (r + j >= nrows) break;
+      float ss = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i)
+        ss += v[j][i].x * v[j][i].x + v[j][i].y * v[j][i].y + v[j][i].z * v[j][i].z + v[j][i].w * v[j][i].w;
+      ss = warp_sum(ss);
+      const float inv = 1.f / fmaxf(sqrtf(ss), kNormEps);
+      __nv_bfloat16* orow = out + (row0 + r + j) * Dp;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int e = (i * 32 + lane) * 4;
+        if (e < Dp) {
+          uint2 pk;
+          pk.x = pack_bf16x2(v[j][i].x * inv, v[j][i].y * inv);
+          pk.y = pack_bf16x2(v[j][i].z * inv, v[j][i].w * inv);
+          *reinterpret_cast<uint2*>(orow + e) = pk;
+        }
+      }
+      if (lane == 0) inv_norm[row0 + r + j] = inv;
+    }
+  }
+}
+
 // One warp per sample: exact fp32 target cosine and everything derived from it.
+
 //   lbl_local : label - class_offset when this shard owns the class, else -1
 //   sub       : value substituted for the target cosine (phi, or the fallback branch)
 //   zt        : s * sub (natural units) or -inf when the label is not in this shard
@@ -119,11 +164,19 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
   }
   const float* xr = x + static_cast<int64_t>(i) * ldx;
   const float* wr = w + loc * ldw;
-  float acc = 0.f;
-  for (int e = lane; e < D; e += 32) acc = fmaf(xr[e], wr[e], acc);
+  float acc = 0.f, ss = 0.f;
+  for (int e = lane; e < D; e += 32) {
+    const float wv = wr[e];
+    acc = fmaf(xr[e], wv, acc);
+    ss = fmaf(wv, wv, ss);
+  }
   acc = warp_sum(acc);
+  ss = warp_sum(ss);
   if (lane == 0) {
-    const float c = acc * inv_nx[i] * inv_nw[loc];
+    // inv_nw == nullptr: the weight is normalised concurrently inside the forward GEMM kernel, so this row's
+    // norm is taken from the row itself
+    const float inw = inv_nw ? inv_nw[loc] : 1.f / fmaxf(sqrtf(ss), kNormEps);
+    const float c = acc * inv_nx[i] * inw;
     const float om = 1.f - c * c;
     const float sine = sqrtf(fminf(fmaxf(om, 0.f), 1.f));
     const float phi = c * cos_m - sine * sin_m;

@@ -175,6 +175,12 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
  * Same results in all modes; the switch exists for A/B measurements and tests. */
 int arcb_set_pair_mode(int mode);
 
+/* Where F.normalize(self.weight) (arc_main.py:159) of arcb_shard_forward runs: 0 = its own kernel before the GEMM,
+ * 2 = inside the forward GEMM kernel (extra warps normalise the rows the coming tiles need, so the HBM-bound pass
+ * overlaps the tensor-bound one; needs a cooperative launch, D % 4 == 0, D <= 2048), 1 (default) = 2 for the shapes
+ * where it is faster on B200 (512 <= B <= 1024, >= 65536 classes), else 0.  Same w_hat / inv_norm bits either way. */
+int arcb_set_forward_norm_mode(int mode);
+
 /* Backward schedule: 1 (default) = one persistent cooperative kernel per shard, 0 = one launch
  * per GEMM and class chunk.  Both produce the same gradients (A/B testing, profiling). */
 int arcb_set_backward_mode(int persistent);

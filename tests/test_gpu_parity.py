@@ -6,6 +6,7 @@ import pytest
 import torch
 
 from conftest import cosine_similarity
+from ddp_classification_pytorch_b200.head import CudaEngine  # noqa: E402
 from ddp_classification_pytorch_b200 import ArcMarginProduct, _lib
 from oracle import arcface_oracle as orc
 
@@ -156,6 +157,51 @@ def test_persistent_and_per_chunk_backward_agree(chunk):
     ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, False)
     assert cosine_similarity(grads[0][0].cpu().numpy(), ref["dx"]) >= GRAD_COS
     assert cosine_similarity(grads[0][1].cpu().numpy(), ref["dw"]) >= GRAD_COS
+
+
+@pytest.mark.parametrize("shape", [(300, 192, 3000), (64, 100, 517), (520, 512, 9000), (128, 2048, 700)])
+def test_weight_normalised_inside_the_gemm_matches_separate_kernel(shape):
+    """F.normalize(weight) as extra warps of the forward GEMM kernel vs its own kernel: the same w_hat / inv_norm
+    bits, the same statistics (the target cosine takes its row norm from another reduction order: 1e-6), the same
+    gradients -- for ragged sizes, several tiles per CTA and every register-path width."""
+    import ctypes
+    B, D, C = shape
+    gen = torch.Generator().manual_seed(11)
+    w = ((torch.rand(C, D, generator=gen) * 2 - 1) * 0.05).cuda()
+    w[3] = 0  # a clamped row (norm below eps)
+    x = torch.randn(B, D, generator=gen).cuda()
+    y = torch.randint(0, C, (B,), generator=gen).cuda()
+    L = _lib.lib()
+    eng = CudaEngine()
+    cfg = {"s": 30.0, "m": 0.5, "easy_margin": False, "class_offset": 0, "chunk_classes": 512}
+    Dp = L.arcb_padded_dim(D)
+    out = []
+    try:
+        for mode in (2, 0):
+            L.arcb_set_forward_norm_mode(mode)
+            n0 = L.arcb_launch_count()
+            stats, state = eng.shard_forward(x, w, y, cfg)
+            launches = L.arcb_launch_count() - n0
+            lse, zt, loss = eng.merge_loss(stats, 1, B)
+            dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt)
+            _sync_ok()
+            ws = state[3]
+            a, b = ctypes.c_void_p(), ctypes.c_void_p()
+            _lib.check(L.arcb_ws_weight_slots(ws.data_ptr(), C, D, ctypes.byref(a), ctypes.byref(b)))
+            off_a, off_b = a.value - ws.data_ptr(), b.value - ws.data_ptr()
+            what = ws[off_a: off_a + C * Dp * 2].view(torch.bfloat16).view(C, Dp).clone()
+            inv = ws[off_b: off_b + C * 4].view(torch.float32).clone()
+            out.append((stats.clone(), what, inv, loss.clone(), dw, dxhat, launches))
+    finally:
+        L.arcb_set_forward_norm_mode(1)
+    f, u = out
+    assert f[6] == u[6] - 1                      # the normalisation launch is gone
+    assert torch.equal(f[1].view(torch.int16), u[1].view(torch.int16))
+    assert torch.equal(f[2], u[2])
+    torch.testing.assert_close(f[0], u[0], rtol=2e-6, atol=1e-6)
+    torch.testing.assert_close(f[3], u[3], rtol=1e-6, atol=0)
+    torch.testing.assert_close(f[4], u[4], rtol=1e-3, atol=1e-7)
+    torch.testing.assert_close(f[5], u[5], rtol=1e-3, atol=1e-7)
 
 
 def _check_top3(head_aux, ref_logits, s):

@@ -204,11 +204,22 @@ merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, f
   const int k0 = blockIdx.y * per;
   const int k1 = min(n, k0 + per);
   float m = -INFINITY, l = 0.f;
-  for (int k = k0; k < k1; ++k) {  // online merge: one pass, no second read
-    const float2 p = part[k * ldp + row];
-    if (p.x == -INFINITY) continue;  // empty slice: nothing to add (and -inf - -inf would be NaN)
-    const float nm = fmaxf(m, p.x);
-    l = l * exp2f(m - nm) + p.y * exp2f(p.x - nm);
+  // online merge, one pass; eight partials are fetched before any of them is used so that the (strided,
+  // latency-bound) loads overlap
+  for (int k = k0; k < k1; k += 8) {
+    float2 p[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      p[j] = (k + j < k1) ? part[static_cast<int64_t>(k + j) * ldp + row] : make_float2(-INFINITY, 0.f);
+    float gm = p[0].x;
+#pragma unroll
+    for (int j = 1; j < 8; ++j) gm = fmaxf(gm, p[j].x);
+    if (gm == -INFINITY) continue;  // only empty partials: nothing to add (and -inf - -inf would be NaN)
+    const float nm = fmaxf(m, gm);
+    float acc = l * exp2f(m - nm);  // m = -inf: l is 0 and exp2f(-inf) = 0
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc += p[j].y * exp2f(p[j].x - nm);  // empty partial: 0 * 2^-inf = 0
+    l = acc;
     m = nm;
   }
   if (k0 >= k1) { m = -INFINITY; l = 0.f; }

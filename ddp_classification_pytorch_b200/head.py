@@ -407,6 +407,42 @@ class ArcMarginProduct(nn.Module):
         cfg["want_top3"] = bool(want_top3)
         return _FusedLossFn.apply(input, self.weight, label, cfg)
 
+    # ---- accuracy counters of the trainer / validation loop (arc_main.py:335-345, :377-395) -------------------
+    @torch.no_grad()
+    def correct_counts(self, label, reduce_group=None):
+        """``(top1_correct, top3_correct, samples)`` as a device int64 tensor ``[3]`` from the ``aux`` of the last
+        ``forward_loss(..., want_top3=True)`` -- what ``torch.max(out, 1)`` / ``out.topk(3)`` + ``eq(labels)`` give
+        in the reference, without the logits and without a host sync.  ``reduce_group``: sum the counters over
+        the ranks of that group (data-parallel validation: every rank scored different samples); the reference
+        multiplies rank 0's counts by the world size instead (arc_main.py:393-395).  Do not pass a group in
+        class-sharded mode: there every rank already scored the same global batch."""
+        if "top3" not in self.aux:
+            raise RuntimeError("call forward_loss(input, label, want_top3=True) first")
+        top3 = self.aux["top3"]
+        lab = label.detach().reshape(-1).to(device=top3.device, dtype=top3.dtype)
+        hit = top3 == lab[:, None]
+        counts = torch.stack([hit[:, 0].sum(), hit.any(dim=1).sum(),
+                              torch.tensor(lab.numel(), device=top3.device, dtype=torch.int64)]).to(torch.int64)
+        if reduce_group is not None and torch.distributed.get_world_size(reduce_group) > 1:
+            torch.distributed.all_reduce(counts, group=reduce_group)
+        return counts
+
+    # ---- checkpoints (the reference never saves the head, arc_main.py:407-410 commented out) ------------------
+    def full_state_dict(self):
+        """``{'weight': [out_features, in_features]}`` -- the reference class's ``state_dict()`` layout, also in
+        class-sharded mode (gathers the shards; collective: every rank of the group must call it)."""
+        return {"weight": self.full_weight()}
+
+    @torch.no_grad()
+    def load_full_state_dict(self, state_dict):
+        """Load a full ``[out_features, in_features]`` weight (a reference-layout checkpoint, or one written with
+        another world size): every rank keeps the rows of its own class range."""
+        w = state_dict["weight"]
+        if tuple(w.shape) != (self.out_features, self.in_features):
+            raise RuntimeError(f"weight has shape {tuple(w.shape)}, expected {(self.out_features, self.in_features)}")
+        self.weight.copy_(w[self.class_lo:self.class_hi].to(device=self.weight.device, dtype=self.weight.dtype))
+        return self
+
     @torch.no_grad()
     def full_weight(self):
         """The complete ``[out_features, in_features]`` weight (gathers the shards) for checkpoints."""

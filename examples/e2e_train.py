@@ -78,6 +78,8 @@ def main():
     ap.add_argument("--head", default="replicated", choices=["replicated", "sharded", "torch"])
     ap.add_argument("--image", type=int, default=224)
     ap.add_argument("--channels-last", action="store_true")
+    ap.add_argument("--fused-head-optimizer", action="store_true",
+                    help="step the head with HeadSGD (one pass that also prepares the next forward's normalised weight)")
     args = ap.parse_args()
 
     import torchvision
@@ -109,8 +111,15 @@ def main():
         model = nn.parallel.DistributedDataParallel(model, device_ids=[local])
         if args.head != "sharded":
             head = nn.parallel.DistributedDataParallel(head, device_ids=[local])  # arc_main.py:243
-    opt = torch.optim.SGD([{"params": model.parameters()}, {"params": head.parameters()}],
-                          lr=0.001, momentum=0.9, weight_decay=5e-4)  # arc_main.py:252-253
+    head_opt = None
+    if args.fused_head_optimizer and args.head != "torch":
+        from ddp_classification_pytorch_b200 import HeadSGD
+        opt = torch.optim.SGD(model.parameters(), lr=0.001, momentum=0.9, weight_decay=5e-4)
+        head_opt = HeadSGD(head.module if isinstance(head, nn.parallel.DistributedDataParallel) else head,
+                           lr=0.001, momentum=0.9, weight_decay=5e-4)
+    else:
+        opt = torch.optim.SGD([{"params": model.parameters()}, {"params": head.parameters()}],
+                              lr=0.001, momentum=0.9, weight_decay=5e-4)  # arc_main.py:252-253
 
     g = torch.Generator(device=dev).manual_seed(rank)
     x = torch.randn(args.batch, 3, args.image, args.image, device=dev, generator=g)
@@ -121,6 +130,8 @@ def main():
 
     def step():
         opt.zero_grad(set_to_none=True)
+        if head_opt is not None:
+            head_opt.zero_grad(set_to_none=True)
         feats = model(x)  # arc_main.py:325
         if args.head == "sharded" and world > 1:
             f_all, y_all = _GatherRows.apply(feats, group), _GatherRows.apply(y, group)
@@ -134,6 +145,8 @@ def main():
                 dist.all_reduce(p.grad)
                 p.grad /= world
         opt.step()  # arc_main.py:330
+        if head_opt is not None:
+            head_opt.step()
         return loss
 
     for _ in range(args.warmup):

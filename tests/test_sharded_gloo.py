@@ -98,6 +98,19 @@ def _worker(rank, world, port, B, D, C, easy, out):
             and np.array_equal(head.aux["top3"].numpy(), ref["top3"])
             and np.array_equal(head.aux["argmax"].numpy(), ref["argmax"])
         )
+        # accuracy counters (arc_main.py:338-345): sharded mode scores the same global batch on every rank
+        counts = head.correct_counts(y)
+        top3 = ref["top3"]
+        ok = ok and counts.tolist() == [int((top3[:, 0] == y.numpy()).sum()),
+                                        int((top3 == y.numpy()[:, None]).any(1).sum()), B]
+        # data-parallel counters: each rank scored its own samples -> summed over the group
+        summed = head.correct_counts(y, reduce_group=dist.group.WORLD)
+        ok = ok and summed.tolist() == [world * c for c in counts.tolist()]
+        # checkpoint interchange with the reference layout: full weight out, full weight in (other row order)
+        sd = head.full_state_dict()
+        ok = ok and list(sd) == ["weight"] and torch.equal(sd["weight"], w_full)
+        head.load_full_state_dict({"weight": torch.flip(w_full, dims=[0])})
+        ok = ok and torch.equal(head.weight.detach(), torch.flip(w_full, dims=[0])[lo:hi])
         out[rank] = bool(ok)
     finally:
         dist.destroy_process_group()

@@ -418,12 +418,15 @@ int pair_mode() {
 bool use_pair_gemm() { return pair_mode() == 2; }      // forward / unit-test GEMMs
 bool use_pair_backward() { return pair_mode() >= 1; }  // persistent backward
 
-// ARCB_DYN=0: CTA pairs take a fixed share of the tile list instead of claiming tiles as they go (A/B runs)
+// How CTA pairs get their tiles in the persistent backward: 1 = they claim them as they go (default), 0 = each pair
+// takes a fixed share of the list (A/B runs; ARCB_DYN=0 or arcb_set_backward_mode(2)).  -1 = not yet read.
+std::atomic<int> g_dyn_feed{-1};
 bool use_dynamic_feed() {
-  static int dyn = -1;
+  int dyn = g_dyn_feed.load(std::memory_order_relaxed);
   if (dyn < 0) {
     const char* e = getenv("ARCB_DYN");
     dyn = (e && e[0] == '0') ? 0 : 1;
+    g_dyn_feed.store(dyn, std::memory_order_relaxed);
   }
   return dyn == 1;
 }
@@ -523,8 +526,10 @@ int arcb_set_forward_norm_mode(int mode) {
   return ARCB_OK;
 }
 
-int arcb_set_backward_mode(int persistent) {
-  g_bwd_mode.store(persistent ? 1 : 0, std::memory_order_relaxed);
+int arcb_set_backward_mode(int mode) {
+  if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "backward mode must be 0, 1 or 2");
+  g_bwd_mode.store(mode ? 1 : 0, std::memory_order_relaxed);
+  g_dyn_feed.store(mode == 2 ? 0 : 1, std::memory_order_relaxed);
   return ARCB_OK;
 }
 

@@ -181,9 +181,10 @@ int arcb_set_pair_mode(int mode);
  * where it is faster on B200 (512 <= B <= 1024, >= 65536 classes), else 0.  Same w_hat / inv_norm bits either way. */
 int arcb_set_forward_norm_mode(int mode);
 
-/* Backward schedule: 1 (default) = one persistent cooperative kernel per shard, 0 = one launch
- * per GEMM and class chunk.  Both produce the same gradients (A/B testing, profiling). */
-int arcb_set_backward_mode(int persistent);
+/* Backward schedule: 1 (default) = one persistent cooperative kernel per shard whose CTA pairs claim tiles from the
+ * global tile list as they go, 2 = the same kernel with a fixed share of the list per CTA pair, 0 = one launch
+ * per GEMM and class chunk.  All produce the same gradients (A/B testing, profiling). */
+int arcb_set_backward_mode(int mode);
 
 /* Leading dimension (elements) of the dxhat buffer for feature size D. */
 int64_t arcb_padded_dim(int64_t D);

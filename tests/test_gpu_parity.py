@@ -143,7 +143,7 @@ def test_persistent_and_per_chunk_backward_agree(chunk):
     L = _lib.lib()
     grads = []
     try:
-        for mode in (1, 0):
+        for mode in (1, 0, 2):  # claimed tiles, one launch per GEMM and chunk, fixed share of the tile list
             L.arcb_set_backward_mode(mode)
             head = _module(w.numpy(), 30.0, 0.5, False, chunk_classes=chunk)
             xg = x.cuda().requires_grad_(True)
@@ -152,8 +152,9 @@ def test_persistent_and_per_chunk_backward_agree(chunk):
             grads.append((xg.grad.clone(), head.weight.grad.clone()))
     finally:
         L.arcb_set_backward_mode(1)
-    torch.testing.assert_close(grads[0][0], grads[1][0], rtol=1e-3, atol=1e-6)
-    torch.testing.assert_close(grads[0][1], grads[1][1], rtol=1e-3, atol=1e-6)
+    for other in grads[1:]:
+        torch.testing.assert_close(grads[0][0], other[0], rtol=1e-3, atol=1e-6)
+        torch.testing.assert_close(grads[0][1], other[1], rtol=1e-3, atol=1e-6)
     ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, False)
     assert cosine_similarity(grads[0][0].cpu().numpy(), ref["dx"]) >= GRAD_COS
     assert cosine_similarity(grads[0][1].cpu().numpy(), ref["dw"]) >= GRAD_COS
@@ -202,6 +203,44 @@ def test_weight_normalised_inside_the_gemm_matches_separate_kernel(shape):
     torch.testing.assert_close(f[3], u[3], rtol=1e-6, atol=0)
     torch.testing.assert_close(f[4], u[4], rtol=1e-3, atol=1e-7)
     torch.testing.assert_close(f[5], u[5], rtol=1e-3, atol=1e-7)
+
+
+def _random_shapes(n, seed):
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(n):
+        B = int(rng.integers(1, 700))
+        D = int(rng.choice([8, 36, 64, 100, 128, 200, 256, 384, 512]))
+        C = int(rng.integers(1, 6000))
+        chunk = int(rng.choice([128, 256, 512, 1024, 2048]))
+        out.append((B, D, C, chunk, bool(rng.integers(0, 2)), float(rng.choice([16.0, 30.0, 64.0]))))
+    return out
+
+
+_EDGE_SHAPES = [(1, 64, 1, 128, False, 30.0), (3, 70, 5, 128, True, 30.0), (129, 66, 257, 256, False, 30.0),
+                (2, 512, 2, 2048, False, 64.0)]
+
+
+@pytest.mark.parametrize("case", _random_shapes(10, seed=2024) + _EDGE_SHAPES)
+def test_random_shapes_vs_oracle(case):
+    """Seeded sweep over ragged batch / feature / class counts and chunk lengths (tiles that are partly or wholly
+    padding, shards smaller than one tile, many short chunks for the tile list and the claiming logic)."""
+    B, D, C, chunk, easy, s_ = case
+    gen = torch.Generator().manual_seed(B * 7919 + C)
+    w = (torch.rand(C, D, generator=gen) * 2 - 1) * 0.1
+    x = torch.randn(B, D, generator=gen)
+    y = torch.randint(0, C, (B,), generator=gen)
+    head = _module(w.numpy(), s_, 0.5, easy, chunk_classes=chunk)
+    xg = x.cuda().requires_grad_(True)
+    loss = head.forward_loss(xg, y.cuda())
+    loss.backward()
+    _sync_ok()
+    ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), s_, 0.5, easy)
+    assert abs(loss.item() - ref["loss"]) <= LOSS_RTOL * abs(ref["loss"])
+    if np.linalg.norm(ref["dx"]) > 0:
+        assert cosine_similarity(xg.grad.cpu().numpy(), ref["dx"]) >= GRAD_COS
+        assert cosine_similarity(head.weight.grad.cpu().numpy(), ref["dw"]) >= GRAD_COS
+        assert np.linalg.norm(head.weight.grad.cpu().numpy()) == pytest.approx(np.linalg.norm(ref["dw"]), rel=3e-2)
 
 
 def _check_top3(head_aux, ref_logits, s):

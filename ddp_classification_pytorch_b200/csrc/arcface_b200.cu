@@ -191,25 +191,22 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   if (W.total > ws_bytes)
     return fail(ARCB_ERR_WORKSPACE, "workspace too small: need %lld bytes, got %lld", (long long)W.total,
                 (long long)ws_bytes);
-  rc = launch_l2norm(x, B, D, ldx, W.xhat, W.Dp, W.inv_nx, st, ARCB_K_L2NORM_X);
-  if (rc) return rc;
   if (w_mode == 0) {
     rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
     if (rc) return rc;
-  } else if (w_mode == 2) {  // per-B-tile "rows normalised" counters of the fused kernel
-    ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * ((Cs + kBNTile - 1) / kBNTile), st));
   }
+  // w_mode 2: the per-B-tile "rows normalised" counters of the fused kernel are cleared by the kernel below
+  const int n_zero = w_mode == 2 ? static_cast<int>((Cs + kBNTile - 1) / kBNTile) : 0;
   const double md = static_cast<double>(m);
   const float cos_m = static_cast<float>(cos(md)), sin_m = static_cast<float>(sin(md));
   const float th = static_cast<float>(cos(M_PI - md)), mm = static_cast<float>(sin(M_PI - md) * md);
   const int blocks = static_cast<int>((W.Bp + 7) / 8);
   LaunchScope ls(ARCB_K_TARGET_PREP, st);
-  // the target row's norm is always taken from the row itself (inv_nw = nullptr): the weight may still be being
-  // normalised (w_mode 2), and the target logit must not depend on which of the three modes produced w_hat
-  target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.inv_nx, nullptr, (int)B,
-                                             (int)W.Bp, (int)D, Cs,
-                                             class_offset, s, cos_m, sin_m, th, mm, easy, W.lbl_local, W.sub, W.zt,
-                                             W.dphi, W.cos_t);
+  // per-sample work in one launch: F.normalize(input) and the exact fp32 target cosine / margin branch
+  const int xvec = (D % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+  target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.xhat, (int)W.Dp, W.inv_nx, xvec, (int)B,
+                                             (int)W.Bp, (int)D, Cs, class_offset, s, cos_m, sin_m, th, mm, easy,
+                                             W.lbl_local, W.sub, W.zt, W.dphi, W.cos_t, W.counters, n_zero);
   ARCB_CUDA(cudaGetLastError());
   *out_ws = W;
   return ARCB_OK;
@@ -220,7 +217,7 @@ constexpr int kLaunchRefused = 1;  // internal: the cooperative launch was refus
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
 template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
-                          int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st,
+                          int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st, BwdSetup su,
                           unsigned long long* trace = nullptr) {
   const int64_t B = W.B, Cs = W.Cs, D = W.D;
   BwdPlan pl;
@@ -292,7 +289,6 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   }
   pl.xw_done = W.counters + pl.n_chunks;
   pl.claim = W.counters + 2 * pl.n_chunks;
-  ARCB_CUDA(cudaMemsetAsync(W.counters, 0, sizeof(unsigned int) * (2 * pl.n_chunks + 1), st));
   {
     // the tile list: written once here, then read (one 32-byte record per tile) by every role of every CTA
     const int nph = pl.n_chunks + pl.lag;
@@ -304,8 +300,12 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     }
     pl.items = W.items;
     pl.total_items = static_cast<int>(total);
+    su.zero_c = W.counters;
+    su.n_c = 2 * pl.n_chunks + 1;
+    su.n_phases = nph;
     LaunchScope ls(ARCB_K_BWD_PREP, st);
-    bwd_items_kernel<<<nph, 128, 0, st>>>(pl, W.items);
+    const int blocks = nph > 2 * device_sm_count() ? nph : 2 * device_sm_count();
+    bwd_setup_kernel<<<blocks, 256, 0, st>>>(pl, W.items, su);
     ARCB_CUDA(cudaGetLastError());
   }
 
@@ -720,11 +720,14 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
   const int blocks = static_cast<int>((B + 255) / 256);
-  {
-    LaunchScope ls(ARCB_K_MERGE, st, 3);
-    merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, 2 * tiles_n, W.Bp, (int)B, W.rec2, W.Bp);
-    merge_stats_kernel<<<dim3(blocks, 1), 256, 0, st>>>(W.rec2, kMergeSlices, W.Bp, (int)B, W.rec, W.Bp);
-    pack_stats_kernel<<<blocks, 256, 0, st>>>(W.rec, W.zt, (int)B, stats);
+  const int n_part = 2 * tiles_n;
+  if (n_part > 4 * kMergeSlices) {  // two levels: 64 slices in parallel, then the 64 results + the shard record
+    LaunchScope ls(ARCB_K_MERGE, st, 2);
+    merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, n_part, W.Bp, (int)B, W.rec2, W.Bp);
+    merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(W.rec2, kMergeSlices, W.Bp, W.zt, (int)B, stats);
+  } else {
+    LaunchScope ls(ARCB_K_MERGE, st, 1);
+    merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(W.part, n_part, W.Bp, W.zt, (int)B, stats);
   }
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;
@@ -883,15 +886,13 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   if (chunk > round_up(Cs, 128)) chunk = round_up(Cs, 128);
   __nv_bfloat16* gt = static_cast<__nv_bfloat16*>(scratch);
 
-  if (!ext) {
-    const int blocks = static_cast<int>((W.Bp + 255) / 256);
-    LaunchScope ls(ARCB_K_BWD_PREP, st);
-    bwd_prep_kernel<<<blocks, 256, 0, st>>>(lse, target_logit, grad_loss, s, (int)B, (int)W.Bp, W.lse2, W.zt2,
-                                            W.gscale);
-    ARCB_CUDA(cudaGetLastError());
-  }
-  ARCB_CUDA(cudaMemsetAsync(W.tproj, 0, Cs * 4, st));
-  ARCB_CUDA(cudaMemsetAsync(dxhat, 0, B * W.Dp * 4, st));
+  // one set-up launch in front of the GEMMs (bwd_setup_kernel); the persistent schedule adds its tile list to it
+  BwdSetup su;
+  su.lse = ext ? nullptr : lse; su.zt = target_logit; su.grad_loss = grad_loss; su.s = s;
+  su.B = (int)B; su.Bp = (int)W.Bp; su.lse2 = W.lse2; su.zt2 = W.zt2; su.gscale = W.gscale;
+  su.zero_a = W.tproj; su.n_a = Cs;
+  su.zero_b = dxhat; su.n_b = B * W.Dp;
+  su.zero_c = nullptr; su.n_c = 0; su.n_phases = 0;
 
   if (use_persistent_backward()) {
     // multi-buffered scratch: 4 buffers of `pchunk` classes each (fewer if the scratch is small)
@@ -922,10 +923,10 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
         if (use_pair_backward()) {
           if (use_dynamic_feed())
             return launch_bwd_persistent<false, true, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st,
-                                                                  trace);
-          return launch_bwd_persistent<false, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, trace);
+                                                                  su, trace);
+          return launch_bwd_persistent<false, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, su, trace);
         }
-        return launch_bwd_persistent<false, false, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, trace);
+        return launch_bwd_persistent<false, false, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, su, trace);
       }
     }
     if (use_pair_backward()) {  // a pair's tile has 256 rows: chunks (= scratch buffers) must be whole tiles
@@ -933,21 +934,26 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
       if (pc2 >= 256) {
         if (use_dynamic_feed())
-          rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
-                   : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+          rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su)
+                   : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
         else
-          rc = ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st)
-                   : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st);
+          rc = ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su)
+                   : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
         if (rc != kLaunchRefused) return rc;
       }
     }
     if (pchunk >= 128) {
       if (pchunk > round_up(Cs, 128)) pchunk = round_up(Cs, 128);
-      rc = ext ? launch_bwd_persistent<true, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st)
-               : launch_bwd_persistent<false, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st);
+      rc = ext ? launch_bwd_persistent<true, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st, su)
+               : launch_bwd_persistent<false, false>(W, s, grad_logits, ldgl, gt, pchunk, nbuf, dw, dxhat, st, su);
       if (rc != kLaunchRefused) return rc;
     }
-    // refused twice: one launch per GEMM and chunk needs no co-residency (memsets above are still valid)
+    // refused twice: one launch per GEMM and chunk needs no co-residency
+  }
+  {  // per-chunk schedule: the same set-up without a tile list
+    LaunchScope ls(ARCB_K_BWD_PREP, st);
+    bwd_setup_kernel<<<2 * device_sm_count(), 256, 0, st>>>(BwdPlan{}, nullptr, su);
+    ARCB_CUDA(cudaGetLastError());
   }
 
   const int sms = device_sm_count();

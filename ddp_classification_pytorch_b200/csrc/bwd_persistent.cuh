@@ -78,7 +78,7 @@ struct BwdPlan {
   unsigned int* claim;       // dynamic feed: next unclaimed list index (zeroed before the launch)
   int rot;                   // slot rotation per dealing round (see ItemWalker), 0 = plain round-robin
   int debug_epi;             // debug (ARCB_DEBUG_EPI): 1 = G epilogue skips math + smem stores, 2 = also skips the TMEM loads
-  const int4* items;         // [total_items][2] the global tile list, written by bwd_items_kernel before the launch
+  const int4* items;         // [total_items][2] the global tile list, written by bwd_setup_kernel before the launch
   int total_items;
 };
 
@@ -157,7 +157,7 @@ __device__ __forceinline__ bool pick_b(int j, int n_b, int total, int& idx_b, in
 }
 
 // Item j of phase `phase` (the arithmetic of the global list: integer divisions, done once per item by
-// bwd_items_kernel instead of by every role of every CTA in front of every tile).
+// bwd_setup_kernel instead of by every role of every CTA in front of every tile).
 __device__ inline void make_item(const BwdPlan& pl, int phase, int j, Item& it) {
   const int ctas = pl.tile_rows / kBM;
   const int phase_size = phase_items(pl, phase);
@@ -215,17 +215,53 @@ __host__ __device__ inline long long phase_begin_of(const BwdPlan& pl, int p) {
   return prefix(p, true) + prefix(p - pl.lag, false);
 }
 
-// One block per phase writes that phase's items (two int4 each) into the table every role reads.
-__global__ void __launch_bounds__(128) bwd_items_kernel(const BwdPlan pl, int4* __restrict__ out) {
-  const int p = blockIdx.x;
-  const long long begin = phase_begin_of(pl, p);
-  const int n = phase_items(pl, p);
-  for (int j = threadIdx.x; j < n; j += blockDim.x) {
-    Item it;
-    make_item(pl, p, j, it);
-    out[2 * (begin + j)] = make_int4(it.kind, it.chunk, it.m_blk, it.n_blk);
-    out[2 * (begin + j) + 1] = make_int4(it.kb0, it.kb1, static_cast<int>(it.target), it.buf);
+// Everything the backward needs set up before its GEMMs start, in ONE launch (it used to be two kernels and three
+// memsets, i.e. five dependent launches in front of a kernel that takes 0.3 ms on an 8-way shard):
+//   * the tile list: one block per phase writes that phase's records (two int4 each);
+//   * per-sample inputs of the recompute epilogue: lse2 = lse * log2(e) (+inf on padding), zt2 likewise, and
+//     gscale = upstream grad * s / B                                  (skipped when grad_logits is given);
+//   * zeroes: the per-class projections t_j, the dxhat accumulator, the chunk counters + claim counter.
+struct BwdSetup {
+  const float* lse;        // nullptr: no per-sample preparation (grad_logits path)
+  const float* zt;
+  const float* grad_loss;  // device scalar or nullptr (= 1)
+  float s;
+  int B, Bp;
+  float* lse2;
+  float* zt2;
+  float* gscale;
+  float* zero_a;           // t_j
+  long long n_a;
+  float* zero_b;           // dxhat
+  long long n_b;
+  unsigned int* zero_c;    // counters
+  int n_c;
+  int n_phases;            // 0: no tile list (per-chunk schedule)
+};
+
+__global__ void __launch_bounds__(256) bwd_setup_kernel(const BwdPlan pl, int4* __restrict__ out, const BwdSetup su) {
+  for (int p = blockIdx.x; p < su.n_phases; p += gridDim.x) {
+    const long long begin = phase_begin_of(pl, p);
+    const int n = phase_items(pl, p);
+    for (int j = threadIdx.x; j < n; j += blockDim.x) {
+      Item it;
+      make_item(pl, p, j, it);
+      out[2 * (begin + j)] = make_int4(it.kind, it.chunk, it.m_blk, it.n_blk);
+      out[2 * (begin + j) + 1] = make_int4(it.kb0, it.kb1, static_cast<int>(it.target), it.buf);
+    }
   }
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthr = static_cast<long long>(gridDim.x) * blockDim.x;
+  if (su.lse) {
+    if (tid == 0) *su.gscale = (su.grad_loss ? *su.grad_loss : 1.f) * su.s / static_cast<float>(su.B);
+    for (long long i = tid; i < su.Bp; i += nthr) {
+      su.lse2[i] = (i < su.B) ? su.lse[i] * kLog2e : INFINITY;
+      su.zt2[i] = (i < su.B) ? su.zt[i] * kLog2e : -INFINITY;
+    }
+  }
+  for (long long i = tid; i < su.n_a; i += nthr) su.zero_a[i] = 0.f;
+  for (long long i = tid; i < su.n_b; i += nthr) su.zero_b[i] = 0.f;
+  for (long long i = tid; i < su.n_c; i += nthr) su.zero_c[i] = 0u;
 }
 
 // Every role of a CTA (or CTA pair) walks the same sub-sequence of the global list: tiles first, first + step, ...

@@ -131,28 +131,50 @@ __device__ __forceinline__ void l2norm_rows_warp(const float* __restrict__ x, in
 //   zt        : s * sub (natural units) or -inf when the label is not in this shard
 //   dphi      : d sub / d cos   (finite limit cos_m where the reference produces NaN)
 //   cos_t     : the fp32 cosine itself
+// The same warp first normalises its sample (F.normalize(input), arc_main.py:159: bf16 unit row, zero padded to Dp,
+// and 1 / max(||x||, eps)) -- one launch for everything that is per sample.  `vec`: rows are 16-byte aligned and
+// D % 4 == 0 (128-bit loads, same summation order as l2norm_rows_kernel).
 __global__ void __launch_bounds__(256)
 target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, int64_t ldw,
-                   const int64_t* __restrict__ labels, const float* __restrict__ inv_nx,
-                   const float* __restrict__ inv_nw, int B, int Bp, int D, int64_t Cs, int64_t class_offset, float s,
+                   const int64_t* __restrict__ labels, __nv_bfloat16* __restrict__ xhat, int Dp,
+                   float* __restrict__ inv_nx, int vec, int B, int Bp, int D, int64_t Cs, int64_t class_offset, float s,
                    float cos_m, float sin_m, float th, float mm, int easy, int* __restrict__ lbl_local,
                    float* __restrict__ sub, float* __restrict__ zt, float* __restrict__ dphi,
-                   float* __restrict__ cos_t) {
+                   float* __restrict__ cos_t, unsigned int* __restrict__ zero, int n_zero) {
+  // (also clears the per-tile counters of the forward kernel that normalises the weight itself)
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n_zero; k += gridDim.x * blockDim.x) zero[k] = 0u;
   const int lane = threadIdx.x & 31;
   const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (i >= Bp) return;
-  if (i >= B) {  // padding rows
-    if (lane == 0) {
-      lbl_local[i] = -1;
-      sub[i] = 0.f;
-      zt[i] = -INFINITY;
-      dphi[i] = 0.f;
-      cos_t[i] = 0.f;
+  float inx = 0.f;
+  if (i < B) {
+    const float* xr = x + static_cast<int64_t>(i) * ldx;
+    __nv_bfloat16* orow = xhat + static_cast<int64_t>(i) * Dp;
+    float ss = 0.f;
+    if (vec) {
+      for (int e = lane * 4; e < D; e += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xr + e);
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+      }
+      ss = warp_sum(ss);
+      inx = 1.f / fmaxf(sqrtf(ss), kNormEps);
+      for (int e = lane * 4; e < Dp; e += 128) {
+        const float4 v = (e < D) ? *reinterpret_cast<const float4*>(xr + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+        uint2 pk;
+        pk.x = pack_bf16x2(v.x * inx, v.y * inx);
+        pk.y = pack_bf16x2(v.z * inx, v.w * inx);
+        *reinterpret_cast<uint2*>(orow + e) = pk;
+      }
+    } else {
+      for (int e = lane; e < D; e += 32) ss += xr[e] * xr[e];
+      ss = warp_sum(ss);
+      inx = 1.f / fmaxf(sqrtf(ss), kNormEps);
+      for (int e = lane; e < Dp; e += 32) orow[e] = __float2bfloat16_rn(e < D ? xr[e] * inx : 0.f);
     }
-    return;
+    if (lane == 0) inv_nx[i] = inx;
   }
-  const int64_t loc = labels[i] - class_offset;
-  if (loc < 0 || loc >= Cs) {
+  const int64_t loc = (i < B) ? labels[i] - class_offset : -1;
+  if (loc < 0 || loc >= Cs) {  // padding rows, labels owned by another shard (or out of range)
     if (lane == 0) {
       lbl_local[i] = -1;
       sub[i] = 0.f;
@@ -173,10 +195,10 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
   acc = warp_sum(acc);
   ss = warp_sum(ss);
   if (lane == 0) {
-    // inv_nw == nullptr: the weight is normalised concurrently inside the forward GEMM kernel, so this row's
-    // norm is taken from the row itself
-    const float inw = inv_nw ? inv_nw[loc] : 1.f / fmaxf(sqrtf(ss), kNormEps);
-    const float c = acc * inv_nx[i] * inw;
+    // the class row's norm is taken from the row itself: the weight may still be being normalised (inside the
+    // forward GEMM kernel), and the target logit must not depend on which path produced w_hat
+    const float inw = 1.f / fmaxf(sqrtf(ss), kNormEps);
+    const float c = acc * inx * inw;
     const float om = 1.f - c * c;
     const float sine = sqrtf(fminf(fmaxf(om, 0.f), 1.f));
     const float phi = c * cos_m - sine * sin_m;
@@ -192,20 +214,10 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
   }
 }
 
-// part[n][ldp] (base-2 max, sum) -> out[slice][ldo] = merged (max, sum) over the slice's share of n.
-// grid = (ceil(B / 256), slices): thread = one row, block y = one slice of the partial list, so the
-// 8 B loads of a warp are coalesced and n / slices of them are in flight per thread.
-__global__ void __launch_bounds__(256)
-merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, float2* __restrict__ out,
-                   int64_t ldo) {
-  const int row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= B) return;
-  const int per = (n + gridDim.y - 1) / gridDim.y;
-  const int k0 = blockIdx.y * per;
-  const int k1 = min(n, k0 + per);
+// Online merge of the (base-2 max, sum) partials part[k0 .. k1)[row]: one pass; eight partials are fetched before any
+// of them is used so that the (strided, latency-bound) loads overlap.
+__device__ __forceinline__ float2 merge_partials(const float2* __restrict__ part, int k0, int k1, int64_t ldp, int row) {
   float m = -INFINITY, l = 0.f;
-  // online merge, one pass; eight partials are fetched before any of them is used so that the (strided,
-  // latency-bound) loads overlap
   for (int k = k0; k < k1; k += 8) {
     float2 p[8];
 #pragma unroll
@@ -222,8 +234,30 @@ merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, f
     l = acc;
     m = nm;
   }
-  if (k0 >= k1) { m = -INFINITY; l = 0.f; }
-  out[blockIdx.y * ldo + row] = make_float2(m, l);
+  return make_float2(m, l);
+}
+
+// part[n][ldp] -> out[slice][ldo] = merged (max, sum) over the slice's share of n.
+// grid = (ceil(B / 256), slices): thread = one row, block y = one slice of the partial list, so the
+// 8 B loads of a warp are coalesced and n / slices of them are in flight per thread.
+__global__ void __launch_bounds__(256)
+merge_stats_kernel(const float2* __restrict__ part, int n, int64_t ldp, int B, float2* __restrict__ out,
+                   int64_t ldo) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= B) return;
+  const int per = (n + gridDim.y - 1) / gridDim.y;
+  const int k0 = blockIdx.y * per;
+  out[blockIdx.y * ldo + row] = merge_partials(part, k0, min(n, k0 + per), ldp, row);
+}
+
+// Last merge level + the shard record: part[n][ldp] (all of it) and zt -> stats[B][4] = (m2, l, zt, 0).
+__global__ void __launch_bounds__(128)
+merge_pack_kernel(const float2* __restrict__ part, int n, int64_t ldp, const float* __restrict__ zt, int B,
+                  float* __restrict__ stats) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= B) return;
+  const float2 r = merge_partials(part, 0, n, ldp, row);
+  *reinterpret_cast<float4*>(stats + static_cast<int64_t>(row) * 4) = make_float4(r.x, r.y, zt[row], 0.f);
 }
 
 // stats[P][B][4] = (m2, l, zt, -) per shard -> lse[B] (natural log units), loss = mean(lse - zt).
@@ -258,15 +292,6 @@ loss_kernel(const float* __restrict__ stats, int P, int B, float* __restrict__ l
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (threadIdx.x == 0) *loss = static_cast<float>(v / B);
   }
-}
-
-// rec (merged (m2, l)) + zt -> shard record [B][4]
-__global__ void __launch_bounds__(256)
-pack_stats_kernel(const float2* __restrict__ rec, const float* __restrict__ zt, int B, float* __restrict__ stats) {
-  const int row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= B) return;
-  const float2 r = rec[row];
-  *reinterpret_cast<float4*>(stats + static_cast<int64_t>(row) * 4) = make_float4(r.x, r.y, zt[row], 0.f);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -369,19 +394,6 @@ topk_rescore_kernel(const float* __restrict__ x, int64_t ldx, const float* __res
       top_idx[row * 3 + k] = (all.v[k] == -INFINITY) ? -1 : (class_offset + all.i[k]);
     }
   }
-}
-
-// Backward set-up: lse2[i] = lse[i] * log2(e) (+inf on padding), zt2 likewise, gscale = grad * s / B,
-// and clears the per-chunk accumulators.
-__global__ void __launch_bounds__(256)
-bwd_prep_kernel(const float* __restrict__ lse, const float* __restrict__ zt, const float* __restrict__ grad_loss,
-                float s, int B, int Bp, float* __restrict__ lse2, float* __restrict__ zt2,
-                float* __restrict__ gscale) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) *gscale = (grad_loss ? *grad_loss : 1.f) * s / static_cast<float>(B);
-  if (i >= Bp) return;
-  lse2[i] = (i < B) ? lse[i] * kLog2e : INFINITY;
-  zt2[i] = (i < B) ? zt[i] * kLog2e : -INFINITY;
 }
 
 // dx = (dxh - xh * (xh . dxh)) / ||x||   with xh = x / ||x||;  clamped rows (||x|| <= eps): dx = dxh / eps.

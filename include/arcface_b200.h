@@ -198,11 +198,11 @@ int64_t arcb_padded_dim(int64_t D);
 enum {
   ARCB_K_L2NORM_X = 0,    /* F.normalize(input)                      */
   ARCB_K_L2NORM_W = 1,    /* F.normalize(weight)                     */
-  ARCB_K_TARGET_PREP = 2, /* fp32 target cosine + margin branch      */
+  ARCB_K_TARGET_PREP = 2, /* F.normalize(input) + fp32 target cosine + margin branch */
   ARCB_K_FWD_GEMM = 3,    /* cos GEMM + online softmax statistics    */
   ARCB_K_MERGE = 4,       /* merge of per-tile statistics            */
   ARCB_K_LOSS = 5,        /* cross-entropy from merged statistics    */
-  ARCB_K_BWD_PREP = 6,    /* backward set-up                         */
+  ARCB_K_BWD_PREP = 6,    /* backward set-up (tile list, zeroing)    */
   ARCB_K_BWD_G_GEMM = 7,  /* recompute cos, write bf16 dLoss/dcos    */
   ARCB_K_DX_GEMM = 8,     /* dxhat += G * what                       */
   ARCB_K_DW_GEMM = 9,     /* dW = G^T * xhat with normalise-backward */

@@ -1,36 +1,36 @@
 // Persistent backward kernel of the ArcFace head (autograd behind ARCFACE/arc_main.py:329).
 //
 // One cooperative launch replaces the per-chunk sequence of three GEMM launches.  The classes of
-// the shard are cut into chunks; every chunk k contributes three kinds of 128 x 256 output tiles:
+// the shard are cut into chunks; every chunk k contributes three kinds of output tiles (128 x 256 per CTA):
 //
 //   G(k)  recompute cos^T = w_hat[chunk] * x_hat^T, epilogue -> bf16 dLoss/dcos tile G^T into an
-//         L2-resident double-buffered scratch (buffer k & 1) + per-class projections t_j
+//         L2-resident scratch of nbuf (default 4) chunk buffers (buffer k % nbuf) + per-class projections t_j
 //   X(k)  dX_hat[B, D] += G[B, chunk] * w_hat[chunk, D]     (split along the chunk's classes,
 //         fp32 bulk reduce-add)
 //   W(k)  dW[chunk, D] = inv_norm * (G^T[chunk, B] * x_hat[B, D] - t * w_hat)
 //
-// All CTAs walk ONE global tile list round-robin: phase p = the G tiles of chunk p interleaved with the
-// X / W tiles of chunk p - 2 (see ItemWalker).  Dependencies are two arrays of global counters:
+// There is ONE global tile list, written by bwd_setup_kernel before the launch: phase p = the G tiles of chunk p
+// mixed proportionally with the X / W tiles of chunk p - lag (default 2).  CTA pairs claim the next tile of the
+// list as they go (TileFeed<true>); the single-CTA build takes a fixed share (ItemWalker).  Dependencies are two
+// arrays of global counters:
 //   g_done[k]   half-tiles of G(k) whose stores have completed  -> gates the loads of X(k)/W(k)
 //   xw_done[k]  X/W tiles of chunk k that finished reading G^T  -> gates the stores of G(k+nbuf)
 // Every wait targets a tile that is EARLIER in the list and all CTAs are co-resident (cooperative
 // launch), so the schedule cannot deadlock.
 //
-// Warp roles: 0 = TMA producer, 1 = tcgen05.mma issuer, 2 / 3 = G^T store issuers of epilogue
-// warpgroup 1 / 0 (TMA store + completion + release of g_done, off the epilogue's critical path;
-// warp 2 also owns the TMEM allocation), 4..11 = epilogue (two warpgroups, half the columns each).
-//
-// Shared memory: 4 operand stages of 48 KB (the L2 -> SM latency needs that much in flight), and
-// only 34 KB for the epilogues: one 16 KB slot per epilogue warpgroup -- a [128 x 64] bf16 box of
-// G^T, or a [128 x 32] fp32 chunk of dX / dW -- plus the staged log-sum-exps / labels.
+// Warp roles: 0 = TMA producer, 1 = tcgen05.mma issuer (pair: leader CTA; the follower's warp 1 claims tiles),
+// 2 / 3 = G^T store issuers of epilogue warpgroup 1 / 0 (TMA store + completion + release of g_done, off the
+// epilogue's critical path; warp 2 also owns the TMEM allocation), 4..11 = epilogue (two warpgroups, half the
+// columns each).
 //
 // Two builds of the same kernel (template parameter PAIR):
-//   PAIR = false  one CTA per 128 x 256 tile (cta_group::1), 4 stages of 48 KB
+//   PAIR = false  one CTA per 128 x 256 tile (cta_group::1), 4 operand stages of 48 KB, one 16 KB output slot
+//                 per epilogue warpgroup (a [128 x 64] bf16 box of G^T, or a [128 x 32] fp32 chunk of dX / dW)
 //   PAIR = true   a cluster of two CTAs per 256 x 256 tile (cta_group::2, see gemm2_sm100.cuh): each CTA
-//                 stages its own 128 rows of A and half of B, 6 stages of 32 KB; the backward tiles are
-//                 shared-memory-bandwidth bound (operand traffic + epilogue staging), and the pair cuts the
-//                 operand traffic per SM by a third.  Tiles, counters and epilogues are per CTA as before;
-//                 only the leader issues MMAs.
+//                 stages its own 128 rows of A and half of B, 5 stages of 32 KB, two output slots per
+//                 warpgroup; the backward tiles are shared-memory-bandwidth bound (operand traffic + epilogue
+//                 staging), and the pair cuts the operand traffic per SM by a third.  Tiles, counters and
+//                 epilogues are per CTA as before; only the leader issues MMAs.
 #pragma once
 
 #include "epilogues.cuh"
@@ -65,7 +65,7 @@ struct BwdPlan {
   int n_chunks, chunk_rows;  // chunk_rows % 128 == 0
   int tile_rows;             // accumulator rows of one tile: 128 (one CTA) or 256 (CTA pair)
   int lag;                   // phases between the G tiles of a chunk and its X / W tiles (default 2)
-  int nbuf;                  // scratch buffers of chunk_rows rows each (2 or 3); chunk k uses buffer k % nbuf
+  int nbuf;                  // scratch buffers of chunk_rows rows each (default 4); chunk k uses buffer k % nbuf
   int Cs, B, Bp, D, Dp;
   int g_tiles_n;             // Bp / 256
   int g_kb;                  // Dp / 64

@@ -65,8 +65,8 @@ int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D);
 
 /* Bytes of backward scratch that hold `chunk_classes` classes of bf16 dLoss/dcos for batch B.
  * arcb_shard_backward accepts any scratch >= arcb_scratch_bytes(B, 128); its default persistent
- * kernel splits the scratch into two buffers (needs >= arcb_scratch_bytes(B, 256), otherwise it
- * falls back to one kernel launch per GEMM and chunk). */
+ * kernel splits the scratch into four chunk buffers (fewer when the scratch is small; below
+ * arcb_scratch_bytes(B, 2 * 256) it falls back to one kernel launch per GEMM and chunk). */
 int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes);
 
 /* Chunk length (classes, a multiple of 256) that suits the persistent backward for this problem on the current

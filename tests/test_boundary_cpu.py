@@ -41,6 +41,45 @@ def test_size_queries_without_gpu(built):
     assert L.arcb_launch_count() == 0
 
 
+def test_chunk_suggestion_and_weight_slots_without_gpu(built):
+    """Host-side sizing logic of the backward and of the weight cache (no launches involved)."""
+    L = built
+    for B, C, D in [(1024, 1_000_000, 512), (512, 100_000, 512), (256, 1000, 2048), (64, 10, 512), (4096, 300_000, 256)]:
+        r = L.arcb_suggest_chunk_classes(B, C, D)
+        assert r > 0 and r % 256 == 0
+        assert r <= (C + 255) // 256 * 256                              # never longer than the shard
+        if C >= 64 * 256:
+            assert r >= 16 * 256                                        # short chunks pay too much reduce-add traffic
+    assert L.arcb_suggest_chunk_classes(0, 10, 10) < 0
+    # the weight slots lead the workspace: same offsets whatever the batch size, w_hat first, both 256-byte aligned
+    a, b = ctypes.c_void_p(), ctypes.c_void_p()
+    base = 0x7f0000000000
+    C, D = 10_000, 72
+    assert L.arcb_ws_weight_slots(ctypes.c_void_p(base), C, D, ctypes.byref(a), ctypes.byref(b)) == 0
+    assert a.value == base and (b.value - base) % 256 == 0
+    assert b.value - base >= C * L.arcb_padded_dim(D) * 2
+    for B in (1, 100, 5000):
+        assert L.arcb_ws_bytes(B, C, D) >= (b.value - base) + C * 4
+    assert L.arcb_ws_weight_slots(ctypes.c_void_p(base + 8), C, D, ctypes.byref(a), ctypes.byref(b)) == -1  # alignment
+
+
+def test_mode_switches_and_optimizer_argument_checks(built):
+    L = built
+    assert L.arcb_set_forward_norm_mode(3) == -1 and b"0, 1 or 2" in L.arcb_last_error()
+    assert L.arcb_set_backward_mode(5) == -1
+    assert L.arcb_set_pair_mode(7) != 0
+    for fn, mode in ((L.arcb_set_forward_norm_mode, 1), (L.arcb_set_backward_mode, 1), (L.arcb_set_pair_mode, 1)):
+        assert fn(mode) == 0
+    fake = ctypes.c_void_p(0x7f0000000000)
+    # rejected before anything is launched
+    assert L.arcb_sgd_step(fake, 64, fake, 64, None, 64, 4, 64, 0.1, 0.9, 0.0, 0.0, 0, 1, None, 64, None, None) == -1
+    assert L.arcb_sgd_step(fake, 64, fake, 64, fake, 64, 4, 64, 0.1, 0.0, 0.0, 0.0, 1, 1, None, 64, None, None) == -1
+    assert b"Nesterov" in L.arcb_last_error()
+    assert L.arcb_adam_step(fake, 64, fake, 64, fake, fake, 64, 4, 64, 1e-3, 0.9, 1.0, 1e-8, 0.0, 1, None, 64, None,
+                            None) == -1
+    assert b"betas" in L.arcb_last_error()
+
+
 def test_errors_are_codes_not_exceptions(built):
     L = built
     rc = L.arcb_l2norm_rows(None, 4, 8, 8, None, 64, None, None)

@@ -34,7 +34,7 @@ EXPORTED = [
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
     "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3", "arcb_set_pair_mode",
     "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
-    "arcb_suggest_chunk_classes", "arcb_set_forward_norm_mode",
+    "arcb_suggest_chunk_classes", "arcb_set_forward_norm_mode", "arcb_set_stored_probs_mode",
 ]
 
 KERNEL_KINDS = [
@@ -124,6 +124,8 @@ def _declare(lib):
     lib.arcb_set_pair_mode.argtypes = [i32]
     lib.arcb_set_forward_norm_mode.restype = i32
     lib.arcb_set_forward_norm_mode.argtypes = [i32]
+    lib.arcb_set_stored_probs_mode.restype = i32
+    lib.arcb_set_stored_probs_mode.argtypes = [i32]
     lib.arcb_set_backward_mode.restype = i32
     lib.arcb_set_backward_mode.argtypes = [i32]
     lib.arcb_launch_count.restype = i64

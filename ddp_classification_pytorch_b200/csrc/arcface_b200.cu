@@ -77,6 +77,20 @@ struct LaunchScope {
 constexpr int kBNTile = 256;
 constexpr int kMergeSlices = 64;
 
+// Stored-probabilities mode (arcb_set_stored_probs_mode / ARCB_STORED_PROBS): the fused forward keeps
+// P' = bf16(2^(s2 cos - ref2)) for the whole shard in the workspace and the backward runs without its recompute GEMM.
+// -1 = not yet read from the environment.  The mode changes the workspace size: query and both passes must agree.
+std::atomic<int> g_probs_mode{-1};
+bool stored_probs_mode() {
+  int mode = g_probs_mode.load(std::memory_order_relaxed);
+  if (mode < 0) {
+    const char* e = getenv("ARCB_STORED_PROBS");
+    mode = (e && e[0] == '1') ? 1 : 0;
+    g_probs_mode.store(mode, std::memory_order_relaxed);
+  }
+  return mode == 1;
+}
+
 // Persistent per-shard workspace, carved deterministically from one caller-owned buffer.
 struct Workspace {
   int64_t B, Cs, D, Bp, Dp;
@@ -99,6 +113,9 @@ struct Workspace {
   unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
   int4* items;             // [items_cap][2] tile list of the persistent backward (bwd_items_kernel)
   int64_t items_cap;
+  __nv_bfloat16* probs;    // stored-probabilities mode only: P' [Cs, Bp]; else nullptr
+  __nv_bfloat16* xc;       // stored-probabilities mode only: c_i * x_hat [B, Dp], the dW operand
+  float* cvec;             // stored-probabilities mode only: c_i [Bp]
   int64_t total;
 };
 
@@ -140,6 +157,13 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
     const int64_t T = (Cs + 127) / 128, dn = (D + 255) / 256;
     w.items_cap = T * (w.Bp / kBNTile + dn) + ((B + 127) / 128) * dn * (2 * T + 1);
     w.items = reinterpret_cast<int4*>(take(w.items_cap * 32));
+  }
+  w.probs = nullptr; w.xc = nullptr; w.cvec = nullptr;
+  if (stored_probs_mode()) {  // at the end: every other offset is the same in both modes
+    w.xc = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
+    w.cvec = reinterpret_cast<float*>(take(w.Bp * 4));
+    w.probs = reinterpret_cast<__nv_bfloat16*>(take(Cs * w.Bp * 2));
+    if (!base) w.probs = nullptr, w.xc = nullptr, w.cvec = nullptr;
   }
   w.total = off;
   return w;
@@ -215,7 +239,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
 constexpr int kLaunchRefused = 1;  // internal: the cooperative launch was refused, try the next schedule
 
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
-template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false>
+template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false, bool PROBS = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
                           int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st, BwdSetup su,
                           unsigned long long* trace = nullptr) {
@@ -303,6 +327,9 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     su.zero_c = W.counters;
     su.n_c = 2 * pl.n_chunks + 1;
     su.n_phases = nph;
+    if (PROBS) {
+      su.cos_t = W.cos_t; su.cvec = W.cvec; su.xhat = W.xhat; su.xc = W.xc; su.Dp = (int)W.Dp;
+    }
     LaunchScope ls(ARCB_K_BWD_PREP, st);
     const int blocks = nph > 2 * device_sm_count() ? nph : 2 * device_sm_count();
     bwd_setup_kernel<<<blocks, 256, 0, st>>>(pl, W.items, su);
@@ -315,11 +342,15 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ok = ok && make_tmap_2d(&tmWhatK, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, kBK, kBM);
   constexpr int kBRows = PAIR ? kPBN / 2 : kPBN;  // rows / columns of the B tile one CTA stages
   ok = ok && make_tmap_2d(&tmXhatK, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, kBK, kBRows);
-  ok = ok && make_tmap_2d(&tmGtSt, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, 64, kBM);
-  ok = ok && make_tmap_mn3(&tmGtMN, gt, W.Bp, nbuf * chunk_rows, W.Bp * 2, kBM / 64);
+  // G^T as the dX / dW tiles see it: the chunk scratch, or (stored-probabilities mode) P' of the whole shard
+  const void* gsrc = PROBS ? static_cast<const void*>(W.probs) : static_cast<const void*>(gt);
+  const int64_t grows = PROBS ? Cs : nbuf * chunk_rows;
+  ok = ok && make_tmap_2d(&tmGtSt, gsrc, bf, 2, W.Bp, grows, W.Bp * 2, 64, kBM);
+  ok = ok && make_tmap_mn3(&tmGtMN, gsrc, W.Bp, grows, W.Bp * 2, kBM / 64);
   ok = ok && make_tmap_mn3(&tmWhatMN, W.what, W.Dp, Cs, W.Dp * 2, kBRows / 64);
-  ok = ok && make_tmap_2d(&tmGtK, gt, bf, 2, W.Bp, nbuf * chunk_rows, W.Bp * 2, kBK, kBM);
-  ok = ok && make_tmap_mn3(&tmXhatMN, W.xhat, W.Dp, B, W.Dp * 2, kBRows / 64);
+  ok = ok && make_tmap_2d(&tmGtK, gsrc, bf, 2, W.Bp, grows, W.Bp * 2, kBK, kBM);
+  // dW's B operand: x_hat, or c (.) x_hat when the stored P' still lack the per-sample factor
+  ok = ok && make_tmap_mn3(&tmXhatMN, PROBS ? W.xc : W.xhat, W.Dp, B, W.Dp * 2, kBRows / 64);
   ok = ok && make_tmap_2d(&tmDx, dxhat, f32, 4, D, B, W.Dp * 4, 32, kBM);
   if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the persistent backward could not be encoded");
   static int dw_direct = -1;  // ARCB_DW_DIRECT=1: dW rows are stored straight from registers (tuning aid)
@@ -336,8 +367,9 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ar.cos_t = W.cos_t; ar.tproj = W.tproj; ar.s2 = s * kLog2e; ar.grad_out = grad_logits; ar.ldgo = ldgl;
   ar.s_ext = s; ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.dw_tma = dw_tma ? 1 : 0;
   ar.trace = trace;
+  ar.probs = W.probs; ar.cvec = W.cvec; ar.ldp = W.Bp;
 
-  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE, DYN>;
+  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE, DYN, PROBS>;
   constexpr int kPSmemTotal = PCfg<PAIR>::kSmemTotal;
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -520,6 +552,11 @@ int arcb_set_pair_mode(int mode) {
   return ARCB_OK;
 }
 
+int arcb_set_stored_probs_mode(int on) {
+  g_probs_mode.store(on ? 1 : 0, std::memory_order_relaxed);
+  return ARCB_OK;
+}
+
 int arcb_set_forward_norm_mode(int mode) {
   if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "forward norm mode must be 0, 1 or 2");
   g_fuse_mode.store(mode, std::memory_order_relaxed);
@@ -673,7 +710,7 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   // measured on B200: the overlap pays (4-9 % of the forward) where the GEMM is long enough to hide the pass but
   // short enough that eight extra warps per SM do not cost it more than the pass itself: 512 <= B <= 1024, many
   // classes.  ARCB_FUSE_NORM=2 forces it for every shape (tests).
-  const bool shape_ok = fuse_env == 2 || (B >= 512 && B <= 1024 && Cs >= 65536);
+  const bool shape_ok = !stored_probs_mode() && (fuse_env == 2 || (B >= 512 && B <= 1024 && Cs >= 65536));
   bool fuse = fuse_env && shape_ok && !w_prenormalised && !use_pair_gemm() && (D % 4 == 0) && (ldw % 4 == 0) &&
               D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
   int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
@@ -682,7 +719,19 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
   cudaError_t e;
-  if (fuse) {
+  const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
+  if (W.probs) {
+    // transposed product, one 128-class block per tile row: the partial list has the same 2 * tiles_n entries
+    CUtensorMap tmP;
+    if (!make_tmap_2d(&tmP, W.probs, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W.Bp, Cs, W.Bp * 2, 64, kBM))
+      return fail(ARCB_ERR_CUDA, "tensor map for the stored probabilities could not be encoded");
+    Operand pa{W.what, Cs, W.Dp, W.Dp}, pb{W.xhat, B, W.Dp, W.Dp};
+    EpiFwdProbs::Params pp{W.cos_t, W.sub, W.lbl_local, W.part, (int)W.Bp, (int)B, (int)W.Bp, (int)Cs, s * kLog2e};
+    {
+      LaunchScope ls(ARCB_K_FWD_GEMM, st);
+      e = launch_gemm<EpiFwdProbs, kBNTile, 3, false, false>(pa, pb, &tmP, 2ll * tiles_n * kBM, W.Bp, W.Dp, 1, pp, st);
+    }
+  } else if (fuse) {
     NormArgs na;
     na.w = w; na.ldw = ldw; na.rows = Cs; na.D = (int)D; na.Dp = (int)W.Dp; na.what = W.what; na.inv_nw = W.inv_nw;
     na.done = W.counters;
@@ -707,7 +756,7 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
       if (rc) return rc;
     }
   }
-  if (!fuse) {
+  if (!fuse && !W.probs) {
     LaunchScope ls(ARCB_K_FWD_GEMM, st);
     static int fwd_stages = 0;
     if (!fwd_stages) {
@@ -719,7 +768,6 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
     else e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
-  const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
   const int blocks = static_cast<int>((B + 255) / 256);
   const int n_part = 2 * tiles_n;
   if (n_part > 4 * kMergeSlices) {  // two levels: 64 slices in parallel, then the 64 results + the shard record
@@ -894,6 +942,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   su.zero_a = W.tproj; su.n_a = Cs;
   su.zero_b = dxhat; su.n_b = B * W.Dp;
   su.zero_c = nullptr; su.n_c = 0; su.n_phases = 0;
+  su.cos_t = nullptr; su.cvec = nullptr; su.xhat = nullptr; su.xc = nullptr; su.Dp = 0;
 
   if (use_persistent_backward()) {
     // multi-buffered scratch: 4 buffers of `pchunk` classes each (fewer if the scratch is small)
@@ -934,7 +983,9 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       int64_t pc2 = pchunk / 256 * 256;
       if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
       if (pc2 >= 256) {
-        if (use_dynamic_feed())
+        if (use_dynamic_feed() && W.probs && !ext)  // stored-probabilities mode: no recompute GEMM
+          rc = launch_bwd_persistent<false, true, false, true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
+        else if (use_dynamic_feed())
           rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su)
                    : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
         else
@@ -992,7 +1043,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       const int tiles = static_cast<int>(((B + kBM - 1) / kBM) * ((D + kBNTile - 1) / kBNTile));
       int split = sms / (tiles > 0 ? tiles : 1);
       if (split < 1) split = 1;
-      EpiRedAdd::Params ep{(int)B, (int)D};
+      EpiRedAdd::Params ep{(int)B, (int)D, nullptr};
       LaunchScope ls(ARCB_K_DX_GEMM, st);
       cudaError_t e = launch_gemm<EpiRedAdd, kBNTile, 3, true, true>(a, b, &tmDx, B, D, rows, split, ep, st);
       if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));

@@ -181,6 +181,12 @@ int arcb_set_pair_mode(int mode);
  * where it is faster on B200 (512 <= B <= 1024, >= 65536 classes), else 0.  Same w_hat / inv_norm bits either way. */
 int arcb_set_forward_norm_mode(int mode);
 
+/* Stored-probabilities mode (experimental, off by default; ARCB_STORED_PROBS=1): arcb_shard_forward additionally
+ * keeps P' = bf16(2^(s log2e cos - ref_i)) for the whole shard ([Cs, Bp] at the end of the workspace, which
+ * arcb_ws_bytes then includes) so that the backward needs no recompute GEMM.  The workspace size depends on the
+ * mode: set it before arcb_ws_bytes and keep it unchanged until the matching arcb_shard_backward has been called. */
+int arcb_set_stored_probs_mode(int on);
+
 /* Backward schedule: 1 (default) = one persistent cooperative kernel per shard whose CTA pairs claim tiles from the
  * global tile list as they go, 2 = the same kernel with a fixed share of the list per CTA pair, 0 = one launch
  * per GEMM and class chunk.  All produce the same gradients (A/B testing, profiling). */

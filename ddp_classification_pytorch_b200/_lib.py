@@ -32,10 +32,19 @@ EXPORTED = [
     "arcb_version", "arcb_last_error", "arcb_check_watchdog", "arcb_l2norm_rows", "arcb_l2norm_rows_bwd",
     "arcb_gemm_bf16", "arcb_ws_bytes", "arcb_scratch_bytes", "arcb_shard_forward", "arcb_shard_logits",
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
-    "arcb_profile_collect", "arcb_set_backward_mode", "arcb_shard_forward_static", "arcb_shard_top3", "arcb_set_pair_mode",
+    "arcb_profile_collect", "arcb_shard_forward_static", "arcb_shard_top3",
     "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
-    "arcb_suggest_chunk_classes", "arcb_set_forward_norm_mode", "arcb_set_stored_probs_mode",
+    "arcb_suggest_chunk_classes",
 ]
+
+# per-call flags of include/arcface_b200.h (0 = library defaults)
+FWD_NORM_SEPARATE = 0x1
+FWD_NORM_FUSED = 0x2
+FWD_PAIR = 0x4
+GEMM_PAIR = 0x4
+BWD_PER_CHUNK = 0x10
+BWD_SINGLE_CTA = 0x20
+BWD_STATIC_SHARE = 0x40
 
 KERNEL_KINDS = [
     "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",
@@ -92,18 +101,18 @@ def _declare(lib):
     lib.arcb_l2norm_rows_bwd.restype = i32
     lib.arcb_l2norm_rows_bwd.argtypes = [vp, i64, vp, i64, i64, i64, vp, i64, vp]
     lib.arcb_gemm_bf16.restype = i32
-    lib.arcb_gemm_bf16.argtypes = [vp, i32, vp, i32, i64, i64, i64, i64, i64, vp, i64, i32, vp]
+    lib.arcb_gemm_bf16.argtypes = [vp, i32, vp, i32, i64, i64, i64, i64, i64, vp, i64, i32, i32, vp]
     lib.arcb_ws_bytes.restype = i64
-    lib.arcb_ws_bytes.argtypes = [i64, i64, i64]
+    lib.arcb_ws_bytes.argtypes = [i64, i64, i64, i32]
     lib.arcb_suggest_chunk_classes.restype = i64
     lib.arcb_suggest_chunk_classes.argtypes = [i64, i64, i64]
     lib.arcb_scratch_bytes.restype = i64
     lib.arcb_scratch_bytes.argtypes = [i64, i64]
     fwd_args = [vp, i64, vp, i64, vp, i64, i64, i64, i64, f32, f32, i32, vp, i64]
     lib.arcb_shard_forward.restype = i32
-    lib.arcb_shard_forward.argtypes = fwd_args + [vp, vp]
+    lib.arcb_shard_forward.argtypes = fwd_args + [vp, i32, vp]
     lib.arcb_shard_forward_prenorm.restype = i32
-    lib.arcb_shard_forward_prenorm.argtypes = fwd_args + [vp, vp]
+    lib.arcb_shard_forward_prenorm.argtypes = fwd_args + [vp, i32, vp]
     lib.arcb_ws_weight_slots.restype = i32
     lib.arcb_ws_weight_slots.argtypes = [vp, i64, i64, c.POINTER(vp), c.POINTER(vp)]
     lib.arcb_sgd_step.restype = i32
@@ -119,15 +128,7 @@ def _declare(lib):
     lib.arcb_merge_loss.restype = i32
     lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
     lib.arcb_shard_backward.restype = i32
-    lib.arcb_shard_backward.argtypes = [i64, i64, i64, f32, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, vp]
-    lib.arcb_set_pair_mode.restype = i32
-    lib.arcb_set_pair_mode.argtypes = [i32]
-    lib.arcb_set_forward_norm_mode.restype = i32
-    lib.arcb_set_forward_norm_mode.argtypes = [i32]
-    lib.arcb_set_stored_probs_mode.restype = i32
-    lib.arcb_set_stored_probs_mode.argtypes = [i32]
-    lib.arcb_set_backward_mode.restype = i32
-    lib.arcb_set_backward_mode.argtypes = [i32]
+    lib.arcb_shard_backward.argtypes = [i64, i64, i64, f32, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp, vp, i32, vp]
     lib.arcb_launch_count.restype = i64
     lib.arcb_launch_count.argtypes = []
     lib.arcb_profile_enable.restype = i32

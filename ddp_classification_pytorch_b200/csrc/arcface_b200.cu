@@ -50,7 +50,8 @@ inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 std::atomic<int64_t> g_launches{0};
 constexpr int kProfMax = 8192;
 struct Profiler {
-  bool on = false;
+  std::atomic<bool> on{false};
+  std::mutex mu;  // guards n / kind / created: forward (main thread) and backward (autograd thread) both launch
   int n = 0;
   cudaEvent_t beg[kProfMax];
   cudaEvent_t end[kProfMax];
@@ -63,10 +64,15 @@ struct LaunchScope {
   int slot;
   LaunchScope(int kind, cudaStream_t s, int nkernels = 1) : st(s), slot(-1) {
     g_launches.fetch_add(nkernels, std::memory_order_relaxed);
-    if (g_prof.on && g_prof.n < kProfMax) {
-      slot = g_prof.n++;
-      g_prof.kind[slot] = kind;
-      cudaEventRecord(g_prof.beg[slot], st);
+    if (g_prof.on.load(std::memory_order_relaxed)) {
+      {
+        std::lock_guard<std::mutex> lock(g_prof.mu);
+        if (g_prof.n < kProfMax) {
+          slot = g_prof.n++;
+          g_prof.kind[slot] = kind;
+        }
+      }
+      if (slot >= 0) cudaEventRecord(g_prof.beg[slot], st);
     }
   }
   ~LaunchScope() {
@@ -77,19 +83,42 @@ struct LaunchScope {
 constexpr int kBNTile = 256;
 constexpr int kMergeSlices = 64;
 
-// Stored-probabilities mode (arcb_set_stored_probs_mode / ARCB_STORED_PROBS): the fused forward keeps
-// P' = bf16(2^(s2 cos - ref2)) for the whole shard in the workspace and the backward runs without its recompute GEMM.
-// -1 = not yet read from the environment.  The mode changes the workspace size: query and both passes must agree.
-std::atomic<int> g_probs_mode{-1};
-bool stored_probs_mode() {
-  int mode = g_probs_mode.load(std::memory_order_relaxed);
-  if (mode < 0) {
-    const char* e = getenv("ARCB_STORED_PROBS");
-    mode = (e && e[0] == '1') ? 1 : 0;
-    g_probs_mode.store(mode, std::memory_order_relaxed);
-  }
-  return mode == 1;
+// Tuning / debugging knobs from the environment.  Read ONCE (std::call_once) and immutable afterwards, so there is
+// nothing for concurrent callers to race on; everything that selects a code path per call is the `flags` argument of
+// the entry points (include/arcface_b200.h), never process state.
+struct EnvKnobs {
+  int lag = 2;            // ARCB_LAG: phases between a chunk's G tiles and its X / W tiles
+  int x_splits = 0;       // ARCB_X_SPLITS: class slices per dX tile (0 = heuristic)
+  int kind_mask = 7;      // ARCB_DEBUG_KINDS: tile kinds that run (wrong results unless 7)
+  int debug_epi = 0;      // ARCB_DEBUG_EPI: G epilogue without math (1) / without TMEM loads (2)
+  int scratch_bufs = 4;   // ARCB_SCRATCH_BUFS: chunk buffers of the persistent backward
+  int trace = 0;          // ARCB_TRACE: per-tile clock stamps into the tail of the scratch
+  int norm_look = 0;      // ARCB_NORM_LOOK: look-ahead (B tiles) of the in-GEMM normaliser
+  int default_flags = 0;  // ARCB_DEFAULT_FLAGS: OR-ed into every call's flags (A/B runs of the tools)
+};
+const EnvKnobs& env_knobs() {
+  static EnvKnobs k;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    auto geti = [](const char* name, int dflt) {
+      const char* e = getenv(name);
+      return e ? static_cast<int>(strtol(e, nullptr, 0)) : dflt;
+    };
+    int v = geti("ARCB_LAG", 2);
+    k.lag = (v >= 1 && v <= 4) ? v : 2;
+    k.x_splits = geti("ARCB_X_SPLITS", 0);
+    v = geti("ARCB_DEBUG_KINDS", 7) & 7;
+    k.kind_mask = v ? v : 7;
+    k.debug_epi = geti("ARCB_DEBUG_EPI", 0);
+    v = geti("ARCB_SCRATCH_BUFS", 4);
+    k.scratch_bufs = (v >= 2 && v <= 6) ? v : 4;
+    k.trace = geti("ARCB_TRACE", 0) == 1;
+    k.norm_look = geti("ARCB_NORM_LOOK", 0);
+    k.default_flags = geti("ARCB_DEFAULT_FLAGS", 0);
+  });
+  return k;
 }
+inline int effective_flags(int flags) { return flags | env_knobs().default_flags; }
 
 // Persistent per-shard workspace, carved deterministically from one caller-owned buffer.
 struct Workspace {
@@ -113,9 +142,6 @@ struct Workspace {
   unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
   int4* items;             // [items_cap][2] tile list of the persistent backward (bwd_items_kernel)
   int64_t items_cap;
-  __nv_bfloat16* probs;    // stored-probabilities mode only: P' [Cs, Bp]; else nullptr
-  __nv_bfloat16* xc;       // stored-probabilities mode only: c_i * x_hat [B, Dp], the dW operand
-  float* cvec;             // stored-probabilities mode only: c_i [Bp]
   int64_t total;
 };
 
@@ -157,13 +183,6 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
     const int64_t T = (Cs + 127) / 128, dn = (D + 255) / 256;
     w.items_cap = T * (w.Bp / kBNTile + dn) + ((B + 127) / 128) * dn * (2 * T + 1);
     w.items = reinterpret_cast<int4*>(take(w.items_cap * 32));
-  }
-  w.probs = nullptr; w.xc = nullptr; w.cvec = nullptr;
-  if (stored_probs_mode()) {  // at the end: every other offset is the same in both modes
-    w.xc = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
-    w.cvec = reinterpret_cast<float*>(take(w.Bp * 4));
-    w.probs = reinterpret_cast<__nv_bfloat16*>(take(Cs * w.Bp * 2));
-    if (!base) w.probs = nullptr, w.xc = nullptr, w.cvec = nullptr;
   }
   w.total = off;
   return w;
@@ -239,7 +258,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
 constexpr int kLaunchRefused = 1;  // internal: the cooperative launch was refused, try the next schedule
 
 // ONE cooperative launch for the whole backward of a shard (bwd_persistent.cuh).
-template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false, bool PROBS = false>
+template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
                           int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st, BwdSetup su,
                           unsigned long long* trace = nullptr) {
@@ -248,11 +267,7 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   pl.chunk_rows = static_cast<int>(chunk_rows);
   pl.nbuf = nbuf;
   {
-    static int lag = 0;  // ARCB_LAG: tuning aid; nbuf >= lag + 2 keeps buffer-reuse waits a phase away
-    if (!lag) {
-      const char* e = getenv("ARCB_LAG");
-      lag = (e && e[0] >= '1' && e[0] <= '4') ? e[0] - '0' : 2;
-    }
+    const int lag = env_knobs().lag;  // nbuf >= lag + 2 keeps buffer-reuse waits a phase away
     pl.lag = lag < nbuf ? lag : (nbuf > 1 ? nbuf - 1 : 1);
   }
   pl.n_chunks = static_cast<int>((Cs + chunk_rows - 1) / chunk_rows);
@@ -274,43 +289,15 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     // another 128 KB of fp32 reduce-add traffic per tile column (measured best on B200: 4, see profiles/)
     int want_splits = (groups + tiles_mn - 1) / tiles_mn;
     if (want_splits > 4) want_splits = 4;
-    {
-      static int xs = -1;  // ARCB_X_SPLITS: override the number of class slices per dX tile (tuning aid)
-      if (xs < 0) {
-        const char* e = getenv("ARCB_X_SPLITS");
-        xs = e ? atoi(e) : 0;
-      }
-      if (xs > 0) want_splits = xs;
-    }
+    if (env_knobs().x_splits > 0) want_splits = env_knobs().x_splits;
     int per = (kbt + want_splits - 1) / want_splits;
     if (per < 4) per = 4;
     pl.x_kb_per_split = per;
   }
   pl.g_done = W.counters;
-  {
-    static int mask = -1;
-    if (mask < 0) {
-      const char* e = getenv("ARCB_DEBUG_KINDS");
-      mask = e ? atoi(e) & 7 : 7;
-      if (mask == 0) mask = 7;
-    }
-    pl.kind_mask = mask;
-  }
-  {
-    static int dbg = -1;
-    if (dbg < 0) {
-      const char* e = getenv("ARCB_DEBUG_EPI");
-      dbg = e ? atoi(e) : 0;
-    }
-    pl.debug_epi = dbg;
-    static int rot = -1;  // ARCB_ROT: slot rotation per dealing round of the tile list (tuning aid)
-    if (rot < 0) {
-      const char* e = getenv("ARCB_ROT");
-      rot = e ? atoi(e) : 0;
-      if (rot < 0) rot = 0;
-    }
-    pl.rot = rot;
-  }
+  pl.kind_mask = env_knobs().kind_mask;
+  pl.debug_epi = env_knobs().debug_epi;
+  pl.rot = 0;
   pl.xw_done = W.counters + pl.n_chunks;
   pl.claim = W.counters + 2 * pl.n_chunks;
   {
@@ -327,9 +314,6 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
     su.zero_c = W.counters;
     su.n_c = 2 * pl.n_chunks + 1;
     su.n_phases = nph;
-    if (PROBS) {
-      su.cos_t = W.cos_t; su.cvec = W.cvec; su.xhat = W.xhat; su.xc = W.xc; su.Dp = (int)W.Dp;
-    }
     LaunchScope ls(ARCB_K_BWD_PREP, st);
     const int blocks = nph > 2 * device_sm_count() ? nph : 2 * device_sm_count();
     bwd_setup_kernel<<<blocks, 256, 0, st>>>(pl, W.items, su);
@@ -342,23 +326,16 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ok = ok && make_tmap_2d(&tmWhatK, W.what, bf, 2, W.Dp, Cs, W.Dp * 2, kBK, kBM);
   constexpr int kBRows = PAIR ? kPBN / 2 : kPBN;  // rows / columns of the B tile one CTA stages
   ok = ok && make_tmap_2d(&tmXhatK, W.xhat, bf, 2, W.Dp, B, W.Dp * 2, kBK, kBRows);
-  // G^T as the dX / dW tiles see it: the chunk scratch, or (stored-probabilities mode) P' of the whole shard
-  const void* gsrc = PROBS ? static_cast<const void*>(W.probs) : static_cast<const void*>(gt);
-  const int64_t grows = PROBS ? Cs : nbuf * chunk_rows;
+  const void* gsrc = gt;  // G^T as the dX / dW tiles see it: the chunk scratch
+  const int64_t grows = nbuf * chunk_rows;
   ok = ok && make_tmap_2d(&tmGtSt, gsrc, bf, 2, W.Bp, grows, W.Bp * 2, 64, kBM);
   ok = ok && make_tmap_mn3(&tmGtMN, gsrc, W.Bp, grows, W.Bp * 2, kBM / 64);
   ok = ok && make_tmap_mn3(&tmWhatMN, W.what, W.Dp, Cs, W.Dp * 2, kBRows / 64);
   ok = ok && make_tmap_2d(&tmGtK, gsrc, bf, 2, W.Bp, grows, W.Bp * 2, kBK, kBM);
-  // dW's B operand: x_hat, or c (.) x_hat when the stored P' still lack the per-sample factor
-  ok = ok && make_tmap_mn3(&tmXhatMN, PROBS ? W.xc : W.xhat, W.Dp, B, W.Dp * 2, kBRows / 64);
+  ok = ok && make_tmap_mn3(&tmXhatMN, W.xhat, W.Dp, B, W.Dp * 2, kBRows / 64);
   ok = ok && make_tmap_2d(&tmDx, dxhat, f32, 4, D, B, W.Dp * 4, 32, kBM);
   if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the persistent backward could not be encoded");
-  static int dw_direct = -1;  // ARCB_DW_DIRECT=1: dW rows are stored straight from registers (tuning aid)
-  if (dw_direct < 0) {
-    const char* e = getenv("ARCB_DW_DIRECT");
-    dw_direct = (e && e[0] == '1') ? 1 : 0;
-  }
-  const bool dw_tma = !dw_direct && (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
+  const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
                       make_tmap_2d(&tmDw, dw, f32, 4, D, Cs, D * 4, 32, kBM);
   if (!dw_tma) tmDw = tmDx;
 
@@ -367,17 +344,16 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   ar.cos_t = W.cos_t; ar.tproj = W.tproj; ar.s2 = s * kLog2e; ar.grad_out = grad_logits; ar.ldgo = ldgl;
   ar.s_ext = s; ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.dw_tma = dw_tma ? 1 : 0;
   ar.trace = trace;
-  ar.probs = W.probs; ar.cvec = W.cvec; ar.ldp = W.Bp;
 
-  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE, DYN, PROBS>;
+  auto kern = bwd_persistent_kernel<EXT, PAIR, TRACE, DYN>;
   constexpr int kPSmemTotal = PCfg<PAIR>::kSmemTotal;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (!attr_set[dev]) {
+  if (!attr_set[dev].load(std::memory_order_acquire)) {  // idempotent: a race only repeats the call
     ARCB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPSmemTotal));
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   const long long total_items = pl.total_items;
   int groups = device_sm_count() / (PAIR ? 2 : 1);
@@ -435,58 +411,6 @@ int static_ws_address(void** out) {
   return ARCB_OK;
 }
 
-// CTA pairs (cta_group::2): 0 = nowhere, 1 = persistent backward only (default: measured best), 2 = every GEMM.
-// -1 = not yet read from the environment (ARCB_PAIR).
-std::atomic<int> g_pair_mode{-1};
-int pair_mode() {
-  int mode = g_pair_mode.load(std::memory_order_relaxed);
-  if (mode < 0) {
-    const char* e = getenv("ARCB_PAIR");
-    mode = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
-    g_pair_mode.store(mode, std::memory_order_relaxed);
-  }
-  return mode;
-}
-bool use_pair_gemm() { return pair_mode() == 2; }      // forward / unit-test GEMMs
-bool use_pair_backward() { return pair_mode() >= 1; }  // persistent backward
-
-// How CTA pairs get their tiles in the persistent backward: 1 = they claim them as they go (default), 0 = each pair
-// takes a fixed share of the list (A/B runs; ARCB_DYN=0 or arcb_set_backward_mode(2)).  -1 = not yet read.
-std::atomic<int> g_dyn_feed{-1};
-bool use_dynamic_feed() {
-  int dyn = g_dyn_feed.load(std::memory_order_relaxed);
-  if (dyn < 0) {
-    const char* e = getenv("ARCB_DYN");
-    dyn = (e && e[0] == '0') ? 0 : 1;
-    g_dyn_feed.store(dyn, std::memory_order_relaxed);
-  }
-  return dyn == 1;
-}
-
-// F.normalize(weight) inside the forward GEMM kernel: 0 = never (separate kernel), 1 = where it pays (default),
-// 2 = whenever the shape allows it.  -1 = not yet read from the environment (ARCB_FUSE_NORM).
-std::atomic<int> g_fuse_mode{-1};
-int forward_norm_mode() {
-  int mode = g_fuse_mode.load(std::memory_order_relaxed);
-  if (mode < 0) {
-    const char* e = getenv("ARCB_FUSE_NORM");
-    mode = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
-    g_fuse_mode.store(mode, std::memory_order_relaxed);
-  }
-  return mode;
-}
-
-std::atomic<int> g_bwd_mode{-1};  // -1: from the environment (default persistent), 0: per-chunk launches, 1: persistent
-bool use_persistent_backward() {
-  int mode = g_bwd_mode.load(std::memory_order_relaxed);
-  if (mode < 0) {
-    const char* e = getenv("ARCB_BWD_PERSISTENT");
-    mode = (e && e[0] == '0') ? 0 : 1;
-    g_bwd_mode.store(mode, std::memory_order_relaxed);
-  }
-  return mode == 1;
-}
-
 }  // namespace
 
 namespace {
@@ -528,51 +452,28 @@ int launch_optim(float* w, int64_t ldw, const float* dw, int64_t ldg, float* s0,
 
 extern "C" {
 
-int arcb_version(void) { return 100; }
+int arcb_version(void) { return 20000; }
 
 const char* arcb_last_error(void) { return g_err; }
 
 int arcb_check_watchdog(void* stream) {
-  ARCB_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  // A fired watchdog has trapped its kernel: the stream (and the context) report a launch failure from here on.
+  const cudaError_t e = cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess)
+    return fail(ARCB_ERR_TIMEOUT, "a kernel was aborted (device-side pipeline watchdog or a fault): %s",
+                cudaGetErrorString(e));
   unsigned int h[4] = {0, 0, 0, 0};
   ARCB_CUDA(cudaMemcpyFromSymbol(h, g_wait_timeout, sizeof(h)));
-  if (h[0]) {
-    unsigned int z[4] = {0, 0, 0, 0};
-    cudaMemcpyToSymbol(g_wait_timeout, z, sizeof(z));
-    return fail(ARCB_ERR_TIMEOUT, "pipeline watchdog fired: barrier tag 0x%x, block %u, parity %u", h[1], h[2], h[3]);
-  }
+  if (h[0]) return fail(ARCB_ERR_TIMEOUT, "pipeline watchdog fired: barrier tag 0x%x, block %u, arg %u", h[1], h[2], h[3]);
   return ARCB_OK;
 }
 
 int64_t arcb_padded_dim(int64_t D) { return round_up(D, 64); }
 
-int arcb_set_pair_mode(int mode) {
-  if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "pair mode must be 0, 1 or 2");
-  g_pair_mode.store(mode, std::memory_order_relaxed);
-  return ARCB_OK;
-}
-
-int arcb_set_stored_probs_mode(int on) {
-  g_probs_mode.store(on ? 1 : 0, std::memory_order_relaxed);
-  return ARCB_OK;
-}
-
-int arcb_set_forward_norm_mode(int mode) {
-  if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "forward norm mode must be 0, 1 or 2");
-  g_fuse_mode.store(mode, std::memory_order_relaxed);
-  return ARCB_OK;
-}
-
-int arcb_set_backward_mode(int mode) {
-  if (mode < 0 || mode > 2) return fail(ARCB_ERR_INVALID, "backward mode must be 0, 1 or 2");
-  g_bwd_mode.store(mode ? 1 : 0, std::memory_order_relaxed);
-  g_dyn_feed.store(mode == 2 ? 0 : 1, std::memory_order_relaxed);
-  return ARCB_OK;
-}
-
 int64_t arcb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 int arcb_profile_enable(int on) {
+  std::lock_guard<std::mutex> lock(g_prof.mu);
   if (on && !g_prof.created) {
     for (int i = 0; i < kProfMax; ++i) {
       ARCB_CUDA(cudaEventCreate(&g_prof.beg[i]));
@@ -580,8 +481,8 @@ int arcb_profile_enable(int on) {
     }
     g_prof.created = true;
   }
-  g_prof.on = on != 0;
   g_prof.n = 0;
+  g_prof.on.store(on != 0, std::memory_order_relaxed);
   return ARCB_OK;
 }
 
@@ -592,6 +493,7 @@ int arcb_profile_collect(double* ms_by_kind, int64_t* launches_by_kind, int nkin
     launches_by_kind[k] = 0;
   }
   ARCB_CUDA(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lock(g_prof.mu);
   for (int i = 0; i < g_prof.n; ++i) {
     float ms = 0.f;
     ARCB_CUDA(cudaEventElapsedTime(&ms, g_prof.beg[i], g_prof.end[i]));
@@ -627,15 +529,16 @@ int arcb_l2norm_rows_bwd(const float* x, int64_t ldx, const float* dxhat, int64_
 }
 
 int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, int64_t N, int64_t K, int64_t lda,
-                   int64_t ldb, float* out, int64_t ldo, int split_k, void* stream) {
+                   int64_t ldb, float* out, int64_t ldo, int split_k, int flags, void* stream) {
   if (!A || !B || !out) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  const bool pair_gemm = (effective_flags(flags) & ARCB_GEMM_PAIR) != 0;
   if (M <= 0 || N <= 0 || K <= 0 || (lda % 8) || (ldb % 8)) return fail(ARCB_ERR_INVALID, "bad GEMM sizes");
   Operand a{A, M, K, lda}, b{B, N, K, ldb};
   EpiStore::Params ep{out, ldo, (int)M, (int)N, split_k > 1 ? 1 : 0};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e;
   LaunchScope ls(ARCB_K_GEMM_TEST, st);
-  if (use_pair_gemm()) {
+  if (pair_gemm) {
     // an MN-major operand is addressed in whole 64-element blocks: its (zero padded) leading dimension is the extent
     if ((a_mn && (lda % 64 || lda < M)) || (b_mn && (ldb % 64 || ldb < N)))
       return fail(ARCB_ERR_INVALID, "pair GEMM: an MN-major operand needs a leading dimension that is a multiple of 64");
@@ -654,7 +557,8 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
   return ARCB_OK;
 }
 
-int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D) {
+int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D, int flags) {
+  (void)flags;  // no flag changes the layout today; the argument keeps the query a pure function if one ever does
   if (B <= 0 || Cs <= 0 || D <= 0) return -1;
   return carve(nullptr, B, Cs, D).total;
 }
@@ -699,53 +603,38 @@ int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes) {
 
 static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
                               int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
-                              int easy_margin, void* ws, int64_t ws_bytes, float* stats, void* stream,
+                              int easy_margin, void* ws, int64_t ws_bytes, float* stats, int flags, void* stream,
                               bool w_prenormalised) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (!stats) return fail(ARCB_ERR_INVALID, "null stats pointer");
+  flags = effective_flags(flags);
+  if ((flags & ARCB_FWD_NORM_SEPARATE) && (flags & ARCB_FWD_NORM_FUSED))
+    return fail(ARCB_ERR_INVALID, "ARCB_FWD_NORM_SEPARATE and ARCB_FWD_NORM_FUSED exclude each other");
+  const bool pair_gemm = (flags & ARCB_FWD_PAIR) != 0;
   Workspace W;
-  // F.normalize(weight) inside the GEMM kernel (ARCB_FUSE_NORM=0 switches back to the separate kernel); needs
-  // 16-byte aligned rows like the vector path of the stand-alone kernel, D <= 2048 and the one-CTA tile shape
-  const int fuse_env = forward_norm_mode();
-  // measured on B200: the overlap pays (4-9 % of the forward) where the GEMM is long enough to hide the pass but
-  // short enough that eight extra warps per SM do not cost it more than the pass itself: 512 <= B <= 1024, many
-  // classes.  ARCB_FUSE_NORM=2 forces it for every shape (tests).
-  const bool shape_ok = !stored_probs_mode() && (fuse_env == 2 || (B >= 512 && B <= 1024 && Cs >= 65536));
-  bool fuse = fuse_env && shape_ok && !w_prenormalised && !use_pair_gemm() && (D % 4 == 0) && (ldw % 4 == 0) &&
-              D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
+  // F.normalize(weight) inside the GEMM kernel; needs 16-byte aligned rows like the vector path of the stand-alone
+  // kernel, D <= 2048 and the one-CTA tile shape.  Measured on B200: the overlap pays (4-9 % of the forward) where the
+  // GEMM is long enough to hide the pass but short enough that eight extra warps per SM do not cost it more than the
+  // pass itself: 512 <= B <= 1024, many classes.  ARCB_FWD_NORM_FUSED forces it for every shape that allows it.
+  const bool shape_ok = (flags & ARCB_FWD_NORM_FUSED) || (B >= 512 && B <= 1024 && Cs >= 65536);
+  bool fuse = !(flags & ARCB_FWD_NORM_SEPARATE) && shape_ok && !w_prenormalised && !pair_gemm && (D % 4 == 0) &&
+              (ldw % 4 == 0) && D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
   int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
                           w_prenormalised ? 1 : (fuse ? 2 : 0));
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
-  cudaError_t e;
+  cudaError_t e = cudaSuccess;
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
-  if (W.probs) {
-    // transposed product, one 128-class block per tile row: the partial list has the same 2 * tiles_n entries
-    CUtensorMap tmP;
-    if (!make_tmap_2d(&tmP, W.probs, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W.Bp, Cs, W.Bp * 2, 64, kBM))
-      return fail(ARCB_ERR_CUDA, "tensor map for the stored probabilities could not be encoded");
-    Operand pa{W.what, Cs, W.Dp, W.Dp}, pb{W.xhat, B, W.Dp, W.Dp};
-    EpiFwdProbs::Params pp{W.cos_t, W.sub, W.lbl_local, W.part, (int)W.Bp, (int)B, (int)W.Bp, (int)Cs, s * kLog2e};
-    {
-      LaunchScope ls(ARCB_K_FWD_GEMM, st);
-      e = launch_gemm<EpiFwdProbs, kBNTile, 3, false, false>(pa, pb, &tmP, 2ll * tiles_n * kBM, W.Bp, W.Dp, 1, pp, st);
-    }
-  } else if (fuse) {
+  if (fuse) {
     NormArgs na;
     na.w = w; na.ldw = ldw; na.rows = Cs; na.D = (int)D; na.Dp = (int)W.Dp; na.what = W.what; na.inv_nw = W.inv_nw;
     na.done = W.counters;
     const int tiles_m = (int)((B + kBM - 1) / kBM);
     const int ahead = (device_sm_count() + tiles_m - 1) / tiles_m + 2;  // a CTA's last tile is at most this far from the end
     na.lookahead = ahead > 64 ? ahead : 64;                             // 64 B tiles of w_hat = 16 MB at D = 512
-    {
-      static int look = -1;  // ARCB_NORM_LOOK: override (tuning aid)
-      if (look < 0) {
-        const char* e1 = getenv("ARCB_NORM_LOOK");
-        look = e1 ? atoi(e1) : 0;
-      }
-      if (look > 0) na.lookahead = look > ahead ? look : ahead;
-    }
+    const int look = env_knobs().norm_look;
+    if (look > 0) na.lookahead = look > ahead ? look : ahead;
     {
       LaunchScope ls(ARCB_K_FWD_GEMM, st);
       e = launch_gemm_norm<EpiFwdStats, 4>(a, b, B, Cs, W.Dp, ep, na, st);
@@ -756,15 +645,9 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
       if (rc) return rc;
     }
   }
-  if (!fuse && !W.probs) {
+  if (!fuse) {
     LaunchScope ls(ARCB_K_FWD_GEMM, st);
-    static int fwd_stages = 0;
-    if (!fwd_stages) {
-      const char* e3 = getenv("ARCB_FWD_STAGES");
-      fwd_stages = (e3 && e3[0] == '3') ? 3 : 4;
-    }
-    if (use_pair_gemm()) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
-    else if (fwd_stages == 3) e = launch_gemm<EpiFwdStats, kBNTile, 3, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    if (pair_gemm) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
     else e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
@@ -784,16 +667,16 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
 
 int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
                        int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
-                       int64_t ws_bytes, float* stats, void* stream) {
+                       int64_t ws_bytes, float* stats, int flags, void* stream) {
   return shard_forward_impl(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, stats,
-                            stream, false);
+                            flags, stream, false);
 }
 
 int arcb_shard_forward_prenorm(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
                                int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
-                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, void* stream) {
+                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, int flags, void* stream) {
   return shard_forward_impl(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, stats,
-                            stream, true);
+                            flags, stream, true);
 }
 
 int arcb_ws_weight_slots(void* ws, int64_t Cs, int64_t D, void** w_hat_bf16, float** inv_norm_w) {
@@ -859,7 +742,7 @@ int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64
   // Nothing in the forward workspace has to start from zero: every region is fully rewritten
   // (normalised operands incl. their padding, per-sample target data, per-tile partials) before it is read.
   return arcb_shard_forward(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, kStaticWsBytes,
-                            stats, stream);
+                            stats, 0, stream);
 }
 
 int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
@@ -918,11 +801,15 @@ int arcb_merge_loss(const float* stats, int64_t P, int64_t B, float* lse, float*
 
 int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int64_t ws_bytes, const float* lse,
                         const float* target_logit, const float* grad_loss, const float* grad_logits, int64_t ldgl,
-                        void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, void* stream) {
+                        void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, int flags, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = check_dims(B, Cs, D);
   if (rc) return rc;
   if (!ws || !scratch || !dw || !dxhat) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  flags = effective_flags(flags);
+  const bool persistent = !(flags & ARCB_BWD_PER_CHUNK);
+  const bool pair_bwd = !(flags & ARCB_BWD_SINGLE_CTA);
+  const bool dyn_feed = !(flags & ARCB_BWD_STATIC_SHARE);
   const bool ext = grad_logits != nullptr;
   if (!ext && (!lse || !target_logit)) return fail(ARCB_ERR_INVALID, "lse / target_logit required");
   if (ext && ldgl < Cs) return fail(ARCB_ERR_INVALID, "grad_logits leading dimension smaller than Cs");
@@ -942,36 +829,25 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   su.zero_a = W.tproj; su.n_a = Cs;
   su.zero_b = dxhat; su.n_b = B * W.Dp;
   su.zero_c = nullptr; su.n_c = 0; su.n_phases = 0;
-  su.cos_t = nullptr; su.cvec = nullptr; su.xhat = nullptr; su.xc = nullptr; su.Dp = 0;
 
-  if (use_persistent_backward()) {
+  if (persistent) {
     // multi-buffered scratch: 4 buffers of `pchunk` classes each (fewer if the scratch is small)
-    static int want_bufs = 0;
-    if (!want_bufs) {
-      const char* e = getenv("ARCB_SCRATCH_BUFS");
-      want_bufs = (e && e[0] >= '2' && e[0] <= '6') ? e[0] - '0' : 4;
-    }
-    int nbuf = want_bufs;
+    int nbuf = env_knobs().scratch_bufs;
     int64_t pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
     while (pchunk < 256 && nbuf > 2) {
       --nbuf;
       pchunk = scratch_bytes / (W.Bp * 2) / nbuf / 128 * 128;
     }
     // debug trace (ARCB_TRACE=1, fused path only): the last 1 MiB of the scratch receives per-tile clock stamps
-    static int want_trace = -1;
-    if (want_trace < 0) {
-      const char* e = getenv("ARCB_TRACE");
-      want_trace = (e && e[0] == '1') ? 1 : 0;
-    }
-    if (want_trace && !ext && scratch_bytes > (4ll << 20)) {
+    if (env_knobs().trace && !ext && scratch_bytes > (4ll << 20)) {
       const int64_t usable = scratch_bytes - (1ll << 20);
       unsigned long long* trace = reinterpret_cast<unsigned long long*>(static_cast<char*>(scratch) + usable);
       ARCB_CUDA(cudaMemsetAsync(trace, 0, 1ll << 20, st));
       int64_t pc = usable / (W.Bp * 2) / nbuf / 256 * 256;
       if (pc > round_up(Cs, 256)) pc = round_up(Cs, 256);
       if (pc >= 256) {
-        if (use_pair_backward()) {
-          if (use_dynamic_feed())
+        if (pair_bwd) {
+          if (dyn_feed)
             return launch_bwd_persistent<false, true, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st,
                                                                   su, trace);
           return launch_bwd_persistent<false, true, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, su, trace);
@@ -979,13 +855,11 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
         return launch_bwd_persistent<false, false, true>(W, s, grad_logits, ldgl, gt, pc, nbuf, dw, dxhat, st, su, trace);
       }
     }
-    if (use_pair_backward()) {  // a pair's tile has 256 rows: chunks (= scratch buffers) must be whole tiles
+    if (pair_bwd) {  // a pair's tile has 256 rows: chunks (= scratch buffers) must be whole tiles
       int64_t pc2 = pchunk / 256 * 256;
       if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
       if (pc2 >= 256) {
-        if (use_dynamic_feed() && W.probs && !ext)  // stored-probabilities mode: no recompute GEMM
-          rc = launch_bwd_persistent<false, true, false, true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
-        else if (use_dynamic_feed())
+        if (dyn_feed)
           rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su)
                    : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
         else

@@ -98,9 +98,6 @@ struct BwdArgs {
   const __nv_bfloat16* what;
   const float* inv_nw;
   int dw_tma;
-  __nv_bfloat16* probs;   // PROBS only: P' [Cs, Bp] (label entries are patched in place)
-  const float* cvec;      // PROBS only: c_i = gscale * 2^(ref2_i - lse2_i) [Bp], 0 on padding
-  int64_t ldp;            // PROBS only: Bp
   unsigned long long* trace;  // TRACE builds only: [8 CTAs][kTraceItems][kTraceWords] clock64 stamps
 };
 
@@ -240,13 +237,6 @@ struct BwdSetup {
   unsigned int* zero_c;    // counters
   int n_c;
   int n_phases;            // 0: no tile list (per-chunk schedule)
-  // stored-probabilities mode (cvec != nullptr): c_i = gscale * 2^(ref2_i - lse2_i) with ref2_i = s2 (cos_t,i + 1),
-  // and the dW operand xc = bf16(c_i * x_hat_i)
-  const float* cos_t;
-  float* cvec;
-  const __nv_bfloat16* xhat;
-  __nv_bfloat16* xc;
-  int Dp;
 };
 
 __global__ void __launch_bounds__(256) bwd_setup_kernel(const BwdPlan pl, int4* __restrict__ out, const BwdSetup su) {
@@ -267,19 +257,6 @@ __global__ void __launch_bounds__(256) bwd_setup_kernel(const BwdPlan pl, int4* 
     for (long long i = tid; i < su.Bp; i += nthr) {
       su.lse2[i] = (i < su.B) ? su.lse[i] * kLog2e : INFINITY;
       su.zt2[i] = (i < su.B) ? su.zt[i] * kLog2e : -INFINITY;
-    }
-  }
-  if (su.cvec) {  // one warp per sample
-    const int lane = threadIdx.x & 31;
-    const float gs = (su.grad_loss ? *su.grad_loss : 1.f) * su.s / static_cast<float>(su.B);
-    const float s2 = su.s * kLog2e;
-    for (long long i = tid >> 5; i < su.Bp; i += nthr >> 5) {
-      float c = 0.f;
-      if (i < su.B) c = gs * ex2_approx(s2 * (su.cos_t[i] + 1.f) - su.lse[i] * kLog2e);
-      if (lane == 0) su.cvec[i] = c;
-      if (i < su.B)
-        for (int d = lane; d < su.Dp; d += 32)
-          su.xc[i * su.Dp + d] = __float2bfloat16_rn(c * __bfloat162float(su.xhat[i * su.Dp + d]));
     }
   }
   for (long long i = tid; i < su.n_a; i += nthr) su.zero_a[i] = 0.f;
@@ -444,7 +421,7 @@ __device__ __forceinline__ void ld3(void* dst, const CUtensorMap* tm, uint32_t b
   }
 }
 
-template <bool EXT, bool PAIR, bool TRACE, bool DYN, bool PROBS = false>
+template <bool EXT, bool PAIR, bool TRACE, bool DYN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [Cs, Dp]   box 64 x 128  (A of G)
                       const __grid_constant__ CUtensorMap tmXhatK,   // x_hat [B, Dp]    box 64 x 256  (B of G)
@@ -457,10 +434,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
                       const __grid_constant__ CUtensorMap tmDw,      // dW    [Cs, D] f32 box 32 x 128
                       const BwdPlan pl, const BwdArgs ar) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  if ((smem_u32(smem) & 1023u) != 0u) {  // the 128 B swizzle needs 1024 B aligned tiles; no slack is reserved
-    if (threadIdx.x == 0 && atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) g_wait_timeout[1] = 0xa11u;
-    return;
-  }
+  if ((smem_u32(smem) & 1023u) != 0u) watchdog_abort(0xa11u, 0u);  // 128 B swizzle needs 1024 B aligned tiles; no slack is reserved
   using C = PCfg<PAIR>;
   constexpr int kPStages = C::kStages;
   constexpr int kPStageBytes = C::kStageBytes;
@@ -478,10 +452,6 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
   uint64_t* feed_taken = feed_empty + C::kRing;               // ... and the claimer's own producer has started on it
   uint8_t* ring_smem = smem + C::kRingOff;
   static_assert(!DYN || PAIR, "the dynamic feed uses the follower CTA's idle warp 1 as claimer");
-  static_assert(!PROBS || !EXT, "stored probabilities belong to the fused-loss path");
-  // PROBS (stored-probabilities mode): the forward left P' = bf16(2^(s2 cos - ref2)) for the whole shard, so a G item
-  // needs no MMA -- it is an epilogue-only pass over its P' tile (t_j, exact label entries) -- and the X / W tiles
-  // load P' itself (the G^T tensor maps describe [Cs, Bp] instead of the chunk scratch).
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + C::kNumBars);
   const int rank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;   // position inside the CTA pair
   const bool leader = rank == 0;
@@ -548,7 +518,6 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       int item_no = -1;
       while (w.next(pl, it)) {
         if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
-        if (PROBS && it.kind == kItemG) continue;  // epilogue-only tile
         ++item_no;
         unsigned long long* tr = trace_slot<TRACE>(ar, item_no);
         long long w_empty = 0;
@@ -563,7 +532,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         }
         const int mblk = it.m_blk * C::kCtas + rank;            // this CTA's 128-row block of the tile
         const int c0 = it.chunk * pl.chunk_rows;                // first class of the chunk in the shard
-        const int buf_row = PROBS ? c0 : it.buf * pl.chunk_rows;  // first row of the chunk in G^T (scratch buffer / P')
+        const int buf_row = it.buf * pl.chunk_rows;             // first row of the chunk in the G^T scratch
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           if (tr) {
             const long long t0 = clock64();
@@ -616,7 +585,6 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       int item_no = -1;
       while (w.next(pl, it)) {
         if (it.kb0 >= it.kb1 || !((pl.kind_mask >> it.kind) & 1)) continue;
-        if (PROBS && it.kind == kItemG) continue;  // epilogue-only tile
         ++item_no;
         unsigned long long* tr = trace_slot<TRACE>(ar, item_no);
         long long w_full = 0;
@@ -678,7 +646,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       Item it;
       uint32_t n_box = 0;  // boxes this issuer has sent so far (two per G tile); box n lives in buffer n % kBufs
       while (w.next(pl, it)) {
-        if (PROBS || it.kind != kItemG || it.kb0 >= it.kb1 || !(pl.kind_mask & 1)) continue;
+        if (it.kind != kItemG || it.kb0 >= it.kb1 || !(pl.kind_mask & 1)) continue;
         const int buf_row = it.buf * pl.chunk_rows;
         const int mblk = it.m_blk * C::kCtas + rank;
         for (int bx = 0; bx < 2; ++bx, ++n_box) {
@@ -726,84 +694,6 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
       if (tr) {
         tr[4] = clock64();
         tr[9] = it.kind;
-      }
-      if constexpr (PROBS) {
-        if (it.kind == kItemG) {
-          // ---- epilogue-only pass over the P' tile of this CTA: 128 classes x this warpgroup's 128 samples ----
-          //   t_j += sum_i c_i P'_ji cos_ji  with  cos_ji = (ref2_i + log2 P'_ji) / s2  (from the stored, rounded P');
-          //   label entries: exact fp32 gradient g_t (target_prep data), contribution g_t * cos_t, and the entry is
-          //   rewritten as g_t / c_i so that c_i * P' is the true gradient for the dX / dW tiles that follow.
-          const int mblk_t = it.m_blk * C::kCtas + rank;
-          const int c0_t = it.chunk * pl.chunk_rows;
-          const int row_local = mblk_t * kBM + row_in_tile;
-          const int cls = c0_t + row_local;
-          const bool row_ok = row_local < plan_rows(pl, it.chunk);
-          const int col_base = it.n_blk * kPBN + wg * 128;
-          float* ref_s = lse_s;                               // ref2_i
-          float* cs_s = reinterpret_cast<float*>(lbl_s);      // c_i / s2
-          named_bar_sync(2 + wg, kWgThreads);                 // the previous tile's readers of the staging are done
-          {
-            const int i = col_base + wg_tid;
-            const bool in_b = i < pl.B;
-            ref_s[wg_tid] = in_b ? ar.s2 * (__ldg(ar.cos_t + i) + 1.f) : 0.f;
-            cs_s[wg_tid] = in_b ? __ldcg(ar.cvec + i) / ar.s2 : 0.f;
-          }
-          named_bar_sync(2 + wg, kWgThreads);
-          const __nv_bfloat16* prow = ar.probs + static_cast<int64_t>(row_ok ? cls : 0) * ar.ldp + col_base;
-          float tsum = 0.f;
-          // the whole 256-byte row segment is requested before any of it is used: one memory latency per tile
-          // instead of four (P' comes from HBM here; the dX / dW tiles then find the chunk in L2)
-          uint4 rawall[16];
-#pragma unroll
-          for (int q = 0; q < 16; ++q) rawall[q] = *reinterpret_cast<const uint4*>(prow + q * 8);
-#pragma unroll
-          for (int cl = 0; cl < 128; cl += 32) {
-            uint4 raw[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) raw[q] = rawall[(cl >> 3) + q];
-            if (row_ok) {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const uint32_t wr[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const float p0 = __uint_as_float(wr[e] << 16), p1 = __uint_as_float(wr[e] & 0xffff0000u);
-                  const int j = cl + q * 8 + 2 * e;
-                  // P' = 0 (flushed): no contribution (and log2 would be -inf)
-                  tsum += (p0 > 0.f) ? cs_s[j] * p0 * (ref_s[j] + lg2_approx(p0)) : 0.f;
-                  tsum += (p1 > 0.f) ? cs_s[j + 1] * p1 * (ref_s[j + 1] + lg2_approx(p1)) : 0.f;
-                }
-              }
-            }
-            // label columns of this chunk that fall into this tile's 128 classes (warp-uniform, rare)
-            const int my_lbl = __ldg(ar.lbl_local + col_base + cl + lane);
-            unsigned hit = __ballot_sync(0xffffffffu, static_cast<unsigned>(my_lbl - (c0_t + mblk_t * kBM)) <
-                                                          static_cast<unsigned>(kBM));
-            while (hit) {
-              const int j = __ffs(hit) - 1;
-              hit &= hit - 1;
-              const int tl = __shfl_sync(0xffffffffu, my_lbl, j);
-              if (tl == cls && row_ok) {  // the one thread that owns the label's class row
-                const int i = col_base + cl + j;
-                const float ct = __ldg(ar.cos_t + i);
-                const float gt = gscale * (ex2_approx(__ldg(ar.zt2 + i) - __ldg(ar.lse2 + i)) - 1.f) * __ldg(ar.dphi + i);
-                const float ci = cs_s[cl + j] * ar.s2;
-                const float pold = __bfloat162float(prow[cl + j]);  // what the loop above has just added for it
-                // remove what the stored entry contributed above, add the exact term
-                if (pold > 0.f) tsum -= cs_s[cl + j] * pold * (ref_s[cl + j] + lg2_approx(pold));
-                tsum += gt * ct;
-                ar.probs[static_cast<int64_t>(cls) * ar.ldp + i] = __float2bfloat16_rn(ci != 0.f ? gt / ci : 0.f);
-              }
-            }
-          }
-          if (row_ok) atomicAdd(ar.tproj + cls, tsum);
-          named_bar_sync(2 + wg, kWgThreads);  // every thread's atomics and patches are issued
-          if (wg_tid == 0) {
-            __threadfence();
-            atomicAdd(pl.g_done + it.chunk, 1u);  // each G tile counts twice: once per warpgroup (as the store issuers did)
-          }
-          continue;  // no accumulator was involved: the TMEM stage and the output slots stay as they are
-        }
       }
       // per-tile row data is fetched before waiting for the accumulator, so its latency is hidden
       float lse_v = 0.f;
@@ -941,7 +831,7 @@ bwd_persistent_kernel(const __grid_constant__ CUtensorMap tmWhatK,   // w_hat [C
         EpiRedAdd::Params p;
         p.M = pl.B;
         p.N = pl.D;
-        p.row_scale = PROBS ? ar.cvec : nullptr;  // dX_hat_i = c_i * sum_j P'_ji w_hat_j
+        p.row_scale = nullptr;
         EpiRedAdd::template consume<kPBN, kBufs>(p, ost, tc, tmDx, taddr, row_in_tile, epi_tid, epi_smem);
         tc_fence_before();
         __syncwarp();

@@ -385,129 +385,6 @@ struct EpiBwdG {
 };
 
 // ------------------------------------------------------------------------------------
-// Forward that KEEPS the probabilities (stored-probabilities mode: the backward then needs no recompute GEMM).
-// The product is taken transposed -- rows = classes of this shard, columns = batch samples, like the backward's
-// recompute tile -- and every entry is written as
-//     P'[j, i] = bf16( 2^( s2 * cos_ji - ref2_i ) ),   ref2_i = s2 * (cos_target,i + 1)
-// a per-sample reference known BEFORE the GEMM (target_prep): no running maximum, every term inside bf16 / fp32
-// range for s <= 78 (cos_max - 1.36 <= cos_t + 1 <= cos_max + 1.08 always holds).  The label entry carries the
-// margin value (2^(s2 * sub_i - ref2_i)).  The tile goes through a 128B-swizzled smem tile + 4 bulk tensor stores
-// into P' [Cs, Bp]; one pass down the columns of that smem tile gives, per sample and 128-class block, the
-// (max, sum) partial in exactly the format EpiFwdStats produces, from the ROUNDED values (what the backward will
-// use, so the softmax it implies sums to one): part[m_blk][i] = (ref2_i + log2(max P'), sum P' / max P').
-struct EpiFwdProbs {
-  static constexpr int kStageBytes = kBM * 256 * 2;             // bf16 tile, 4 boxes of [128 x 64]
-  static constexpr int kSmemBytes = kStageBytes + 256 * 4 * 2;  // + ref2 and labels of the tile's samples
-  static constexpr bool kUsesTmC = true;                        // tmC: P' [Cs, Bp] bf16, box [128 x 64]
-  struct Params {
-    const float* cos_t;      // [Bp] exact fp32 target cosine (0 on padding)
-    const float* sub;        // [Bp] value that replaces the target cosine (phi or the fallback)
-    const int* lbl_local;    // [Bp], -1 = not in this shard / padding
-    float2* part;            // [ceil(rows / 128)][ldp]
-    int ldp;
-    int B, Bp, Cs;
-    float s2;
-  };
-  struct State {
-    float ref2;  // of sample (tile column) epi_tid, kept from consume() to finish()
-  };
-  __device__ static void init(const Params&, State& st) { st.ref2 = INFINITY; }
-  __device__ static void drain(int epi_tid) {
-    if (epi_tid == 0) tma_store_wait_all0();
-  }
-  template <int BN>
-  __device__ static void consume(const Params& p, State& st, const TileCoord& tc, const CUtensorMap&, uint32_t taddr,
-                                 int row_in_tile, int epi_tid, uint8_t* smem) {
-    static_assert(BN == 256, "staging tile is sized for BN = 256");
-    if (epi_tid == 0) tma_store_wait_read0();  // the previous tile's stores have finished reading the staging tile
-    float* ref_s = reinterpret_cast<float*>(smem + kStageBytes);
-    int* lbl_s = reinterpret_cast<int*>(smem + kStageBytes + 256 * 4);
-    const int col = tc.n_blk * BN + epi_tid;
-    st.ref2 = (col < p.B) ? p.s2 * (__ldg(p.cos_t + col) + 1.f) : INFINITY;  // padding samples: P' = 0
-    ref_s[epi_tid] = st.ref2;
-    lbl_s[epi_tid] = (col < p.Bp) ? __ldg(p.lbl_local + col) : -1;
-    named_bar_sync(1, kEpiThreads);  // also: every thread is past finish() of the previous tile
-    const int wg = epi_tid >> 7;
-    const int lane = epi_tid & 31;
-    const int cls = tc.m_blk * kBM + row_in_tile;  // class row of this thread inside the shard
-    const bool row_ok = cls < p.Cs;
-    const uint32_t srow = smem_u32(smem) + row_in_tile * 128;
-    const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
-    for (int c = wg * (BN / 2); c < (wg + 1) * (BN / 2); c += 32) {
-      float v[32];
-      tmem_ld32(taddr + c, v);
-      float g[32];
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const float4 r4 = *reinterpret_cast<const float4*>(ref_s + c + j);
-        g[j + 0] = row_ok ? ex2_approx(fmaf(v[j + 0], p.s2, -r4.x)) : 0.f;
-        g[j + 1] = row_ok ? ex2_approx(fmaf(v[j + 1], p.s2, -r4.y)) : 0.f;
-        g[j + 2] = row_ok ? ex2_approx(fmaf(v[j + 2], p.s2, -r4.z)) : 0.f;
-        g[j + 3] = row_ok ? ex2_approx(fmaf(v[j + 3], p.s2, -r4.w)) : 0.f;
-      }
-      // label columns of this chunk that fall into this tile's 128 classes (warp-uniform, rare)
-      const int my_lbl = lbl_s[c + lane];
-      unsigned hit = __ballot_sync(0xffffffffu, static_cast<unsigned>(my_lbl - tc.m_blk * kBM) < static_cast<unsigned>(kBM));
-      while (hit) {
-        const int j = __ffs(hit) - 1;
-        hit &= hit - 1;
-        const int tl = __shfl_sync(0xffffffffu, my_lbl, j);
-        if (tl == cls) {  // the one thread that owns the label's class row
-          const int i = tc.n_blk * BN + c + j;
-          const float pt = ex2_approx(fmaf(__ldg(p.sub + i), p.s2, -ref_s[c + j]));
-#pragma unroll
-          for (int jj = 0; jj < 32; ++jj)
-            if (jj == j) g[jj] = pt;
-        }
-      }
-      const uint32_t box = srow + static_cast<uint32_t>(c >> 6) * (kBM * 128);
-      const uint32_t q0 = static_cast<uint32_t>((c & 63) >> 3);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint32_t a = box + (((q0 + q) ^ sw) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(g[q * 8 + 0], g[q * 8 + 1])),
-                     "r"(pack_bf16x2(g[q * 8 + 2], g[q * 8 + 3])), "r"(pack_bf16x2(g[q * 8 + 4], g[q * 8 + 5])),
-                     "r"(pack_bf16x2(g[q * 8 + 6], g[q * 8 + 7]))
-                     : "memory");
-      }
-    }
-  }
-  template <int BN>
-  __device__ static void finish(const Params& p, State& st, const TileCoord& tc, const CUtensorMap& tmC, int, int epi_tid,
-                                uint8_t* smem) {
-    fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
-    named_bar_sync(1, kEpiThreads);
-    if (epi_tid == 0) {
-#pragma unroll
-      for (int bx = 0; bx < BN / 64; ++bx) {
-        const int col0 = tc.n_blk * BN + bx * 64;
-        if (col0 < p.Bp) tma_store_2d(&tmC, smem + bx * (kBM * 128), col0, tc.m_blk * kBM);
-      }
-      tma_store_commit();
-    }
-    // column pass: thread t owns sample column t of the tile; 128 rows of 2 bytes, lanes side by side in a row
-    const int col = tc.n_blk * BN + epi_tid;
-    const uint32_t cbase = smem_u32(smem) + static_cast<uint32_t>(epi_tid >> 6) * (kBM * 128) +
-                           static_cast<uint32_t>((epi_tid & 7) * 2);
-    const uint32_t q = static_cast<uint32_t>((epi_tid & 63) >> 3);
-    float mx = 0.f, sum = 0.f;
-#pragma unroll 8
-    for (int r = 0; r < kBM; ++r) {
-      unsigned short h;
-      const uint32_t a = cbase + static_cast<uint32_t>(r) * 128 + ((q ^ static_cast<uint32_t>(r & 7)) << 4);
-      asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h) : "r"(a));
-      const float v = __uint_as_float(static_cast<uint32_t>(h) << 16);
-      mx = fmaxf(mx, v);
-      sum += v;
-    }
-    if (col < p.B) {
-      const float2 out = (mx > 0.f) ? make_float2(st.ref2 + log2f(mx), sum / mx) : make_float2(-INFINITY, 0.f);
-      p.part[static_cast<int64_t>(tc.m_blk) * p.ldp + col] = out;
-    }
-  }
-};
-
-// ------------------------------------------------------------------------------------
 // Split-K partial sums: global[M, N] += tile, as bulk tensor reduce-adds (fp32) in L2.
 struct EpiRedAdd {
   static constexpr int kSmemBytes = kChunkOutSmem;

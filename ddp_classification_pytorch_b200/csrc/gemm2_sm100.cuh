@@ -65,10 +65,7 @@ gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
 
-  if ((smem_u32(smem) & 1023u) != 0u) {  // no alignment slack is reserved; uniform over the cluster
-    if (threadIdx.x == 0 && atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) g_wait_timeout[1] = 0xa12u;
-    return;
-  }
+  if ((smem_u32(smem) & 1023u) != 0u) watchdog_abort(0xa12u, 0u);  // no alignment slack is reserved
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -223,7 +220,6 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
   sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
   sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
   sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
-  sc.debug_split_b = 0;
   if (split_k < 1) split_k = 1;
   if (split_k > sc.kb_total) split_k = sc.kb_total;
   sc.kb_per_split = (sc.kb_total + split_k - 1) / split_k;
@@ -234,14 +230,14 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
   if (pairs > total) pairs = total;
   if (pairs < 1) pairs = 1;
   auto kern = gemm2_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN>;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];  // zero-initialised; forward and backward call in from different threads
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (!attr_set[dev]) {
+  if (!attr_set[dev].load(std::memory_order_acquire)) {  // idempotent: a race only repeats the call
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return e;
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);

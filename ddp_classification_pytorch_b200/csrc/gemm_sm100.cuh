@@ -22,6 +22,8 @@
 
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "ptx_sm100.cuh"
 #include "rowwise.cuh"
 
@@ -38,7 +40,6 @@ struct GemmSched {
   int k_splits;
   int kb_total;      // number of kBK-blocks over the whole K extent
   int kb_per_split;  // ceil(kb_total / k_splits)
-  int debug_split_b; // experiment switch (ARCB_DEBUG_SPLIT_B): load a K-major B tile as four boxes
 };
 
 // Work of the optional normaliser warps (NORM = true: warps 12..15, forward GEMM only): F.normalize(self.weight)
@@ -159,13 +160,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               tma_load_2d(sa + j * (kBK * 128), &tmA, &full[stage], tc.m_blk * kBM + j * 64, kb * kBK);
           }
           if constexpr (!B_MN) {
-            if (sc.debug_split_b) {  // experiment: same bytes as four 64-row boxes (needs a 64-row tensor-map box)
-#pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_2d(sb + j * (64 * 128), &tmB, &full[stage], kb * kBK, tc.n_blk * BN + j * 64);
-            } else {
-              tma_load_2d(sb, &tmB, &full[stage], kb * kBK, tc.n_blk * BN);
-            }
+            tma_load_2d(sb, &tmB, &full[stage], kb * kBK, tc.n_blk * BN);
           } else {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
@@ -284,7 +279,8 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_
 
 // Resolved once per process through the runtime, so the library does not link libcuda.
 inline PFN_encodeTiled get_encode_fn() {
-  static PFN_encodeTiled fn = nullptr;
+  static std::atomic<PFN_encodeTiled> cached{nullptr};
+  PFN_encodeTiled fn = cached.load(std::memory_order_acquire);
   if (fn) return fn;
   void* p = nullptr;
   cudaDriverEntryPointQueryResult qres;
@@ -292,6 +288,7 @@ inline PFN_encodeTiled get_encode_fn() {
       qres != cudaDriverEntryPointSuccess)
     return nullptr;
   fn = reinterpret_cast<PFN_encodeTiled>(p);
+  cached.store(fn, std::memory_order_release);
   return fn;
 }
 
@@ -349,16 +346,17 @@ inline bool make_operand_tmap(CUtensorMap* tm, const Operand& op, int box_mn) {
 }
 
 inline int device_sm_count() {
-  static int sms[64] = {0};
+  static std::atomic<int> sms[64];
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (sms[dev] == 0) {
-    int n = 0;
+  int n = sms[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    sms[dev] = n > 0 ? n : 148;
+    if (n <= 0) n = 148;
+    sms[dev].store(n, std::memory_order_relaxed);
   }
-  return sms[dev];
+  return n;
 }
 
 // Launch one GEMM.  M/N/K are the logical extents; split_k > 1 partitions K across CTAs (the
@@ -371,18 +369,12 @@ inline cudaError_t launch_gemm(const Operand& a, const Operand& b, const CUtenso
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
   CUtensorMap tmA, tmB, tmC;
   if (!make_operand_tmap<A_MN>(&tmA, a, kBM)) return cudaErrorInvalidValue;
-  static int dbg_split = -1;
-  if (dbg_split < 0) {
-    const char* e = getenv("ARCB_DEBUG_SPLIT_B");
-    dbg_split = (e && e[0] == '1') ? 1 : 0;
-  }
-  if (!make_operand_tmap<B_MN>(&tmB, b, (dbg_split && !B_MN) ? 64 : BN)) return cudaErrorInvalidValue;
+  if (!make_operand_tmap<B_MN>(&tmB, b, BN)) return cudaErrorInvalidValue;
   if (tmC_opt) tmC = *tmC_opt; else tmC = tmA;
   GemmSched sc;
   sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
   sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
   sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
-  sc.debug_split_b = dbg_split;
   if (split_k < 1) split_k = 1;
   if (split_k > sc.kb_total) split_k = sc.kb_total;
   sc.kb_per_split = (sc.kb_total + split_k - 1) / split_k;
@@ -393,14 +385,14 @@ inline cudaError_t launch_gemm(const Operand& a, const Operand& b, const CUtenso
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   if (grid > total) grid = total;
   auto kern = gemm_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN>;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];  // zero-initialised; forward and backward call in from different threads
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (!attr_set[dev]) {
+  if (!attr_set[dev].load(std::memory_order_acquire)) {  // idempotent: a race only repeats the call
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return e;
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   kern<<<grid, kGemmThreads, L::kTotal, stream>>>(tmA, tmB, tmC, sc, ep, NormArgs{});
   return cudaGetLastError();
@@ -423,7 +415,6 @@ inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t 
   sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
   sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
   sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
-  sc.debug_split_b = 0;
   sc.kb_per_split = sc.kb_total;
   sc.k_splits = 1;
   const int total = sc.tiles_m * sc.tiles_n;
@@ -431,14 +422,14 @@ inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t 
   int grid = device_sm_count();
   if (grid > total) grid = total;
   auto kern = gemm_sm100_kernel<Epi, BN, STAGES, false, false, true>;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];  // zero-initialised; forward and backward call in from different threads
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (!attr_set[dev]) {
+  if (!attr_set[dev].load(std::memory_order_acquire)) {  // idempotent: a race only repeats the call
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return e;
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);

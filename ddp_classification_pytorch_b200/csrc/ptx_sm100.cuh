@@ -11,11 +11,26 @@ namespace arcb {
 
 // ----------------------------------------------------------------------------------
 // Watchdog.  A mis-programmed pipeline would otherwise spin forever and take the GPU
-// box with it.  A wait that exceeds the budget records (tag, block, parity) here and
-// every later wait in the grid becomes a no-op, so the kernel drains (with garbage
-// results) instead of hanging; the host checks the word after the launch in tests.
+// box with it.  A wait that exceeds the budget (ARCB_WATCHDOG_CYCLES of clock64, ~20 s:
+// far beyond any legitimate wait, also under a sanitizer or on a time-sliced GPU)
+// records (tag, block, parity) and TRAPS: the grid is aborted, the stream's next
+// synchronisation / launch reports the error, and nothing downstream ever consumes
+// results of a pipeline that did not complete.  -DARCB_WATCHDOG_CYCLES=0 removes it.
 // ----------------------------------------------------------------------------------
+#ifndef ARCB_WATCHDOG_CYCLES
+#define ARCB_WATCHDOG_CYCLES 40000000000ll
+#endif
 __device__ unsigned int g_wait_timeout[4] = {0, 0, 0, 0};
+
+__device__ __noinline__ void watchdog_abort(uint32_t tag, uint32_t arg) {
+  if (atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) {
+    g_wait_timeout[1] = tag;
+    g_wait_timeout[2] = blockIdx.x;
+    g_wait_timeout[3] = arg;
+    __threadfence_system();
+  }
+  __trap();
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -57,21 +72,16 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t tag) {
   if (mbar_try_wait(bar, parity)) return;
+#if ARCB_WATCHDOG_CYCLES > 0
   long long t0 = clock64();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3ffu) == 0) {
-      if (*reinterpret_cast<volatile unsigned int*>(&g_wait_timeout[0]) != 0) return;
-      if (clock64() - t0 > 4000000000ll) {  // ~2 s at 1.9 GHz
-        if (atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) {
-          g_wait_timeout[1] = tag;
-          g_wait_timeout[2] = blockIdx.x;
-          g_wait_timeout[3] = parity;
-        }
-        return;
-      }
-    }
+    if ((++spins & 0x3ffu) == 0 && clock64() - t0 > ARCB_WATCHDOG_CYCLES) watchdog_abort(tag, parity);
   }
+#else
+  while (!mbar_try_wait(bar, parity)) {
+  }
+#endif
 }
 
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
@@ -81,23 +91,17 @@ __device__ __forceinline__ void wait_counter(const unsigned int* ctr, unsigned i
   unsigned int v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
   if (v >= target) return;
+#if ARCB_WATCHDOG_CYCLES > 0
   const long long t0 = clock64();
   uint32_t spins = 0;
+#endif
   while (true) {
     __nanosleep(100);
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
     if (v >= target) return;
-    if ((++spins & 0xffu) == 0) {
-      if (*reinterpret_cast<volatile unsigned int*>(&g_wait_timeout[0]) != 0) return;
-      if (clock64() - t0 > 4000000000ll) {
-        if (atomicCAS(&g_wait_timeout[0], 0u, 1u) == 0u) {
-          g_wait_timeout[1] = tag;
-          g_wait_timeout[2] = blockIdx.x;
-          g_wait_timeout[3] = target;
-        }
-        return;
-      }
-    }
+#if ARCB_WATCHDOG_CYCLES > 0
+    if ((++spins & 0xffu) == 0 && clock64() - t0 > ARCB_WATCHDOG_CYCLES) watchdog_abort(tag, target);
+#endif
   }
 }
 

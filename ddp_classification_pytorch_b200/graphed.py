@@ -5,7 +5,10 @@ head whose step is short (up to ~100k classes per GPU: <= 0.6 ms of GPU work spr
 and Python overhead are a visible share of it; replaying a captured graph removes them (measured on B200, B=1024,
 D=512, 125k classes: 0.558 -> 0.506 ms per step).  For long steps it does not pay (1M classes: 4.23 eager vs
 4.36 ms replayed), so this is an opt-in helper, not the default path.  Nothing is cached: every replay runs every
-kernel on whatever the static input buffers hold at that moment.  Single-process heads only (replicated mode): a
+kernel -- including ``F.normalize(self.weight)`` -- on whatever the weight and the static input buffers hold at that
+moment.  (A head with ``cache_normalized_weight`` / a fused optimizer keeps its cache for eager calls, but the
+captured step is recorded with the cache switched off: a replay cannot re-decide "is the cached copy still valid?",
+and a frozen "yes" would silently train on a stale normalised weight with any optimizer that does not refresh it.)  Single-process heads only (replicated mode): a
 class-sharded head would put its two NCCL collectives inside the graph, which is not supported here.
 
     step = GraphedHeadStep(ARC, batch=1024)        # ARC: ArcMarginProduct on a CUDA device
@@ -41,21 +44,25 @@ class GraphedHeadStep:
         self.x = torch.zeros(batch, head.in_features, device=dev, dtype=torch.float32, requires_grad=True)
         self.y = torch.zeros(batch, device=dev, dtype=torch.int64)
         # eager warm-up on a side stream (lazy one-time set-up inside the library, NCCL communicators, allocator pools)
-        side = torch.cuda.Stream(device=dev)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
-            for _ in range(max(1, warmup)):
-                head.weight.grad = None
-                self.x.grad = None
-                head.forward_loss(self.x, self.y, want_top3=self.want_top3).backward()
-        torch.cuda.current_stream(dev).wait_stream(side)
-        torch.cuda.synchronize(dev)
-        head.weight.grad = None
-        self.x.grad = None
-        self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
-            self.loss = head.forward_loss(self.x, self.y, want_top3=self.want_top3)
-            self.loss.backward()
+        saved_cache, head._wcache = head._wcache, None  # the captured forward always normalises the weight itself
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(max(1, warmup)):
+                    head.weight.grad = None
+                    self.x.grad = None
+                    head.forward_loss(self.x, self.y, want_top3=self.want_top3).backward()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            head.weight.grad = None
+            self.x.grad = None
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.loss = head.forward_loss(self.x, self.y, want_top3=self.want_top3)
+                self.loss.backward()
+        finally:
+            head._wcache = saved_cache
         self.aux = dict(head.aux)  # static tensors as well (lse, target_logit, top3 ...)
 
     def __call__(self, features=None, labels=None):

@@ -7,9 +7,12 @@ differentiable w.r.t. ``input`` and ``weight``).  Added, non-breaking surface:
 
 * ``forward_loss(input, label)`` -- head + ``nn.CrossEntropyLoss()`` (arc_main.py:245,:327) fused;
   the B x C logits are never written.  Statistics of the last call are kept in ``.aux``.
+* ``forward(input, label, fused_loss=True)`` -- the same fused loss reached through ``__call__``, i.e. through a
+  ``DistributedDataParallel`` wrapper (arc_main.py:243), so that DDP's reducer all-reduces ``weight.grad``.
 * keyword-only ``process_group`` -- class-sharded mode: this rank owns a contiguous slice of the
   classes and only per-row softmax statistics (forward) and the ``[B, D]`` partial of dX
-  (backward) cross NVLink through ``torch.distributed``.
+  (backward) cross NVLink through ``torch.distributed``.  ``forward_loss(..., gather_batch=True)`` adds the
+  feature / label ``all_gather`` in front and returns dX by ``reduce_scatter`` (data-parallel backbone).
 
 PyTorch is used here for device memory, streams and collectives only; all arithmetic runs in the
 hand-written CUDA kernels, reached through the C ABI with raw pointers.  There is no CPU path:
@@ -85,7 +88,7 @@ class _WeightCache:
         self.generation = 0
 
     def workspace(self, B, Cs, D, device):
-        need = _lib.lib().arcb_ws_bytes(B, Cs, D)
+        need = _lib.lib().arcb_ws_bytes(B, Cs, D, 0)
         if need <= 0:
             raise RuntimeError("arcb_ws_bytes rejected the sizes")
         if self.ws is None or self.key != (Cs, D, device) or need > self.ws_bytes:
@@ -132,7 +135,7 @@ class CudaEngine:
 
     @staticmethod
     def _alloc_ws(B, Cs, D, device):
-        nbytes = _lib.lib().arcb_ws_bytes(B, Cs, D)
+        nbytes = _lib.lib().arcb_ws_bytes(B, Cs, D, 0)
         if nbytes <= 0:
             raise RuntimeError("arcb_ws_bytes rejected the sizes")
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
@@ -163,7 +166,8 @@ class CudaEngine:
             cache = None
             ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
         _lib.check(fn(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"], cfg["m"],
-                      int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), _stream()), "arcb_shard_forward")
+                      int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), int(cfg.get("flags", 0)), _stream()),
+                   "arcb_shard_forward")
         if cache is not None:
             cache.valid = tag
             cache.generation += 1
@@ -218,7 +222,8 @@ class CudaEngine:
         dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
         _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),
                                          _ptr(grad_logits), Cs if grad_logits is not None else 0, _ptr(scratch),
-                                         scratch_bytes, _ptr(dw), _ptr(dxhat), _stream()), "arcb_shard_backward")
+                                         scratch_bytes, _ptr(dw), _ptr(dxhat), int(cfg.get("flags", 0)), _stream()),
+                   "arcb_shard_backward")
         return dw, dxhat
 
     def input_grad(self, xc, dxhat):
@@ -240,7 +245,28 @@ class _FusedLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, label, cfg):
         eng = cfg["engine"]
-        xc, wc, lab = eng.prepare(x, w, label)
+        group = cfg["group"]
+        P = _world(group)
+        gather = bool(cfg.get("gather_batch")) and P > 1
+        ctx.local_rows = None
+        if gather:
+            # data-parallel backbone in front of a class-sharded head (partial-FC style): every rank contributes its
+            # own rows; the shard needs the global batch.  Rows of rank r land at [r * b, (r + 1) * b).
+            if x.dim() != 2:
+                raise IndexError(f"input must be 2-D [B, in_features], got {tuple(x.shape)}")
+            b_local = x.shape[0]
+            xl = x.detach().to(torch.float32).contiguous()
+            ll = label.detach().reshape(-1).long().to(x.device).contiguous()
+            if ll.numel() != b_local:
+                raise IndexError(f"label has {ll.numel()} entries for a batch of {b_local}")
+            xg = torch.empty(P * b_local, xl.shape[1], dtype=xl.dtype, device=xl.device)
+            lg = torch.empty(P * b_local, dtype=ll.dtype, device=ll.device)
+            torch.distributed.all_gather_into_tensor(xg, xl, group=group)
+            torch.distributed.all_gather_into_tensor(lg, ll, group=group)
+            ctx.local_rows = (torch.distributed.get_rank(group) * b_local, b_local)
+            xc, wc, lab = eng.prepare(xg, w, lg)
+        else:
+            xc, wc, lab = eng.prepare(x, w, label)
         B = xc.shape[0]
         if cfg.get("wcache") is not None:
             cfg = dict(cfg, w_tag=(w.data_ptr(), w._version))
@@ -248,8 +274,6 @@ class _FusedLossFn(torch.autograd.Function):
         lease = None
         if len(state) > 5 and state[5] is not None and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]):
             lease = _Lease(state[5])  # the workspace now belongs to this graph until its backward has run
-        group = cfg["group"]
-        P = _world(group)
         if P > 1:  # the only forward exchange: one [B, 4] record per rank
             gathered = torch.empty(P * B, stats.shape[1], dtype=stats.dtype, device=stats.device)  # = [P, B, 4]
             torch.distributed.all_gather_into_tensor(gathered, stats, group=group)
@@ -260,7 +284,7 @@ class _FusedLossFn(torch.autograd.Function):
         ctx.held = (eng, state, lse, zt, cfg, w.dtype, x.dtype)
         ctx.lease = lease
         aux = cfg["aux_out"]
-        aux.update(lse=lse, target_logit=zt, stats=stats)
+        aux.update(lse=lse, target_logit=zt, stats=stats, labels=lab)
         if cfg["want_top3"]:  # predictions for the accuracy counters (arc_main.py:338-345, :377-388)
             val, idx = eng.shard_top3(xc, wc, state, cfg)
             if P > 1:  # keep the best three of the ranks' candidates (index order on equal logits)
@@ -281,9 +305,23 @@ class _FusedLossFn(torch.autograd.Function):
         eng, state, lse, zt, cfg, w_dtype, x_dtype = ctx.held
         g = grad_loss.detach().to(torch.float32).contiguous()
         dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt, grad_loss=g)
-        if _world(cfg["group"]) > 1:  # the only backward exchange: sum of the class shards' dX_hat partials
-            torch.distributed.all_reduce(dxhat, group=cfg["group"])
-        dx = eng.input_grad(xc, dxhat)
+        group = cfg["group"]
+        P = _world(group)
+        if ctx.local_rows is not None:
+            # each rank only needs the gradient of its own rows: reduce_scatter of the class shards' partials
+            #  instead of an all_reduce of all B rows, then F.normalize backward on those rows.
+            # The rows are scaled by the world size: the backbone's DDP reducer will AVERAGE its gradients over the
+            # ranks, and the mean of P per-rank terms that each carry 1/B_global must come out as the global-mean
+            # gradient the reference's per-rank mean + DDP average produces (arc_main.py:326-329).
+            r0, b_local = ctx.local_rows
+            mine = torch.empty(b_local, dxhat.shape[1], dtype=dxhat.dtype, device=dxhat.device)
+            torch.distributed.reduce_scatter_tensor(mine, dxhat, group=group)
+            dx = eng.input_grad(xc[r0:r0 + b_local], mine)
+            dx = dx * float(P)
+        else:
+            if P > 1:  # the only backward exchange: sum of the class shards' dX_hat partials
+                torch.distributed.all_reduce(dxhat, group=group)
+            dx = eng.input_grad(xc, dxhat)
         if ctx.lease is not None:
             ctx.lease.release()
         return dx.to(x_dtype), dw.to(w_dtype), None, None
@@ -332,10 +370,13 @@ class ArcMarginProduct(nn.Module):
         process_group (keyword-only): shard the classes over this ``torch.distributed`` group;
             ``weight`` then holds only this rank's rows and ``forward`` returns only its columns.
         cache_normalized_weight (keyword-only): see :meth:`cache_normalized_weight`.
+        kernel_flags (keyword-only): ``ARCB_*`` bits of include/arcface_b200.h passed with every call of THIS head
+            (kernel schedule selection for A/B runs and tests; 0 = library defaults).  Per head, not per process.
     """
 
     def __init__(self, in_features, out_features, s=30.0, m=0.50, easy_margin=False, *, process_group=None,
-                 chunk_classes: Optional[int] = None, cache_normalized_weight: bool = False, _engine=None):
+                 chunk_classes: Optional[int] = None, cache_normalized_weight: bool = False, kernel_flags: int = 0,
+                 _engine=None):
         super().__init__()
         self.in_features = in_features
         self.out_features = out_features
@@ -363,6 +404,7 @@ class ArcMarginProduct(nn.Module):
         self.th = math.cos(math.pi - m)
         self.mm = math.sin(math.pi - m) * m
         self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES  # 0: chosen per call by the library
+        self.kernel_flags = int(kernel_flags)
         self.aux = {}
         self._engine = _engine if _engine is not None else CudaEngine()
         self._wcache = _WeightCache() if cache_normalized_weight else None
@@ -389,27 +431,49 @@ class ArcMarginProduct(nn.Module):
             "s": float(self.s), "m": float(self.m), "easy_margin": bool(self.easy_margin),
             "class_offset": int(self.class_lo), "group": self.process_group,
             "chunk_classes": int(self.chunk_classes), "aux_out": self.aux, "engine": self._engine,
-            "want_top3": False, "wcache": self._wcache,
+            "want_top3": False, "wcache": self._wcache, "flags": int(self.kernel_flags), "gather_batch": False,
         }
 
-    def forward(self, input, label):
-        """Scaled logits ``[B, classes of this rank]`` exactly as arc_main.py:157-176 returns them."""
+    def forward(self, input, label, fused_loss=False, want_top3=False, gather_batch=False):
+        """Scaled logits ``[B, classes of this rank]`` exactly as arc_main.py:157-176 returns them.
+
+        ``fused_loss=True`` returns ``nn.CrossEntropyLoss()(logits, label)`` instead (see :meth:`forward_loss`) without
+        writing the logits.  This is the form to use when the head is wrapped the way the reference wraps it,
+        ``ARC = DistributedDataParallel(ARC)`` (arc_main.py:243): ``loss = ARC(features, labels, fused_loss=True)`` goes
+        through the wrapper's ``forward``, so DDP's reducer is armed and ``weight.grad`` is all-reduced in backward.
+        Calling ``ARC.module.forward_loss(...)`` would bypass the wrapper and leave every replica with its own
+        un-reduced gradient.
+        """
+        if fused_loss:
+            return self.forward_loss(input, label, want_top3=want_top3, gather_batch=gather_batch)
         return _LogitsFn.apply(input, self.weight, label, self._cfg())
 
-    def forward_loss(self, input, label, want_top3=False):
+    def forward_loss(self, input, label, want_top3=False, gather_batch=False):
         """``nn.CrossEntropyLoss()(self(input, label), label)`` fused (arc_main.py:326-327).
 
         ``want_top3=True`` additionally leaves what the trainer's accuracy counters take from the logits
         (``torch.max(out, 1)``, ``out.topk(3)``, arc_main.py:338-345) in ``.aux``: ``argmax`` [B],
         ``top3`` [B,3] (global class ids) and ``top3_logits`` -- exact fp32 re-scores, not bf16 values.
+
+        ``gather_batch=True`` (class-sharded head behind a data-parallel backbone, arc_main.py:320-330 with the head
+        sharded instead of replicated): ``input`` / ``label`` are this rank's rows only (same count on every rank); they
+        are all-gathered so that every class shard sees the global batch, the loss is the mean over the GLOBAL batch
+        (identical on all ranks; ``aux['labels']`` holds the gathered labels), and backward returns this rank's rows of
+        dX via ``reduce_scatter``, multiplied by the world size so that the backbone's DDP gradient AVERAGE equals the
+        global-mean gradient.  ``weight.grad`` is the plain gradient of that global-mean loss (what the reference's
+        DDP-averaged replicas hold); the head itself must NOT be wrapped in DDP in this mode.
+
+        Not reachable through a DDP wrapper: under ``DistributedDataParallel(ARC)`` call
+        ``ARC(input, label, fused_loss=True)`` instead (see :meth:`forward`).
         """
         cfg = self._cfg()
         cfg["want_top3"] = bool(want_top3)
+        cfg["gather_batch"] = bool(gather_batch)
         return _FusedLossFn.apply(input, self.weight, label, cfg)
 
     # ---- accuracy counters of the trainer / validation loop (arc_main.py:335-345, :377-395) -------------------
     @torch.no_grad()
-    def correct_counts(self, label, reduce_group=None):
+    def correct_counts(self, label=None, reduce_group=None):
         """``(top1_correct, top3_correct, samples)`` as a device int64 tensor ``[3]`` from the ``aux`` of the last
         ``forward_loss(..., want_top3=True)`` -- what ``torch.max(out, 1)`` / ``out.topk(3)`` + ``eq(labels)`` give
         in the reference, without the logits and without a host sync.  ``reduce_group``: sum the counters over
@@ -419,6 +483,8 @@ class ArcMarginProduct(nn.Module):
         if "top3" not in self.aux:
             raise RuntimeError("call forward_loss(input, label, want_top3=True) first")
         top3 = self.aux["top3"]
+        if label is None:  # the labels the last forward scored (the gathered ones with gather_batch=True)
+            label = self.aux["labels"]
         lab = label.detach().reshape(-1).to(device=top3.device, dtype=top3.dtype)
         hit = top3 == lab[:, None]
         counts = torch.stack([hit[:, 0].sum(), hit.any(dim=1).sum(),

@@ -14,7 +14,11 @@
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, no host sync;
  *   - return value 0 = success, negative = error; arcb_last_error() returns a thread-local message;
  *   - matrices are row-major fp32 with an explicit leading dimension where one is given;
- *   - labels are int64 GLOBAL class ids; a shard owns classes [class_offset, class_offset + Cs).
+ *   - labels are int64 GLOBAL class ids; a shard owns classes [class_offset, class_offset + Cs);
+ *   - there is no process-wide mode state: whatever selects a code path is the `flags` argument of the call
+ *     (ARCB_* bits below, 0 = the library's defaults), so two heads in one process may differ and every *_bytes
+ *     query is a pure function of its arguments.  The library may be called from several host threads (forward on
+ *     the main thread, backward on autograd's); its one-time per-device caches are thread-safe.
  */
 #ifndef ARCFACE_B200_H_
 #define ARCFACE_B200_H_
@@ -30,7 +34,23 @@ extern "C" {
 #define ARCB_ERR_INVALID (-1)   /* bad argument (null pointer, size, alignment) */
 #define ARCB_ERR_CUDA (-2)      /* a CUDA call / launch failed */
 #define ARCB_ERR_WORKSPACE (-3) /* workspace / scratch too small */
-#define ARCB_ERR_TIMEOUT (-4)   /* device-side pipeline watchdog fired (debug aid) */
+#define ARCB_ERR_TIMEOUT (-4)   /* a kernel was aborted by the device-side pipeline watchdog */
+
+/* ---- per-call flags (OR them; 0 = defaults) ---- */
+/* arcb_shard_forward / _prenorm: where F.normalize(self.weight) (arc_main.py:159) runs.  Default: inside the forward
+ * GEMM kernel for the shapes where that is faster on B200 (512 <= B <= 1024, >= 65536 classes; extra warps normalise the
+ * rows the coming tiles need, so the HBM-bound pass overlaps the tensor-bound one), else in its own kernel first.
+ * Same w_hat / inv_norm bits either way. */
+#define ARCB_FWD_NORM_SEPARATE 0x1 /* always its own kernel before the GEMM */
+#define ARCB_FWD_NORM_FUSED 0x2    /* inside the GEMM kernel whenever the shape allows (D % 4 == 0, D <= 2048) */
+#define ARCB_FWD_PAIR 0x4          /* forward GEMM on CTA pairs (cta_group::2); default: one CTA per 128 x 256 tile */
+/* arcb_shard_backward: schedule.  Default: ONE persistent cooperative kernel whose CTA pairs (cta_group::2, 256 x 256
+ * tile per pair of SMs) claim tiles from the global tile list as they go.  All schedules give the same gradients. */
+#define ARCB_BWD_PER_CHUNK 0x10    /* one launch per GEMM and class chunk (no co-residency needed) */
+#define ARCB_BWD_SINGLE_CTA 0x20   /* persistent kernel with one CTA per 128 x 256 tile (what ncu can replay) */
+#define ARCB_BWD_STATIC_SHARE 0x40 /* persistent kernel, fixed share of the tile list per CTA pair (A/B runs) */
+/* arcb_gemm_bf16 (unit tests of the GEMM core) */
+#define ARCB_GEMM_PAIR 0x4         /* CTA-pair core (same bit as ARCB_FWD_PAIR) */
 
 /* Library version (major * 10000 + minor * 100 + patch). */
 int arcb_version(void);
@@ -38,8 +58,11 @@ int arcb_version(void);
 /* Message for the last error raised on the calling thread ("" if none). */
 const char* arcb_last_error(void);
 
-/* Synchronises `stream` and reports whether the device-side pipeline watchdog fired since the
- * last call (ARCB_ERR_TIMEOUT) -- used by the tests, never needed on the hot path. */
+/* Synchronises `stream` and reports whether a kernel was aborted (ARCB_ERR_TIMEOUT).  The pipeline kernels carry a
+ * watchdog: a barrier / counter wait that outlives ~20 s of SM clock (no legitimate wait comes near it) records where
+ * it was and TRAPS, so the launch fails loudly -- this and every later CUDA call on the context report the error --
+ * instead of producing results from a pipeline that never completed.  Tests call it after every case; a training
+ * loop needs nothing: its next synchronisation raises. */
 int arcb_check_watchdog(void* stream);
 
 /* ---- row L2 normalisation: F.normalize(input) / F.normalize(self.weight), arc_main.py:159 ----
@@ -58,10 +81,10 @@ int arcb_l2norm_rows_bwd(const float* x, int64_t ldx, const float* dxhat, int64_
  * lda / ldb in elements (multiples of 8).  split_k > 1 accumulates with atomics into `out`
  * (which must then be zeroed by the caller). */
 int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, int64_t N, int64_t K, int64_t lda,
-                   int64_t ldb, float* out, int64_t ldo, int split_k, void* stream);
+                   int64_t ldb, float* out, int64_t ldo, int split_k, int flags, void* stream);
 
-/* Bytes of persistent workspace a shard needs between forward and backward. */
-int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D);
+/* Bytes of persistent workspace a shard needs between forward and backward, for calls made with `flags`. */
+int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D, int flags);
 
 /* Bytes of backward scratch that hold `chunk_classes` classes of bf16 dLoss/dcos for batch B.
  * arcb_shard_backward accepts any scratch >= arcb_scratch_bytes(B, 128); its default persistent
@@ -79,7 +102,7 @@ int64_t arcb_suggest_chunk_classes(int64_t B, int64_t Cs, int64_t D);
  * or -inf if another shard owns the label, 0).  The B x Cs logits are never written. */
 int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
                        int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
-                       int64_t ws_bytes, float* stats, void* stream);
+                       int64_t ws_bytes, float* stats, int flags, void* stream);
 
 /* ---- fused forward without a caller workspace (no counterpart in the reference) ----
  * For hosts that are not allowed to obtain device memory when the call happens: a plugin living inside another
@@ -89,11 +112,15 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
  * (no cudaMalloc / cudaFree, no allocating library routine): the workspace is a fixed ARCB_STATIC_WS_BYTES block
  * that is part of the library image on every GPU that loads it (held until the process exits).
  *   - Arguments and the stats output are exactly those of arcb_shard_forward, minus ws / ws_bytes.
- *   - Sizes whose workspace (arcb_ws_bytes(B, Cs, D)) exceeds ARCB_STATIC_WS_BYTES are rejected with
+ *   - Sizes whose workspace (arcb_ws_bytes(B, Cs, D, 0)) exceeds ARCB_STATIC_WS_BYTES are rejected with
  *     ARCB_ERR_WORKSPACE and a message naming both numbers; nothing is launched.  (32 MiB covers e.g.
  *     B=256, Cs=16384, D=512 or B=1024, Cs=8192, D=1024.)
  *   - The first call on each device looks up the block's device address (with that device current) and caches
- *     it; make that first call before any stream capture begins.
+ *     it; make that first call before any stream capture begins.  The block itself is materialised by the driver
+ *     when the library's device code is loaded on that GPU (with lazy loading: at the first call into the library
+ *     there), so a host that freezes its memory plan should make one library call per device during start-up, before
+ *     the freeze; the cached address does not survive cudaDeviceReset().
+ *   - Arguments are those of arcb_shard_forward with flags = 0 (library defaults).
  *   - All calls on a device share the one block: two calls whose kernels overlap on the GPU (different streams,
  *     or different host threads) race on it -- serialise them.  The block keeps the previous call's contents;
  *     the forward rewrites every region before reading it, so nothing needs clearing between calls.
@@ -110,7 +137,7 @@ int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64
  * workspace while `w` has not changed since (validation loop, arc_main.py:357-404: the weight is constant). */
 int arcb_shard_forward_prenorm(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
                                int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
-                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, void* stream);
+                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, int flags, void* stream);
 
 /* Where a workspace keeps the normalised weight: w_hat [Cs, arcb_padded_dim(D)] bf16 and inv_norm_w [Cs] fp32.
  * The two regions lead the workspace layout, so the addresses do not depend on the batch size. */
@@ -168,29 +195,7 @@ int arcb_merge_loss(const float* stats, int64_t P, int64_t B, float* lse, float*
  * arcb_l2norm_rows_bwd gives dx). */
 int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int64_t ws_bytes, const float* lse,
                         const float* target_logit, const float* grad_loss, const float* grad_logits, int64_t ldgl,
-                        void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, void* stream);
-
-/* Where CTA pairs (cta_group::2: 256 x 256 tile per pair of SMs, B operand shared by the pair) are used:
- * 0 = nowhere (one CTA per 128 x 256 tile), 1 (default) = persistent backward only, 2 = every GEMM.
- * Same results in all modes; the switch exists for A/B measurements and tests. */
-int arcb_set_pair_mode(int mode);
-
-/* Where F.normalize(self.weight) (arc_main.py:159) of arcb_shard_forward runs: 0 = its own kernel before the GEMM,
- * 2 = inside the forward GEMM kernel (extra warps normalise the rows the coming tiles need, so the HBM-bound pass
- * overlaps the tensor-bound one; needs a cooperative launch, D % 4 == 0, D <= 2048), 1 (default) = 2 for the shapes
- * where it is faster on B200 (512 <= B <= 1024, >= 65536 classes), else 0.  Same w_hat / inv_norm bits either way. */
-int arcb_set_forward_norm_mode(int mode);
-
-/* Stored-probabilities mode (experimental, off by default; ARCB_STORED_PROBS=1): arcb_shard_forward additionally
- * keeps P' = bf16(2^(s log2e cos - ref_i)) for the whole shard ([Cs, Bp] at the end of the workspace, which
- * arcb_ws_bytes then includes) so that the backward needs no recompute GEMM.  The workspace size depends on the
- * mode: set it before arcb_ws_bytes and keep it unchanged until the matching arcb_shard_backward has been called. */
-int arcb_set_stored_probs_mode(int on);
-
-/* Backward schedule: 1 (default) = one persistent cooperative kernel per shard whose CTA pairs claim tiles from the
- * global tile list as they go, 2 = the same kernel with a fixed share of the list per CTA pair, 0 = one launch
- * per GEMM and class chunk.  All produce the same gradients (A/B testing, profiling). */
-int arcb_set_backward_mode(int mode);
+                        void* scratch, int64_t scratch_bytes, float* dw, float* dxhat, int flags, void* stream);
 
 /* Leading dimension (elements) of the dxhat buffer for feature size D. */
 int64_t arcb_padded_dim(int64_t D);

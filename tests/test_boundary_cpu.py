@@ -31,13 +31,14 @@ def test_header_symbols_are_exported(built):
 
 def test_size_queries_without_gpu(built):
     L = built
-    assert L.arcb_version() >= 100
+    assert L.arcb_version() >= 20000
     assert L.arcb_padded_dim(512) == 512 and L.arcb_padded_dim(72) == 128
-    ws = L.arcb_ws_bytes(1024, 1_000_000, 512)
+    ws = L.arcb_ws_bytes(1024, 1_000_000, 512, 0)
+    assert ws == L.arcb_ws_bytes(1024, 1_000_000, 512, _lib.BWD_PER_CHUNK | _lib.FWD_NORM_FUSED)  # pure in its arguments
     # dominated by the bf16 copy of the normalised weight (2 B/elem) + per-tile softmax partials
     assert 1_000_000 * 512 * 2 < ws < 1_000_000 * 512 * 2 * 1.1
     assert L.arcb_scratch_bytes(1024, 128 * 148) == 128 * 148 * 1024 * 2
-    assert L.arcb_ws_bytes(0, 10, 10) < 0
+    assert L.arcb_ws_bytes(0, 10, 10, 0) < 0
     assert L.arcb_launch_count() == 0
 
 
@@ -59,17 +60,22 @@ def test_chunk_suggestion_and_weight_slots_without_gpu(built):
     assert a.value == base and (b.value - base) % 256 == 0
     assert b.value - base >= C * L.arcb_padded_dim(D) * 2
     for B in (1, 100, 5000):
-        assert L.arcb_ws_bytes(B, C, D) >= (b.value - base) + C * 4
+        assert L.arcb_ws_bytes(B, C, D, 0) >= (b.value - base) + C * 4
     assert L.arcb_ws_weight_slots(ctypes.c_void_p(base + 8), C, D, ctypes.byref(a), ctypes.byref(b)) == -1  # alignment
 
 
-def test_mode_switches_and_optimizer_argument_checks(built):
+def test_no_process_wide_mode_switches(built):
+    """no global mutable state -- code paths are chosen by the per-call flags argument only."""
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    for gone in ("arcb_set_pair_mode", "arcb_set_forward_norm_mode", "arcb_set_backward_mode", "arcb_set_stored_probs_mode"):
+        assert not hasattr(handle, gone)
+    head_a = ArcMarginProduct(16, 8, kernel_flags=_lib.BWD_PER_CHUNK)
+    head_b = ArcMarginProduct(16, 8)
+    assert head_a._cfg()["flags"] == _lib.BWD_PER_CHUNK and head_b._cfg()["flags"] == 0
+
+
+def test_optimizer_argument_checks(built):
     L = built
-    assert L.arcb_set_forward_norm_mode(3) == -1 and b"0, 1 or 2" in L.arcb_last_error()
-    assert L.arcb_set_backward_mode(5) == -1
-    assert L.arcb_set_pair_mode(7) != 0
-    for fn, mode in ((L.arcb_set_forward_norm_mode, 1), (L.arcb_set_backward_mode, 1), (L.arcb_set_pair_mode, 1)):
-        assert fn(mode) == 0
     fake = ctypes.c_void_p(0x7f0000000000)
     # rejected before anything is launched
     assert L.arcb_sgd_step(fake, 64, fake, 64, None, 64, 4, 64, 0.1, 0.9, 0.0, 0.0, 0, 1, None, 64, None, None) == -1
@@ -84,7 +90,7 @@ def test_errors_are_codes_not_exceptions(built):
     L = built
     rc = L.arcb_l2norm_rows(None, 4, 8, 8, None, 64, None, None)
     assert rc == -1 and b"null" in L.arcb_last_error()
-    rc = L.arcb_shard_backward(4, 4, 4, 30.0, None, 0, None, None, None, None, 0, None, 0, None, None, None)
+    rc = L.arcb_shard_backward(4, 4, 4, 30.0, None, 0, None, None, None, None, 0, None, 0, None, None, 0, None)
     assert rc == -1
 
 

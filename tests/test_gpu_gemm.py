@@ -8,7 +8,7 @@ from ddp_classification_pytorch_b200 import _lib
 pytestmark = pytest.mark.gpu
 
 
-def _run(M, N, K, a_mn, b_mn, split_k, seed=0):
+def _run(M, N, K, a_mn, b_mn, split_k, seed=0, pair=False):
     dev = torch.device("cuda:0")
     g = torch.Generator(device="cpu").manual_seed(seed)
     A = torch.randn(M, K, generator=g).to(dev).bfloat16()
@@ -26,24 +26,27 @@ def _run(M, N, K, a_mn, b_mn, split_k, seed=0):
     L = _lib.lib()
     st = torch.cuda.current_stream().cuda_stream
     _lib.check(L.arcb_gemm_bf16(a_store.data_ptr(), int(a_mn), b_store.data_ptr(), int(b_mn), M, N, K,
-                                a_store.shape[1], b_store.shape[1], out.data_ptr(), N, split_k, st))
+                                a_store.shape[1], b_store.shape[1], out.data_ptr(), N, split_k,
+                                _lib.GEMM_PAIR if pair else 0, st))
     _lib.check(L.arcb_check_watchdog(st))
     err = (out - ref).abs().max().item()
     scale = ref.abs().max().item() + 1e-6
     return err / scale
 
 
+@pytest.mark.parametrize("pair", [False, True])  # one CTA per tile (cta_group::1) / CTA pairs (cta_group::2)
 @pytest.mark.parametrize("a_mn", [False, True])
 @pytest.mark.parametrize("b_mn", [False, True])
 @pytest.mark.parametrize("shape", [(128, 256, 64), (128, 256, 512), (256, 512, 192), (100, 300, 72), (1024, 777, 512)])
-def test_gemm_majors(a_mn, b_mn, shape):
+def test_gemm_majors(a_mn, b_mn, shape, pair):
     M, N, K = shape
-    assert _run(M, N, K, a_mn, b_mn, 1) < 2e-3
+    assert _run(M, N, K, a_mn, b_mn, 1, pair=pair) < 2e-3
 
 
+@pytest.mark.parametrize("pair", [False, True])
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, True)])
-def test_gemm_split_k(a_mn, b_mn):
-    assert _run(256, 512, 64 * 37, a_mn, b_mn, 5) < 2e-3
+def test_gemm_split_k(a_mn, b_mn, pair):
+    assert _run(256, 512, 64 * 37, a_mn, b_mn, 5, pair=pair) < 2e-3
 
 
 def test_gemm_many_tiles_persistent():

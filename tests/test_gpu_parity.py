@@ -140,18 +140,15 @@ def test_persistent_and_per_chunk_backward_agree(chunk):
     w = (torch.rand(C, D, generator=gen) * 2 - 1) * 0.05
     x = torch.randn(B, D, generator=gen)
     y = torch.randint(0, C, (B,), generator=gen)
-    L = _lib.lib()
     grads = []
-    try:
-        for mode in (1, 0, 2):  # claimed tiles, one launch per GEMM and chunk, fixed share of the tile list
-            L.arcb_set_backward_mode(mode)
-            head = _module(w.numpy(), 30.0, 0.5, False, chunk_classes=chunk)
-            xg = x.cuda().requires_grad_(True)
-            head.forward_loss(xg, y.cuda()).backward()
-            _sync_ok()
-            grads.append((xg.grad.clone(), head.weight.grad.clone()))
-    finally:
-        L.arcb_set_backward_mode(1)
+    # claimed tiles (default), one launch per GEMM and chunk, fixed share of the tile list, one CTA per tile:
+    # per-head flags, so the four heads coexist in one process
+    for flags in (0, _lib.BWD_PER_CHUNK, _lib.BWD_STATIC_SHARE, _lib.BWD_SINGLE_CTA):
+        head = _module(w.numpy(), 30.0, 0.5, False, chunk_classes=chunk, kernel_flags=flags)
+        xg = x.cuda().requires_grad_(True)
+        head.forward_loss(xg, y.cuda()).backward()
+        _sync_ok()
+        grads.append((xg.grad.clone(), head.weight.grad.clone()))
     for other in grads[1:]:
         torch.testing.assert_close(grads[0][0], other[0], rtol=1e-3, atol=1e-6)
         torch.testing.assert_close(grads[0][1], other[1], rtol=1e-3, atol=1e-6)
@@ -174,27 +171,23 @@ def test_weight_normalised_inside_the_gemm_matches_separate_kernel(shape):
     y = torch.randint(0, C, (B,), generator=gen).cuda()
     L = _lib.lib()
     eng = CudaEngine()
-    cfg = {"s": 30.0, "m": 0.5, "easy_margin": False, "class_offset": 0, "chunk_classes": 512}
     Dp = L.arcb_padded_dim(D)
     out = []
-    try:
-        for mode in (2, 0):
-            L.arcb_set_forward_norm_mode(mode)
-            n0 = L.arcb_launch_count()
-            stats, state = eng.shard_forward(x, w, y, cfg)
-            launches = L.arcb_launch_count() - n0
-            lse, zt, loss = eng.merge_loss(stats, 1, B)
-            dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt)
-            _sync_ok()
-            ws = state[3]
-            a, b = ctypes.c_void_p(), ctypes.c_void_p()
-            _lib.check(L.arcb_ws_weight_slots(ws.data_ptr(), C, D, ctypes.byref(a), ctypes.byref(b)))
-            off_a, off_b = a.value - ws.data_ptr(), b.value - ws.data_ptr()
-            what = ws[off_a: off_a + C * Dp * 2].view(torch.bfloat16).view(C, Dp).clone()
-            inv = ws[off_b: off_b + C * 4].view(torch.float32).clone()
-            out.append((stats.clone(), what, inv, loss.clone(), dw, dxhat, launches))
-    finally:
-        L.arcb_set_forward_norm_mode(1)
+    for flags in (_lib.FWD_NORM_FUSED, _lib.FWD_NORM_SEPARATE):
+        cfg = {"s": 30.0, "m": 0.5, "easy_margin": False, "class_offset": 0, "chunk_classes": 512, "flags": flags}
+        n0 = L.arcb_launch_count()
+        stats, state = eng.shard_forward(x, w, y, cfg)
+        launches = L.arcb_launch_count() - n0
+        lse, zt, loss = eng.merge_loss(stats, 1, B)
+        dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt)
+        _sync_ok()
+        ws = state[3]
+        a, b = ctypes.c_void_p(), ctypes.c_void_p()
+        _lib.check(L.arcb_ws_weight_slots(ws.data_ptr(), C, D, ctypes.byref(a), ctypes.byref(b)))
+        off_a, off_b = a.value - ws.data_ptr(), b.value - ws.data_ptr()
+        what = ws[off_a: off_a + C * Dp * 2].view(torch.bfloat16).view(C, Dp).clone()
+        inv = ws[off_b: off_b + C * 4].view(torch.float32).clone()
+        out.append((stats.clone(), what, inv, loss.clone(), dw, dxhat, launches))
     f, u = out
     assert f[6] == u[6] - 1                      # the normalisation launch is gone
     assert torch.equal(f[1].view(torch.int16), u[1].view(torch.int16))

@@ -32,13 +32,13 @@ def _forward_both(L, x, w, y, s, m, easy):
     B, D = x.shape
     C = w.shape[0]
     st = torch.cuda.current_stream().cuda_stream
-    ws_bytes = L.arcb_ws_bytes(B, C, D)
+    ws_bytes = L.arcb_ws_bytes(B, C, D, 0)
     assert 0 < ws_bytes <= STATIC_WS_BYTES
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
     ref = torch.full((B, 4), float("nan"), device="cuda")
     new = torch.full((B, 4), float("nan"), device="cuda")
     _lib.check(L.arcb_shard_forward(x.data_ptr(), D, w.data_ptr(), D, y.data_ptr(), B, C, D, 0, s, m, int(easy),
-                                    ws.data_ptr(), ws_bytes, ref.data_ptr(), st), "arcb_shard_forward")
+                                    ws.data_ptr(), ws_bytes, ref.data_ptr(), 0, st), "arcb_shard_forward")
     _lib.check(L.arcb_shard_forward_static(x.data_ptr(), D, w.data_ptr(), D, y.data_ptr(), B, C, D, 0, s, m, int(easy),
                                            new.data_ptr(), st), "arcb_shard_forward_static")
     _lib.check(L.arcb_check_watchdog(st))
@@ -71,7 +71,7 @@ def test_static_forward_rejects_sizes_beyond_its_block():
     x, w, y = _inputs(8, 64, 16, 2)
     stats = torch.zeros(8, 4, device="cuda")
     B, C, D = 1024, 1_000_000, 512  # needs ~1.07 GB of workspace: far beyond 32 MiB
-    assert L.arcb_ws_bytes(B, C, D) > STATIC_WS_BYTES
+    assert L.arcb_ws_bytes(B, C, D, 0) > STATIC_WS_BYTES
     n0 = L.arcb_launch_count()
     rc = L.arcb_shard_forward_static(x.data_ptr(), D, w.data_ptr(), D, y.data_ptr(), B, C, D, 0, 30.0, 0.5, 0,
                                      stats.data_ptr(), torch.cuda.current_stream().cuda_stream)

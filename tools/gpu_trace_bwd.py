@@ -23,7 +23,7 @@ dw = torch.empty(C, D, device="cuda"); dxhat = torch.empty(B, Dp, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
 for _ in range(3):
     _lib.check(L.arcb_shard_backward(B, C, D, 30.0, ws.data_ptr(), ws_bytes, lse.data_ptr(), zt.data_ptr(), one.data_ptr(), None, 0,
-                                     scratch.data_ptr(), nbytes, dw.data_ptr(), dxhat.data_ptr(), st))
+                                     scratch.data_ptr(), nbytes, dw.data_ptr(), dxhat.data_ptr(), 0, st))
 torch.cuda.synchronize()
 tr = scratch[-(1 << 20):].view(torch.int64).cpu().numpy()[: 8 * 1024 * 12].reshape(8, 1024, 12)
 names = {0: "G", 1: "X", 2: "W"}

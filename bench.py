@@ -4,14 +4,21 @@
     ArcFace head fwd+bwd samples/s, 512-d embeddings x 1M classes, batch 1024
 
 ``python bench.py --gpus N --steps K --warmup W`` (N > 1: launched by torchrun, one rank per GPU;
-the 1M classes are sharded by class over the N ranks -- total work fixed => "strong" scaling).
+the classes are sharded by class over the N ranks -- total work fixed => "strong" scaling).
 A step = normalise + cosine logits + margin + cross-entropy + dX + dW for one batch.
+``--config cfg2|cfg3|cfg4`` selects the other shapes BASELINE.json names (default cfg4 = configs[3], the one
+the metric is quoted on).
 
 Printed JSON (rank 0, one line):
   value         samples/s with inputs resident in HBM, CUDA-event timed, max over ranks
   e2e           the same through the public nn.Module API with the step's inputs copied from
                 pinned host memory and the loss read back, inside the timed region
-  roofline      dominant kernel vs the measured bf16 tensor peak (MEASURED_PEAKS.json)
+  roofline      dominant kernel vs the measured peaks (MEASURED_PEAKS.json): burst AND sustained bf16 fractions,
+                `frac` taken against the peak of the regime the timed region ran in, HBM fraction beside it
+  sustained     a second, long pass (>= 2 s of load) of the same step: the power-capped steady state
+  parity        N > 1: the class-sharded result against ONE un-sharded run of the same inputs on rank 0
+                N = 1: the fused result against plain fp32 torch on a sample of rows (all classes)
+                (outside every timed region; the run exits non-zero when a bound is broken)
   cpu_baseline  the oracle's torch-CPU port of the reference head on a bounded sample
 ``--impl reference`` times only that CPU port (the reference itself is eager PyTorch whose CUDA
 path is pinned to a GPU by arc_main.py:168; its CPU arithmetic is what runs on the host cores).
@@ -32,10 +39,18 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-# BASELINE.json configs[3]: the configuration the metric is quoted on (fits one B200: W = 2 GB)
-WORKLOAD = {"B": 1024, "D": 512, "C": 1_000_000, "s": 30.0, "m": 0.5, "easy_margin": False}
-METRIC = "ArcFace head fwd+bwd samples/s (512-d, 1M classes, batch 1024)"
+# the shapes BASELINE.json names (configs[0] is the CPU-only case: a parity-test case, not a bench line)
+CONFIGS = {
+    "cfg2": {"B": 256, "D": 2048, "C": 1000, "name": "BASELINE.json configs[1]",
+             "metric": "ArcFace head fwd+bwd samples/s (2048-d, 1000 classes, batch 256)"},
+    "cfg3": {"B": 512, "D": 512, "C": 100_000, "name": "BASELINE.json configs[2]",
+             "metric": "ArcFace head fwd+bwd samples/s (512-d, 100k classes, batch 512)"},
+    "cfg4": {"B": 1024, "D": 512, "C": 1_000_000, "name": "BASELINE.json configs[3]",
+             "metric": "ArcFace head fwd+bwd samples/s (512-d, 1M classes, batch 1024)"},
+}
+S_SCALE, MARGIN = 30.0, 0.5
 UNIT = "samples/s"
+W_BLOCK = 4096  # rows of W that share one generator seed: the matrix is the same for every shard count
 
 
 def parse_args():
@@ -44,13 +59,26 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=WORKLOAD["B"])
-    ap.add_argument("--classes", type=int, default=WORKLOAD["C"])
-    ap.add_argument("--dim", type=int, default=WORKLOAD["D"])
+    ap.add_argument("--config", default="cfg4", choices=sorted(CONFIGS))
+    ap.add_argument("--batch", type=int, default=0, help="override the config's batch")
+    ap.add_argument("--classes", type=int, default=0, help="override the config's class count")
+    ap.add_argument("--dim", type=int, default=0, help="override the config's feature size")
     ap.add_argument("--easy-margin", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample-rows", type=int, default=0, help="rows of the batch the CPU port runs (0 = auto)")
-    return ap.parse_args()
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--sustained-seconds", type=float, default=2.5,
+                    help="length of the second, power-capped pass (0 = skip it)")
+    ap.add_argument("--cpu-sample-rows", type=int, default=0,
+                    help="rows of the batch the CPU port runs (0 = 256 beside the GPU number, the full batch for --impl reference)")
+    ap.add_argument("--kernel-flags", type=lambda v: int(v, 0), default=0, help="ARCB_* flags for A/B runs")
+    a = ap.parse_args()
+    cfg = CONFIGS[a.config]
+    a.named = not (a.batch or a.classes or a.dim)
+    a.batch = a.batch or cfg["B"]
+    a.classes = a.classes or cfg["C"]
+    a.dim = a.dim or cfg["D"]
+    a.metric = cfg["metric"] if a.named else f"ArcFace head fwd+bwd samples/s ({a.dim}-d, {a.classes} classes, batch {a.batch})"
+    return a
 
 
 def measured_peaks():
@@ -59,9 +87,9 @@ def measured_peaks():
         with open(path) as fh:
             d = json.load(fh)
         return {"burst": float(d["bf16_tflops"]), "sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
-                "hbm": float(d["hbm_gbs"]), "src": "measured"}
+                "hbm": float(d["hbm_gbs"]), "src": "measured (MEASURED_PEAKS.json)"}
     except Exception:
-        return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "src": "fallback"}
+        return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "src": "fallback (B200_PROFILING.md)"}
 
 
 class ClockSampler:
@@ -111,19 +139,29 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def make_inputs(B, D, C_lo, C_hi, C, device, seed=0):
-    """Synthetic inputs of the named shapes: X ~ N(0,1), W ~ xavier_uniform, labels uniform.
+def make_weight_rows(lo, hi, D, C, device):
+    """Rows [lo, hi) of the synthetic weight (xavier_uniform bound of the full [C, D] matrix, arc_main.py:146).
 
-    Every rank draws the same X / labels; W rows are generated per shard (seeded by the shard) so
-    that no rank ever holds the full matrix.
-    """
+    The matrix is defined block by block -- rows [k * W_BLOCK, (k + 1) * W_BLOCK) come from a generator seeded with
+    1000 + k -- so every shard count sees the SAME matrix and no rank ever has to hold more than its own rows."""
+    bound = (6.0 / (C + D)) ** 0.5
+    out = torch.empty(hi - lo, D, dtype=torch.float32, device=device)
+    gw = torch.Generator(device=device)
+    for k in range(lo // W_BLOCK, (hi + W_BLOCK - 1) // W_BLOCK):
+        r0, r1 = k * W_BLOCK, min((k + 1) * W_BLOCK, C)
+        gw.manual_seed(1000 + k)
+        blk = (torch.rand(r1 - r0, D, generator=gw, device=device) * 2 - 1) * bound
+        a, b = max(lo, r0), min(hi, r1)
+        out[a - lo:b - lo] = blk[a - r0:b - r0]
+    return out
+
+
+def make_batch(B, D, C, seed=0):
+    """X ~ N(0,1), labels uniform; identical on every rank and for every shard count."""
     g = torch.Generator(device="cpu").manual_seed(seed)
     x = torch.randn(B, D, generator=g)
     y = torch.randint(0, C, (B,), generator=g)
-    bound = (6.0 / (C + D)) ** 0.5
-    gw = torch.Generator(device=device).manual_seed(1000 + C_lo)
-    w = (torch.rand(C_hi - C_lo, D, generator=gw, device=device) * 2 - 1) * bound
-    return x, y, w
+    return x, y
 
 
 def cpu_port_rate(B_rows, D, C, easy, steps, warmup, threads):
@@ -135,7 +173,7 @@ def cpu_port_rate(B_rows, D, C, easy, steps, warmup, threads):
     w = (torch.rand(C, D, generator=g) * 2 - 1) * bound
     x = torch.randn(B_rows, D, generator=g)
     y = torch.randint(0, C, (B_rows,), generator=g)
-    port = TorchPort(w, WORKLOAD["s"], WORKLOAD["m"], easy)
+    port = TorchPort(w, S_SCALE, MARGIN, easy)
     for _ in range(warmup):
         port.step(x, y)
     t0 = time.perf_counter()
@@ -145,34 +183,20 @@ def cpu_port_rate(B_rows, D, C, easy, steps, warmup, threads):
     return B_rows / dt, dt
 
 
-def size_cpu_sample(args, threads, seconds_per_step):
-    """Rows of the batch the CPU port can process in ~seconds_per_step.
-
-    One CPU step costs a + b * rows (a: normalising / differentiating the full [C, D] weight, b: the B x C
-    passes), so two probing steps give the model and the sample is sized from it (never above the batch)."""
-    r1, r2 = 16, 48
-    _, t1 = cpu_port_rate(r1, args.dim, args.classes, args.easy_margin, 1, 0, threads)
-    _, t2 = cpu_port_rate(r2, args.dim, args.classes, args.easy_margin, 1, 0, threads)
-    b = max((t2 - t1) / (r2 - r1), 1e-6)
-    a = max(t1 - b * r1, 0.0)
-    rows = int((seconds_per_step - a) / b) if seconds_per_step > a else r1
-    return max(r1, min(args.batch, rows)), a, b
-
-
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # the CPU arm runs once, on rank 0
     threads = os.cpu_count() or 1
-    if args.cpu_sample_rows:
-        rows = args.cpu_sample_rows
-    else:  # K + W steps (plus the two probes) should end within ~2 minutes
-        rows, _, _ = size_cpu_sample(args, threads, 100.0 / max(1, args.steps + args.warmup))
+    # always the same sample: the FULL batch of the config (cfg4: ~10 s per step on 16 cores), unless the caller fixes
+    # another row count -- never a size probed at run time (the per-sample cost of a small sample is dominated by the
+    # weight-side passes and is not comparable)
+    rows = args.cpu_sample_rows or args.batch
     rate, dt = cpu_port_rate(rows, args.dim, args.classes, args.easy_margin, args.steps, args.warmup, threads)
     sample = (f"{rows} of {args.batch} batch rows per step, full C={args.classes}, D={args.dim}; torch-CPU fp32 port of "
-              f"the reference head (oracle.TorchPort), {dt:.2f} s/step")
+              f"the reference head (oracle.TorchPort), {dt:.2f} s/step, {args.steps} timed steps after {args.warmup} warm-up")
     line = {
-        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": args.metric, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, 1),
@@ -183,14 +207,44 @@ def run_reference(args):
 
 
 def workload_config(args, world):
+    label = CONFIGS[args.config]["name"] if args.named else "custom shape"
+    big = args.classes // world * args.dim * 4 > 126e6
     return {
         "workload": f"ArcFace head (ArcMarginProduct + CrossEntropyLoss) fwd+bwd, B={args.batch}, D={args.dim}, "
-                    f"C={args.classes}, s=30, m=0.5, easy_margin={bool(args.easy_margin)} (BASELINE.json configs[3])",
+                    f"C={args.classes}, s=30, m=0.5, easy_margin={bool(args.easy_margin)} ({label})",
         "batch": args.batch, "dim": args.dim, "classes": args.classes,
         "parallelism": f"class-sharded x{world}" if world > 1 else "single GPU",
-        "cache": "inputs larger than L2: fp32 W shard read every step "
-                 f"({args.classes // world * args.dim * 4 / 1e6:.0f} MB/GPU vs 126 MB L2)",
+        "cache": ("inputs larger than L2: fp32 W shard read every step "
+                  f"({args.classes // world * args.dim * 4 / 1e6:.0f} MB/GPU vs 126 MB L2)") if big else
+                 "L2 flushed between timed steps (a 256 MB buffer is overwritten; the fills are timed on their own and subtracted)",
     }
+
+
+def cosine(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a @ b) / (a.norm() * b.norm() + 1e-300))
+
+
+def sample_reference_fp32(x, y, w, rows, s, m, easy):
+    """Plain fp32 torch (the reference's op sequence, arc_main.py:159-172 + CrossEntropyLoss) for `rows` of the
+    batch against ALL classes; returns per-row lse, target logit, and d(sum of those rows' losses)/dx."""
+    import math
+    F = torch.nn.functional
+    xs = x[rows].detach().clone().requires_grad_(True)
+    cos = F.linear(F.normalize(xs), F.normalize(w))
+    sine = torch.sqrt((1.0 - torch.pow(cos, 2)).clamp(0, 1))
+    phi = cos * math.cos(m) - sine * math.sin(m)
+    if easy:
+        phi = torch.where(cos > 0, phi, cos)
+    else:
+        phi = torch.where(cos > math.cos(math.pi - m), phi, cos - math.sin(math.pi - m) * m)
+    hot = torch.zeros_like(cos)
+    hot.scatter_(1, y[rows].view(-1, 1), 1)
+    out = (hot * phi + (1.0 - hot) * cos) * s
+    lse = torch.logsumexp(out, dim=1)
+    zt = out.gather(1, y[rows].view(-1, 1)).squeeze(1)
+    (lse - zt).sum().backward()
+    return lse.detach(), zt.detach(), xs.grad.detach()
 
 
 def run_b200(args):
@@ -209,19 +263,28 @@ def run_b200(args):
     L = _lib.lib()  # raises if the CUDA extension is missing: no fallback
 
     B, D, C = args.batch, args.dim, args.classes
-    head = ArcMarginProduct(D, C, s=WORKLOAD["s"], m=WORKLOAD["m"], easy_margin=args.easy_margin, process_group=group)
-    x_cpu, y_cpu, w = make_inputs(B, D, head.class_lo, head.class_hi, C, dev)
+    head = ArcMarginProduct(D, C, s=S_SCALE, m=MARGIN, easy_margin=args.easy_margin, process_group=group,
+                            kernel_flags=args.kernel_flags)
+    x_cpu, y_cpu = make_batch(B, D, C)
     head = head.to(dev)
     with torch.no_grad():
-        head.weight.copy_(w)
-    del w
+        head.weight.copy_(make_weight_rows(head.class_lo, head.class_hi, D, C, dev))
     x_pin, y_pin = x_cpu.pin_memory(), y_cpu.pin_memory()
     x_dev = x_pin.to(dev).requires_grad_(True)
     y_dev = y_pin.to(dev)
 
+    # Timing rule: inputs larger than L2, or L2 flushed between timed iterations.  The fp32 weight shard is re-read
+    # from HBM every step; where it is smaller than L2 (cfg2, cfg3 on many GPUs) a 256 MB buffer is overwritten
+    # between steps and the time of those fills (measured on their own) is subtracted.
+    shard_bytes = (head.class_hi - head.class_lo) * D * 4
+    flush = shard_bytes <= 126e6
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if flush else None
+
     def step_resident():
         head.weight.grad = None
         x_dev.grad = None
+        if flush:
+            flush_buf.fill_(1)
         loss = head.forward_loss(x_dev, y_dev)
         loss.backward()
         return loss
@@ -255,6 +318,8 @@ def run_b200(args):
         enqueue_copy(nxt)                     # next step's inputs: overlaps this step's kernels
         main.wait_event(cur["ready"])
         head.weight.grad = None
+        if flush:
+            flush_buf.fill_(1)
         xd = cur["x"].detach().requires_grad_(True)
         loss = head.forward_loss(xd, cur["y"])
         loss.backward()
@@ -284,7 +349,20 @@ def run_b200(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms[0].item(), ms[1].item()
 
-    for _ in range(max(3, args.warmup)):
+    def flush_cost_ms(steps):
+        if not flush:
+            return 0.0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            flush_buf.fill_(1)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    warm = max(3, args.warmup)  # never fewer than three untimed steps
+    for _ in range(warm):
         step_resident()
     _lib.check(L.arcb_check_watchdog(torch.cuda.current_stream().cuda_stream))
 
@@ -295,12 +373,13 @@ def run_b200(args):
     dev_ms, _ = timed(step_resident, args.steps)
     launches = L.arcb_launch_count() - n0
     clocks = sampler.stop() if rank == 0 else None
+    fl_ms = flush_cost_ms(args.steps)
+    dev_ms_net = max(dev_ms - fl_ms, 1e-6)
     final_loss = step_resident().item()
 
-    # per-kernel timing pass (CUDA events around every launch, on the launching stream): the same K steps again,
-    # straight after the timed region so that clocks / power state are the ones the headline number saw
-    # (a pause before each further pass: the three passes should start from the same power / clock state instead of
-    #  the later ones inheriting the power-capped clocks of the earlier ones)
+    # per-kernel timing pass (CUDA events around every launch, on the launching stream): the same K steps again.
+    # (a pause before each further pass: every pass should start from the same power / clock state instead of the
+    #  later ones inheriting the power-capped clocks of the earlier ones)
     time.sleep(1.0)
     _lib.check(L.arcb_profile_enable(1))
     prof_steps = min(args.steps, 500)  # the record pool holds 8192 launches
@@ -315,10 +394,81 @@ def run_b200(args):
     for _ in range(2):
         step_e2e()
     _, e2e_wall_ms = timed(step_e2e, args.steps)
+    e2e_wall_net = max(e2e_wall_ms - fl_ms, 1e-6)
 
-    ms_per_step = dev_ms / args.steps
-    value = B * args.steps / (dev_ms * 1e-3)
-    e2e_value = B * args.steps / (e2e_wall_ms * 1e-3)
+    # second figure: the same resident step for >= sustained-seconds of continuous load (power-capped steady state)
+    sustained = None
+    if args.sustained_seconds > 0:
+        time.sleep(1.0)
+        long_steps = max(args.steps, int(args.sustained_seconds * 1e3 / max(dev_ms / args.steps, 1e-3)) + 1)
+        long_steps = min(long_steps, 20000)
+        samp2 = ClockSampler(local)
+        if rank == 0:
+            samp2.start()
+        long_ms, _ = timed(step_resident, long_steps)
+        clocks2 = samp2.stop() if rank == 0 else None
+        long_net = max(long_ms - flush_cost_ms(long_steps), 1e-6)
+        sustained = {"steps": long_steps, "seconds": long_ms * 1e-3, "ms_per_step": long_net / long_steps,
+                     "value": B * long_steps / (long_net * 1e-3), "unit": UNIT, "clocks": clocks2}
+
+    ms_per_step = dev_ms_net / args.steps
+    value = B * args.steps / (dev_ms_net * 1e-3)
+    e2e_value = B * args.steps / (e2e_wall_net * 1e-3)
+
+    # ---- parity, outside every timed region --------------------------------------------------------------------
+    parity, parity_ok = None, True
+    if not args.no_parity:
+        head.weight.grad = None
+        x_dev.grad = None
+        loss_s = head.forward_loss(x_dev, y_dev, want_top3=True)
+        loss_s.backward()
+        torch.cuda.synchronize()
+        if world > 1:
+            # the class-sharded result against ONE un-sharded run of the same inputs on rank 0 (full W: fits one GPU)
+            ok_t = torch.ones(1, device=dev)
+            if rank == 0:
+                full = ArcMarginProduct(D, C, s=S_SCALE, m=MARGIN, easy_margin=args.easy_margin).to(dev)
+                with torch.no_grad():
+                    full.weight.copy_(make_weight_rows(0, C, D, C, dev))
+                xu = x_dev.detach().clone().requires_grad_(True)
+                loss_u = full.forward_loss(xu, y_dev, want_top3=True)
+                loss_u.backward()
+                torch.cuda.synchronize()
+                lo, hi = head.class_lo, head.class_hi
+                parity = {
+                    "against": "un-sharded forward_loss + backward of the same inputs on rank 0",
+                    "loss_rel": abs(loss_s.item() - loss_u.item()) / abs(loss_u.item()),
+                    "cos_dx": cosine(x_dev.grad, xu.grad),
+                    "cos_dw_shard0": cosine(head.weight.grad, full.weight.grad[lo:hi]),
+                    "dw_shard0_norm_ratio": float(head.weight.grad.norm() / full.weight.grad[lo:hi].norm()),
+                    "top3_equal_frac": float((head.aux["top3"] == full.aux["top3"]).all(dim=1).float().mean()),
+                    "lse_max_abs_diff": float((head.aux["lse"] - full.aux["lse"]).abs().max()),
+                }
+                parity_ok = (parity["loss_rel"] <= 1e-3 and parity["cos_dx"] >= 0.999 and parity["cos_dw_shard0"] >= 0.999
+                             and parity["top3_equal_frac"] >= 0.99)
+                ok_t.fill_(1.0 if parity_ok else 0.0)
+                del full, xu, loss_u
+            dist.broadcast(ok_t, src=0)
+            parity_ok = bool(ok_t.item() > 0.5)
+        else:
+            # one GPU: plain fp32 torch on a sample of rows against ALL classes (lse, target logit, dX of those rows)
+            n_rows = min(B, 64)
+            rows = torch.arange(0, B, max(1, B // n_rows), device=dev)[:n_rows]
+            lse_r, zt_r, dx_r = sample_reference_fp32(x_dev.detach(), y_dev, head.weight.detach(), rows, S_SCALE, MARGIN,
+                                                      args.easy_margin)
+            lse_g, zt_g = head.aux["lse"][rows], head.aux["target_logit"][rows]
+            loss_rows_ref = float((lse_r - zt_r).double().mean())
+            loss_rows_got = float((lse_g - zt_g).double().mean())
+            parity = {
+                "against": f"plain fp32 torch (reference op sequence) on {n_rows} of {B} rows x all {C} classes",
+                "loss_rel": abs(loss_rows_got - loss_rows_ref) / abs(loss_rows_ref),
+                "lse_max_abs_diff": float((lse_g - lse_r).abs().max()),
+                "target_logit_max_abs_diff": float((zt_g - zt_r).abs().max()),
+                "cos_dx_rows": cosine(x_dev.grad[rows] * B, dx_r),  # the module's loss is the MEAN over B rows
+                "dx_norm_ratio": float((x_dev.grad[rows] * B).norm() / dx_r.norm()),
+            }
+            parity_ok = (parity["loss_rel"] <= 1e-3 and parity["cos_dx_rows"] >= 0.999
+                         and parity["target_logit_max_abs_diff"] <= 1e-3)
 
     if rank == 0:
         peaks = measured_peaks()
@@ -328,42 +478,78 @@ def run_b200(args):
         # algorithmic GEMMs per launch kind: the persistent backward does all three backward GEMMs
         # (recompute + dX + dW; only dX and dW count as algorithmic flops)
         gemms_in = {"fwd_gemm": 1, "bwd_g_gemm": 0, "dx_gemm": 1, "dw_gemm": 1, "bwd_persistent": 2}
+        # algorithmic HBM bytes per weight element and launch kind (14 B x C x D per step in all):
+        # forward = read fp32 W 4 + write bf16 w_hat 2 + read it 2 (the first two only when the kernel normalises);
+        # backward = read w_hat 2 + write fp32 dW 4
+        fused_norm = "l2norm_w" not in kinds
+        bytes_in = {"fwd_gemm": 8.0 if fused_norm else 2.0, "bwd_persistent": 6.0, "dw_gemm": 4.0, "dx_gemm": 2.0,
+                    "bwd_g_gemm": 2.0, "l2norm_w": 6.0}
         gemm_kinds = {k: v for k, v in kinds.items() if k in gemms_in}
         dom = max(gemm_kinds, key=lambda k: gemm_kinds[k][0])
         dom_ms, dom_n = gemm_kinds[dom]
         dom_flops = flops_per_gemm * gemms_in[dom]
-        achieved = dom_flops / (dom_ms * 1e-3) / 1e12
-        peak = peaks["sustained"]
+        dom_bytes = bytes_in.get(dom, 0.0) * Cs * D
+        achieved_tf = dom_flops / (dom_ms * 1e-3) / 1e12
+        achieved_gbs = dom_bytes / (dom_ms * 1e-3) / 1e9
+        # which roof binds this kernel: the larger of its ideal times (tensor at the burst peak, HBM at the copy peak)
+        t_tensor, t_hbm = dom_flops / (peaks["burst"] * 1e12), dom_bytes / (peaks["hbm"] * 1e9)
+        bound = "tensor" if t_tensor >= t_hbm else "hbm"
+        timed_seconds = dev_ms * 1e-3
+        regime = "burst" if timed_seconds < 1.0 else "sustained"  # < 1 s of load: clocks have not settled under the cap
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
         # the ncu capture under profiles/ is of the default workload on one GPU: no figure for anything else
-        profiled = (B, C, D, world) == (WORKLOAD["B"], WORKLOAD["C"], WORKLOAD["D"], 1)
+        profiled = (B, C, D, world) == (CONFIGS["cfg4"]["B"], CONFIGS["cfg4"]["C"], CONFIGS["cfg4"]["D"], 1)
         if profiled and os.path.exists(tpath):
             try:
                 traffic = json.load(open(tpath)).get(dom)
             except Exception:
                 traffic = None
+        if bound == "tensor":
+            roof = {"bound": "tensor", "achieved": achieved_tf, "peak": peaks[regime], "unit": "TFLOP/s",
+                    "frac": achieved_tf / peaks[regime]}
+        else:
+            roof = {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks["hbm"], "unit": "GB/s",
+                    "frac": achieved_gbs / peaks["hbm"]}
+        roof.update({
+            "kernel": dom, "traffic": traffic, "regime": f"{regime} (timed region {timed_seconds:.3f} s)",
+            "peak_source": peaks["src"],
+            "frac_burst": achieved_tf / peaks["burst"], "frac_sustained": achieved_tf / peaks["sustained"],
+            "frac_hbm": achieved_gbs / peaks["hbm"], "achieved_tflops": achieved_tf, "achieved_gbs": achieved_gbs,
+            "launches_per_step": dom_n, "ms_per_step": dom_ms,
+            "algorithmic_flops_per_step": dom_flops, "algorithmic_bytes_per_step": dom_bytes,
+            "executed_flops_per_step": flops_per_gemm * {"bwd_persistent": 3, "bwd_g_gemm": 1}.get(dom, gemms_in[dom]),
+        })
+        step_tf = 6.0 * B * C * D / (ms_per_step * 1e-3) / 1e12
+        step_gbs = 14.0 * C * D / (ms_per_step * 1e-3) / 1e9
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "metric": args.metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "warmup_steps_run": warm,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic", "config": workload_config(args, world),
             "loss": final_loss,
-            "step_tflops_algorithmic": 6.0 * B * C * D / (ms_per_step * 1e-3) / 1e12,
-            "step_frac_of_peak": 6.0 * B * C * D / (ms_per_step * 1e-3) / 1e12 / (peak * world),
-            "roofline": {
-                "kernel": dom, "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": f"{peaks['src']} (sustained bf16, MEASURED_PEAKS.json)",
-                "launches_per_step": dom_n, "ms_per_step": dom_ms,
-                "algorithmic_flops_per_step": dom_flops,
-                "executed_flops_per_step": flops_per_gemm * {"bwd_persistent": 3, "bwd_g_gemm": 1}.get(dom, gemms_in[dom]),
-            },
+            "step_tflops_algorithmic": step_tf,
+            "step_frac_of_burst_peak": step_tf / (peaks["burst"] * world),
+            "step_frac_of_sustained_peak": step_tf / (peaks["sustained"] * world),
+            "step_frac_of_hbm_peak": step_gbs / (peaks["hbm"] * world),
+            "roofline": roof,
             "kernels_ms_per_step": {k: round(v[0], 4) for k, v in kinds.items()},
             "kernels_launches_per_step": {k: v[1] for k, v in kinds.items()},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * D * 4 + B * 8, "d2h_bytes_per_step": 4,
-                    "ms_per_step": e2e_wall_ms / args.steps, "timer": "wall clock between device syncs"},
+                    "ms_per_step": e2e_wall_net / args.steps, "timer": "wall clock between device syncs",
+                    "note": "value and e2e are separate passes (1 s apart) in slightly different power states: "
+                            "differences below ~3 % between them are not signal"},
             "gpu_launches": int(launches),
             "clocks": clocks,
+            "parity": parity,
         }
+        if flush:
+            line["l2_flush"] = {"bytes": 256 << 20, "ms_per_step_subtracted": fl_ms / args.steps}
+        if sustained is not None:
+            s_tf = 6.0 * B * C * D / (sustained["ms_per_step"] * 1e-3) / 1e12
+            sustained["step_frac_of_sustained_peak"] = s_tf / (peaks["sustained"] * world)
+            sustained["step_frac_of_burst_peak"] = s_tf / (peaks["burst"] * world)
+            line["sustained"] = sustained
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             rows = args.cpu_sample_rows or min(B, 256)  # ~10-20 s of CPU work in total
@@ -380,6 +566,9 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if not parity_ok:
+        print("bench.py: PARITY CHECK FAILED", file=sys.stderr, flush=True)
+        sys.exit(3)
 
 
 def main():

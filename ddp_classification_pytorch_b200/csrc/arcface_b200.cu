@@ -261,7 +261,7 @@ constexpr int kLaunchRefused = 1;  // internal: the cooperative launch was refus
 template <bool EXT, bool PAIR, bool TRACE = false, bool DYN = false>
 int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits, int64_t ldgl, __nv_bfloat16* gt,
                           int64_t chunk_rows, int nbuf, float* dw, float* dxhat, cudaStream_t st, BwdSetup su,
-                          unsigned long long* trace = nullptr) {
+                          unsigned long long* trace = nullptr, bool cooperative = true) {
   const int64_t B = W.B, Cs = W.Cs, D = W.D;
   BwdPlan pl;
   pl.chunk_rows = static_cast<int>(chunk_rows);
@@ -364,14 +364,21 @@ int launch_bwd_persistent(const Workspace& W, float s, const float* grad_logits,
   cfg.dynamicSmemBytes = kPSmemTotal;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
-  attr[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: they wait on one another
-  attr[0].val.cooperative = 1;
-  attr[1].id = cudaLaunchAttributeClusterDimension;  // PAIR: the two CTAs of a tile share a TPC
-  attr[1].val.clusterDim.x = 2;
-  attr[1].val.clusterDim.y = 1;
-  attr[1].val.clusterDim.z = 1;
+  int na = 0;
+  if (PAIR) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;  // the two CTAs of a tile share a TPC
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (cooperative) {  // all CTAs co-resident: they wait on one another.  (ARCB_BWD_NO_COOP drops the attribute for
+    attr[na].id = cudaLaunchAttributeCooperative;  // profiler runs: one CTA per SM on an idle GPU is co-resident anyway)
+    attr[na].val.cooperative = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = PAIR ? 2 : 1;
+  cfg.numAttrs = na;
   LaunchScope ls(ARCB_K_BWD_PERSISTENT, st);
   const cudaError_t le =
       cudaLaunchKernelEx(&cfg, kern, tmWhatK, tmXhatK, tmGtSt, tmGtMN, tmWhatMN, tmGtK, tmXhatMN, tmDx, tmDw, pl, ar);
@@ -810,6 +817,7 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   const bool persistent = !(flags & ARCB_BWD_PER_CHUNK);
   const bool pair_bwd = !(flags & ARCB_BWD_SINGLE_CTA);
   const bool dyn_feed = !(flags & ARCB_BWD_STATIC_SHARE);
+  const bool coop = !(flags & ARCB_BWD_NO_COOP);
   const bool ext = grad_logits != nullptr;
   if (!ext && (!lse || !target_logit)) return fail(ARCB_ERR_INVALID, "lse / target_logit required");
   if (ext && ldgl < Cs) return fail(ARCB_ERR_INVALID, "grad_logits leading dimension smaller than Cs");
@@ -860,8 +868,10 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
       if (pc2 > round_up(Cs, 256)) pc2 = round_up(Cs, 256);
       if (pc2 >= 256) {
         if (dyn_feed)
-          rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su)
-                   : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);
+          rc = ext ? launch_bwd_persistent<true, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su,
+                                                                    nullptr, coop)
+                   : launch_bwd_persistent<false, true, false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su,
+                                                                     nullptr, coop);
         else
           rc = ext ? launch_bwd_persistent<true, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su)
                    : launch_bwd_persistent<false, true>(W, s, grad_logits, ldgl, gt, pc2, nbuf, dw, dxhat, st, su);

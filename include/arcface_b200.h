@@ -49,6 +49,9 @@ extern "C" {
 #define ARCB_BWD_PER_CHUNK 0x10    /* one launch per GEMM and class chunk (no co-residency needed) */
 #define ARCB_BWD_SINGLE_CTA 0x20   /* persistent kernel with one CTA per 128 x 256 tile (what ncu can replay) */
 #define ARCB_BWD_STATIC_SHARE 0x40 /* persistent kernel, fixed share of the tile list per CTA pair (A/B runs) */
+#define ARCB_BWD_NO_COOP 0x80      /* PROFILING ONLY: default kernel launched without the cooperative attribute (ncu cannot
+                                      replay cooperative + cluster launches).  Safe only on an otherwise idle GPU, where
+                                      one CTA per SM is co-resident anyway; never set it in production. */
 /* arcb_gemm_bf16 (unit tests of the GEMM core) */
 #define ARCB_GEMM_PAIR 0x4         /* CTA-pair core (same bit as ARCB_FWD_PAIR) */
 

@@ -32,6 +32,46 @@ def test_graphed_step_equals_eager(shape):
     _lib.check(_lib.lib().arcb_check_watchdog(torch.cuda.current_stream().cuda_stream))
 
 
+def test_graphed_step_with_cached_head_follows_weight_updates():
+    """A head with the normalised-weight cache (cache_normalized_weight=True) stepped by torch.optim.SGD between
+    replays: the captured step must re-normalise the CURRENT weight on every replay, not freeze the cache's
+    'still valid' decision of capture time."""
+    from ddp_classification_pytorch_b200 import ArcMarginProduct
+    from ddp_classification_pytorch_b200.graphed import GraphedHeadStep
+    B, D, C = 128, 64, 2000
+    torch.manual_seed(5)
+    w0 = (torch.rand(C, D) * 2 - 1) * 0.05
+    batches = [(torch.randn(B, D, device="cuda"), torch.randint(0, C, (B,), device="cuda")) for _ in range(4)]
+
+    def run(graphed):
+        head = ArcMarginProduct(D, C, cache_normalized_weight=graphed).cuda()
+        with torch.no_grad():
+            head.weight.copy_(w0)
+        opt = torch.optim.SGD(head.parameters(), lr=5.0)
+        losses = []
+        if graphed:
+            with torch.no_grad():
+                head.forward_loss(*batches[0])  # fills the cache: an eager forward would now skip the normalisation
+            step = GraphedHeadStep(head, B)
+        for x, y in batches:
+            if graphed:
+                loss = step(x, y)
+            else:
+                head.weight.grad = None
+                loss = head.forward_loss(x, y)
+                loss.backward()
+            losses.append(loss.item())
+            opt.step()
+        torch.cuda.synchronize()
+        return losses, head.weight.detach().clone()
+
+    eager_losses, eager_w = run(False)
+    graph_losses, graph_w = run(True)
+    assert eager_losses[0] != pytest.approx(eager_losses[-1], rel=1e-3)  # the weight really moved
+    assert graph_losses == pytest.approx(eager_losses, rel=1e-5)
+    torch.testing.assert_close(graph_w, eager_w, rtol=1e-4, atol=1e-7)
+
+
 def test_graphed_step_rejects_cpu_head():
     from ddp_classification_pytorch_b200 import ArcMarginProduct
     from ddp_classification_pytorch_b200.graphed import GraphedHeadStep

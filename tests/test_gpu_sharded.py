@@ -86,13 +86,43 @@ def _nccl_worker(rank, world, port, out):
               and torch.equal(head.full_weight().cpu(), w)
               and clear.mean() > 0.9
               and np.array_equal(head.aux["top3"].cpu().numpy()[clear], ref["top3"][clear]))
+        # data-parallel rows in, reduce_scatter of dX out: this rank's rows only
+        b = B // world
+        rows = slice(rank * b, (rank + 1) * b)
+        head.weight.grad = None
+        xl = x[rows].cuda().requires_grad_(True)
+        loss2 = head.forward_loss(xl, y[rows].cuda(), gather_batch=True)
+        loss2.backward()
+        torch.cuda.synchronize()
+        n = world * b
+        ref2 = orc.head_forward_backward(x[:n].numpy(), w.numpy(), y[:n].numpy(), 30.0, 0.5, True)
+        ok = (ok and abs(loss2.item() - ref2["loss"]) <= 1e-3 * abs(ref2["loss"])
+              and tuple(xl.grad.shape) == (b, D)
+              and cosine_similarity(xl.grad.cpu().numpy(), ref2["dx"][rows]) >= 0.999
+              and np.linalg.norm(xl.grad.cpu().numpy()) == pytest.approx(world * np.linalg.norm(ref2["dx"][rows]), rel=2e-2)
+              and cosine_similarity(head.weight.grad.cpu().numpy(), ref2["dw"][lo:hi]) >= 0.999)
+        # the reference's wiring: a replicated head under DDP, fused loss through the wrapper -> dW all-reduced
+        rep = ArcMarginProduct(D, C, s=30.0, m=0.5, easy_margin=True).cuda()
+        with torch.no_grad():
+            rep.weight.copy_(w)
+        arc = torch.nn.parallel.DistributedDataParallel(rep, device_ids=[rank])
+        arc(x[rows].cuda(), y[rows].cuda(), fused_loss=True).backward()
+        torch.cuda.synchronize()
+        per_rank = [orc.head_forward_backward(x[r * b:(r + 1) * b].numpy(), w.numpy(), y[r * b:(r + 1) * b].numpy(),
+                                              30.0, 0.5, True)["dw"] for r in range(world)]
+        ok = ok and cosine_similarity(rep.weight.grad.cpu().numpy(), sum(per_rank) / world) >= 0.999
+        grads = [torch.empty_like(rep.weight.grad) for _ in range(world)]
+        dist.all_gather(grads, rep.weight.grad.contiguous())
+        ok = ok and all(torch.equal(grads[0], gr) for gr in grads)
         out[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_nccl_two_ranks_equal_unsharded():
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_ranks_equal_unsharded(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     with socket.socket() as s:
@@ -100,10 +130,10 @@ def test_nccl_two_ranks_equal_unsharded():
         port = s.getsockname()[1]
     with ctx.Manager() as mgr:
         out = mgr.dict()
-        procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, out)) for r in range(2)]
+        procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, out)) for r in range(world)]
         for p in procs:
             p.start()
         for p in procs:
             p.join(300)
             assert p.exitcode == 0
-        assert out.get(0) is True and out.get(1) is True, dict(out)
+        assert all(out.get(r) is True for r in range(world)), dict(out)

@@ -129,3 +129,108 @@ def test_sharded_head_equals_unsharded_oracle(world, easy):
             p.join(120)
             assert p.exitcode == 0
         assert all(out.get(r) is True for r in range(world)), dict(out)
+
+
+# ---- the reference's own multi-GPU wiring: DistributedDataParallel(ARC), arc_main.py:243 -------------------------
+def _ddp_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        B, D, C = 12, 16, 37
+        g = torch.Generator().manual_seed(77)
+        w_full = (torch.rand(C, D, generator=g) * 2 - 1) * 0.1
+        xs = [torch.randn(B, D, generator=g) for _ in range(world)]      # every rank scores its OWN batch
+        ys = [torch.randint(0, C, (B,), generator=g) for _ in range(world)]
+        head = ArcMarginProduct(D, C, s=30.0, m=0.5, easy_margin=True, _engine=OracleEngine())
+        with torch.no_grad():
+            head.weight.copy_(w_full)
+        arc = torch.nn.parallel.DistributedDataParallel(head)            # arc_main.py:243
+        xg = xs[rank].clone().requires_grad_(True)
+        loss = arc(xg, ys[rank], fused_loss=True)                        # through the wrapper: the reducer is armed
+        loss.backward()                                                  # arc_main.py:329
+        refs = [orc.head_forward_backward(xs[r].numpy(), w_full.numpy(), ys[r].numpy(), 30.0, 0.5, True) for r in range(world)]
+        mean_dw = sum(r["dw"] for r in refs) / world                     # what DDP's all-reduce (average) must leave
+        grads = [torch.empty_like(head.weight.grad) for _ in range(world)]
+        dist.all_gather(grads, head.weight.grad.contiguous())
+        ok = (
+            abs(loss.item() - refs[rank]["loss"]) < 1e-5 * abs(refs[rank]["loss"])
+            and all(torch.equal(grads[0], gr) for gr in grads)           # replicas hold the SAME gradient
+            and np.allclose(head.weight.grad.numpy(), mean_dw, rtol=1e-4, atol=1e-8)
+            and np.allclose(xg.grad.numpy(), refs[rank]["dx"], rtol=1e-4, atol=1e-8)
+        )
+        # the trap this entry exists for: the module's own method bypasses the wrapper, nothing is reduced
+        head.weight.grad = None
+        head.forward_loss(xs[rank], ys[rank]).backward()
+        dist.all_gather(grads, head.weight.grad.contiguous())
+        ok = ok and not torch.equal(grads[0], grads[1])
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fused_loss_through_ddp_wrapper_reduces_weight_grad():
+    world = 2
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        out = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_ddp_worker, args=(r, world, port, out)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+            assert p.exitcode == 0
+        assert all(out.get(r) is True for r in range(world)), dict(out)
+
+
+# ---- class-sharded head behind a data-parallel backbone: all_gather of the batch, reduce_scatter of dX -------------
+def _gather_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        b, D, C = 10, 16, 53
+        g = torch.Generator().manual_seed(5)
+        w_full = (torch.rand(C, D, generator=g) * 2 - 1) * 0.1
+        x_all = torch.randn(world * b, D, generator=g)
+        y_all = torch.randint(0, C, (world * b,), generator=g)
+        head = ArcMarginProduct(D, C, s=30.0, m=0.5, easy_margin=False, process_group=dist.group.WORLD,
+                                _engine=OracleEngine())
+        lo, hi = head.class_lo, head.class_hi
+        with torch.no_grad():
+            head.weight.copy_(w_full[lo:hi])
+        rows = slice(rank * b, (rank + 1) * b)
+        xg = x_all[rows].clone().requires_grad_(True)
+        loss = head.forward_loss(xg, y_all[rows], want_top3=True, gather_batch=True)
+        loss.backward()
+        ref = orc.head_forward_backward(x_all.numpy(), w_full.numpy(), y_all.numpy(), 30.0, 0.5, False)
+        counts = head.correct_counts()  # scores the gathered labels kept in aux
+        top3 = ref["top3"]
+        ok = (
+            abs(loss.item() - ref["loss"]) < 1e-5 * abs(ref["loss"])                      # mean over the GLOBAL batch
+            and tuple(xg.grad.shape) == (b, D)
+            and np.allclose(xg.grad.numpy(), world * ref["dx"][rows], rtol=1e-4, atol=1e-8)  # own rows, x world (DDP averages)
+            and np.allclose(head.weight.grad.numpy(), ref["dw"][lo:hi], rtol=1e-4, atol=1e-8)
+            and torch.equal(head.aux["labels"], y_all)
+            and counts.tolist() == [int((top3[:, 0] == y_all.numpy()).sum()),
+                                    int((top3 == y_all.numpy()[:, None]).any(1).sum()), world * b]
+        )
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gather_batch_reduce_scatter_equals_global_oracle(world):
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        out = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_gather_worker, args=(r, world, port, out)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+            assert p.exitcode == 0
+        assert all(out.get(r) is True for r in range(world)), dict(out)

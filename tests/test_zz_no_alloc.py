@@ -64,6 +64,11 @@ def test_static_forward_matches_workspace_forward_two_calls_in_a_row():
         with torch.no_grad():
             head.weight.copy_(w)
         assert loss.item() == pytest.approx(head.forward_loss(x, y).item(), rel=1e-3)
+        # ... and it is the RIGHT loss, not merely the same one: the CPU oracle on the same inputs
+        from oracle import arcface_oracle as orc
+        ref = orc.head_forward_backward(x.cpu().numpy(), w.cpu().numpy(), y.cpu().numpy(), 30.0, 0.5, easy)
+        assert loss.item() == pytest.approx(ref["loss"], rel=1e-3)
+        torch.testing.assert_close(lse.cpu().double(), torch.tensor(ref["lse"]).double(), rtol=2e-3, atol=1e-4)
 
 
 def test_static_forward_rejects_sizes_beyond_its_block():

@@ -12,7 +12,7 @@ and its DDP gradient all-reduce stay plain torch / cuDNN / NCCL; only the head i
 --head replicated : the reference's scheme -- every rank holds the full head under DDP (arc_main.py:243),
                     dW [C,D] is all-reduced by DDP.
 --head sharded    : classes sharded over the ranks; features / labels are all-gathered so every rank's shard sees
-                    the global batch; only [B,4] statistics and the [B,D] dX partial cross NVLink.
+                    the global batch; only [B,4] statistics cross NVLink in forward, dX returns by reduce_scatter.
 --head torch      : the reference head in eager fp32 PyTorch (oracle.TorchPort's op sequence), for comparison.
 """
 from __future__ import annotations
@@ -30,22 +30,6 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 import torch.nn.functional as F
-
-
-class _GatherRows(torch.autograd.Function):
-    """all_gather along dim 0; backward keeps this rank's rows of the (already fully reduced) gradient."""
-
-    @staticmethod
-    def forward(ctx, t, group):
-        world = dist.get_world_size(group)
-        ctx.rank, ctx.rows = dist.get_rank(group), t.shape[0]
-        out = torch.empty(world * t.shape[0], *t.shape[1:], dtype=t.dtype, device=t.device)
-        dist.all_gather_into_tensor(out, t.contiguous(), group=group)
-        return out
-
-    @staticmethod
-    def backward(ctx, g):
-        return g[ctx.rank * ctx.rows:(ctx.rank + 1) * ctx.rows].contiguous(), None
 
 
 class EagerArcHead(nn.Module):
@@ -80,10 +64,10 @@ def main():
     ap.add_argument("--channels-last", action="store_true")
     ap.add_argument("--fused-head-optimizer", action="store_true",
                     help="step the head with HeadSGD (one pass that also prepares the next forward's normalised weight)")
+    ap.add_argument("--out", default="", help="append the JSON result line to this file as well")
     args = ap.parse_args()
 
-    import torchvision
-    from ddp_classification_pytorch_b200 import ArcMarginProduct
+    from ddp_classification_pytorch_b200.trainer import ArcFaceTrainer, reference_backbone
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -95,81 +79,48 @@ def main():
     torch.backends.cudnn.benchmark = True  # arc_main.py:51
     torch.manual_seed(999)  # arc_main.py:61
 
-    model = torchvision.models.resnet50(weights=None)  # arc_main.py:223 (pretrained weights need the network)
-    model.fc = nn.Sequential(nn.Linear(model.fc.in_features, 512), nn.ReLU(), nn.Linear(512, 256), nn.LogSoftmax(dim=1))
-    model = model.to(dev)
+    model = reference_backbone(pretrained=False).to(dev)  # arc_main.py:223-231 (pretrained weights need the network)
     if args.channels_last:
         model = model.to(memory_format=torch.channels_last)
     group = dist.group.WORLD if world > 1 else None
-    if args.head == "torch":
-        head = EagerArcHead(256, args.classes).to(dev)
-    else:
-        head = ArcMarginProduct(256, args.classes, s=30, m=0.5, easy_margin=True,  # arc_main.py:234
-                                process_group=group if args.head == "sharded" else None).to(dev)
-    if world > 1:
-        model = nn.SyncBatchNorm.convert_sync_batchnorm(model)  # arc_main.py:239
-        model = nn.parallel.DistributedDataParallel(model, device_ids=[local])
-        if args.head != "sharded":
-            head = nn.parallel.DistributedDataParallel(head, device_ids=[local])  # arc_main.py:243
-    head_opt = None
-    if args.fused_head_optimizer and args.head != "torch":
-        from ddp_classification_pytorch_b200 import HeadSGD
-        opt = torch.optim.SGD(model.parameters(), lr=0.001, momentum=0.9, weight_decay=5e-4)
-        head_opt = HeadSGD(head.module if isinstance(head, nn.parallel.DistributedDataParallel) else head,
-                           lr=0.001, momentum=0.9, weight_decay=5e-4)
-    else:
-        opt = torch.optim.SGD([{"params": model.parameters()}, {"params": head.parameters()}],
-                              lr=0.001, momentum=0.9, weight_decay=5e-4)  # arc_main.py:252-253
+    trainer = ArcFaceTrainer(
+        model, 256, args.classes, head="sharded" if args.head == "sharded" else "replicated", process_group=group,
+        s=30.0, m=0.5, easy_margin=True,  # arc_main.py:234
+        lr=0.001, momentum=0.9, weight_decay=5e-4, fused_head_optimizer=args.fused_head_optimizer,
+        head_module=EagerArcHead(256, args.classes) if args.head == "torch" else None, device=dev)
 
     g = torch.Generator(device=dev).manual_seed(rank)
     x = torch.randn(args.batch, 3, args.image, args.image, device=dev, generator=g)
     if args.channels_last:
         x = x.to(memory_format=torch.channels_last)
     y = torch.randint(0, args.classes, (args.batch,), device=dev, generator=g)
-    head_mod = head.module if isinstance(head, nn.parallel.DistributedDataParallel) else head
-
-    def step():
-        opt.zero_grad(set_to_none=True)
-        if head_opt is not None:
-            head_opt.zero_grad(set_to_none=True)
-        feats = model(x)  # arc_main.py:325
-        if args.head == "sharded" and world > 1:
-            f_all, y_all = _GatherRows.apply(feats, group), _GatherRows.apply(y, group)
-            # mean over the GLOBAL batch on every rank; DDP then averages the backbone grads over ranks
-            loss = head_mod.forward_loss(f_all, y_all) * world
-        else:
-            loss = head_mod.forward_loss(feats, y)  # head + CrossEntropy fused (arc_main.py:326-327)
-        loss.backward()  # arc_main.py:329
-        if isinstance(head, nn.parallel.DistributedDataParallel):  # forward_loss bypasses DDP's hooks: reduce dW here
-            for p in head_mod.parameters():
-                dist.all_reduce(p.grad)
-                p.grad /= world
-        opt.step()  # arc_main.py:330
-        if head_opt is not None:
-            head_opt.step()
-        return loss
 
     for _ in range(args.warmup):
-        step()
+        trainer.step(x, y)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        loss = step()
+        loss = trainer.step(x, y)
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print(json.dumps({
+        line = json.dumps({
             "metric": "ResNet-50 + ArcFace end-to-end training images/s (synthetic 224x224)",
             "value": args.batch * world * args.steps / (ms.item() * 1e-3), "unit": "images/s", "n_gpus": world,
             "ms_per_step": ms.item() / args.steps, "head": args.head, "classes": args.classes,
-            "global_batch": args.batch * world, "loss": float(loss.detach()) / (world if args.head == "sharded" and world > 1 else 1),
-            "backbone": "torchvision resnet50 fp32 (cuDNN), untouched", "data": "synthetic"}))
+            "global_batch": args.batch * world, "loss": float(loss),
+            "loss_is": "mean over the global batch" if args.head == "sharded" and world > 1 else "mean over rank 0's rows",
+            "backbone": "torchvision resnet50 fp32 (cuDNN), untouched", "data": "synthetic"})
+        print(line)
+        if args.out:
+            with open(args.out, "a") as fh:
+                fh.write(line + "\n")
     if world > 1:
         dist.destroy_process_group()
 

@@ -19,7 +19,7 @@ _SRC = os.path.join(_PKG_DIR, "csrc", "arcface_b200.cu")
 _HDRS = [
     os.path.join(_PKG_DIR, "csrc", n)
     for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "gemm2_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh",
-              "optim_rows.cuh")
+              "optim_rows.cuh", "fwd_resident.cuh")
 ] + [os.path.join(_ROOT, "include", "arcface_b200.h")]
 
 NVCC_FLAGS = [
@@ -41,6 +41,8 @@ EXPORTED = [
 FWD_NORM_SEPARATE = 0x1
 FWD_NORM_FUSED = 0x2
 FWD_PAIR = 0x4
+FWD_STREAMING = 0x8
+FWD_BLOCK_MAXIMA = 0x200
 GEMM_PAIR = 0x4
 BWD_PER_CHUNK = 0x10
 BWD_SINGLE_CTA = 0x20

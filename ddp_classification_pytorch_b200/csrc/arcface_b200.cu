@@ -19,6 +19,7 @@
 #include "epilogues.cuh"
 #include "gemm2_sm100.cuh"
 #include "gemm_sm100.cuh"
+#include "fwd_resident.cuh"
 #include "rowwise.cuh"
 #include "optim_rows.cuh"
 
@@ -142,6 +143,8 @@ struct Workspace {
   unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
   int4* items;             // [items_cap][2] tile list of the persistent backward (bwd_items_kernel)
   int64_t items_cap;
+  float* bmax;             // resident forward: block maxima [2 * tiles_n][Bp], second half of the `part` region
+  int* fwd_mode;           // which forward filled the workspace (kFwd*): tells arcb_shard_top3 where the block maxima are
   int64_t total;
 };
 
@@ -184,6 +187,9 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
     w.items_cap = T * (w.Bp / kBNTile + dn) + ((B + 127) / 128) * dn * (2 * T + 1);
     w.items = reinterpret_cast<int4*>(take(w.items_cap * 32));
   }
+  // the resident forward leaves only 2 * lanes partials per row (lanes <= tiles_n / 4) in the first half of `part`
+  w.bmax = w.part ? reinterpret_cast<float*>(w.part + tiles_n * w.Bp) : nullptr;
+  w.fwd_mode = reinterpret_cast<int*>(take(4));
   w.total = off;
   return w;
 }
@@ -221,7 +227,7 @@ int launch_l2norm(const float* x, int64_t rows, int64_t D, int64_t ldx, __nv_bfl
 // Steps shared by the fused and the materialising forward: normalise, target preparation.
 int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
                    int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy, void* ws_ptr,
-                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, int w_mode = 0) {
+                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, int w_mode = 0, int fwd_mode = kFwdStreaming) {
   // w_mode: 0 = normalise the weight here, 1 = the workspace already holds w_hat / inv_norm of this weight,
   //         2 = the forward GEMM kernel normalises it on the fly (launch_gemm_norm)
   int rc = check_dims(B, Cs, D);
@@ -249,7 +255,8 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   const int xvec = (D % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
   target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.xhat, (int)W.Dp, W.inv_nx, xvec, (int)B,
                                              (int)W.Bp, (int)D, Cs, class_offset, s, cos_m, sin_m, th, mm, easy,
-                                             W.lbl_local, W.sub, W.zt, W.dphi, W.cos_t, W.counters, n_zero);
+                                             W.lbl_local, W.sub, W.zt, W.dphi, W.cos_t, W.counters, n_zero, W.fwd_mode,
+                                             fwd_mode);
   ARCB_CUDA(cudaGetLastError());
   *out_ws = W;
   return ARCB_OK;
@@ -626,13 +633,50 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   const bool shape_ok = (flags & ARCB_FWD_NORM_FUSED) || (B >= 512 && B <= 1024 && Cs >= 65536);
   bool fuse = !(flags & ARCB_FWD_NORM_SEPARATE) && shape_ok && !w_prenormalised && !pair_gemm && (D % 4 == 0) &&
               (ldw % 4 == 0) && D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
+  // x_hat-resident schedule (fwd_resident.cuh): the sample block stays in shared memory, one partial per row and CTA
+  const bool want_bmax = (flags & ARCB_FWD_BLOCK_MAXIMA) != 0;
+  const bool resident = !(flags & ARCB_FWD_STREAMING) && !pair_gemm && resident_forward_applies(B, Cs, round_up(D, 64));
   int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
-                          w_prenormalised ? 1 : (fuse ? 2 : 0));
+                          w_prenormalised ? 1 : (fuse ? 2 : 0),
+                          resident ? (want_bmax ? kFwdResidentBmax : kFwdResident) : kFwdStreaming);
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
   cudaError_t e = cudaSuccess;
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
+  NormArgs na_res{};
+  if (fuse) {
+    na_res.w = w; na_res.ldw = ldw; na_res.rows = Cs; na_res.D = (int)D; na_res.Dp = (int)W.Dp; na_res.what = W.what;
+    na_res.inv_nw = W.inv_nw; na_res.done = W.counters;
+    const int ahead = resident_lanes(B) + 2;  // a CTA's last tile is at most this far from the end
+    na_res.lookahead = ahead > 64 ? ahead : 64;
+    const int look = env_knobs().norm_look;
+    if (look > 0) na_res.lookahead = look > ahead ? look : ahead;
+  }
+  if (resident) {
+    ResParams rp{W.lbl_local, W.sub, W.part, want_bmax ? W.bmax : nullptr, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
+    if (fuse) {
+      {
+        LaunchScope ls(ARCB_K_FWD_GEMM, st);
+        e = launch_fwd_resident<true>(a, b, B, Cs, W.Dp, rp, na_res, st);
+      }
+      if (e != cudaSuccess) {  // the grid cannot be made co-resident right now: normalise in a kernel of its own
+        fuse = false;
+        rc = launch_l2norm(w, Cs, D, ldw, W.what, W.Dp, W.inv_nw, st, ARCB_K_L2NORM_W);
+        if (rc) return rc;
+      }
+    }
+    if (!fuse) {
+      LaunchScope ls(ARCB_K_FWD_GEMM, st);
+      e = launch_fwd_resident<false>(a, b, B, Cs, W.Dp, rp, NormArgs{}, st);
+    }
+    if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
+    const int n_part = 2 * resident_lanes(B);
+    LaunchScope ls(ARCB_K_MERGE, st, 1);
+    merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(W.part, n_part, W.Bp, W.zt, (int)B, stats);
+    ARCB_CUDA(cudaGetLastError());
+    return ARCB_OK;
+  }
   if (fuse) {
     NormArgs na;
     na.w = w; na.ldw = ldw; na.rows = Cs; na.D = (int)D; na.Dp = (int)W.Dp; na.what = W.what; na.inv_nw = W.inv_nw;
@@ -790,8 +834,8 @@ int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, in
   }
   LaunchScope ls(ARCB_K_TOP3, st);
   topk_rescore_kernel<<<static_cast<unsigned>(B), kTopkThreads, D * 4, st>>>(
-      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, nparts, W.Bp, (int)B, (int)D, Cs, class_offset, s,
-      top_val, top_idx);
+      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, W.bmax, W.fwd_mode, nparts, W.Bp, (int)B, (int)D,
+      Cs, class_offset, s, top_val, top_idx);
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;
 }

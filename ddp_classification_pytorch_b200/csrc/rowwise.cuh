@@ -15,6 +15,8 @@
 namespace arcb {
 
 constexpr float kNormEps = 1e-12f;  // F.normalize default eps
+// which forward kernel filled a workspace (written by target_prep_kernel, read by topk_rescore_kernel)
+enum : int { kFwdStreaming = 0, kFwdResidentBmax = 1, kFwdResident = 2 };
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -140,9 +142,12 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
                    float* __restrict__ inv_nx, int vec, int B, int Bp, int D, int64_t Cs, int64_t class_offset, float s,
                    float cos_m, float sin_m, float th, float mm, int easy, int* __restrict__ lbl_local,
                    float* __restrict__ sub, float* __restrict__ zt, float* __restrict__ dphi,
-                   float* __restrict__ cos_t, unsigned int* __restrict__ zero, int n_zero) {
-  // (also clears the per-tile counters of the forward kernel that normalises the weight itself)
+                   float* __restrict__ cos_t, unsigned int* __restrict__ zero, int n_zero, int* __restrict__ mode_out,
+                   int mode) {
+  // (also clears the per-tile counters of the forward kernel that normalises the weight itself, and records which
+  //  forward schedule is about to fill this workspace)
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n_zero; k += gridDim.x * blockDim.x) zero[k] = 0u;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *mode_out = mode;
   const int lane = threadIdx.x & 31;
   const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (i >= Bp) return;
@@ -326,8 +331,15 @@ __global__ void __launch_bounds__(kTopkThreads)
 topk_rescore_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, int64_t ldw,
                     const float* __restrict__ inv_nx, const float* __restrict__ inv_nw,
                     const int* __restrict__ lbl_local, const float* __restrict__ sub, const float2* __restrict__ part,
-                    int nparts, int64_t ldp, int B, int D, int64_t Cs, int64_t class_offset, float s,
-                    float* __restrict__ top_val, int64_t* __restrict__ top_idx) {
+                    const float* __restrict__ bmax, const int* __restrict__ fwd_mode, int nparts, int64_t ldp, int B,
+                    int D, int64_t Cs, int64_t class_offset, float s, float* __restrict__ top_val,
+                    int64_t* __restrict__ top_idx) {
+  // where the forward left the block maxima: the per-tile partials themselves (streaming schedule) or the separate
+  // array of the resident schedule; a resident forward that was not asked to keep them cannot serve this kernel
+  const int mode = *fwd_mode;
+  if (mode == kFwdResident) __trap();  // arcb_shard_top3 after a forward without ARCB_FWD_BLOCK_MAXIMA: fail loudly
+  const float* bm = (mode == kFwdStreaming) ? reinterpret_cast<const float*>(part) : bmax;
+  const int bm_step = (mode == kFwdStreaming) ? 2 : 1;
   extern __shared__ float xs[];  // D floats: the normalised embedding of this row
   __shared__ Top3 red[kTopkThreads / 32];
   __shared__ float thr_s;
@@ -339,7 +351,7 @@ topk_rescore_kernel(const float* __restrict__ x, int64_t ldx, const float* __res
   // (1) third largest block maximum (base-2 units u = s * log2e * cos)
   Top3 mine;
   for (int k = 0; k < 3; ++k) { mine.v[k] = -INFINITY; mine.i[k] = 0x7fffffff; }
-  for (int p = tid; p < nparts; p += blockDim.x) top3_insert(mine, part[p * ldp + row].x, p);
+  for (int p = tid; p < nparts; p += blockDim.x) top3_insert(mine, bm[(p * ldp + row) * bm_step], p);
   for (int o = 16; o > 0; o >>= 1) {
     Top3 other;
     for (int k = 0; k < 3; ++k) {
@@ -367,7 +379,7 @@ topk_rescore_kernel(const float* __restrict__ x, int64_t ldx, const float* __res
   Top3 best;
   for (int k = 0; k < 3; ++k) { best.v[k] = -INFINITY; best.i[k] = 0x7fffffff; }
   for (int p = 0; p < nparts; ++p) {
-    if (!(part[p * ldp + row].x >= thr)) continue;  // block-uniform
+    if (!(bm[(p * ldp + row) * bm_step] >= thr)) continue;  // block-uniform
     const int c_begin = p * 128;
     const int c_end = min(static_cast<int64_t>(c_begin + 128), Cs);
     for (int c = c_begin + warp; c < c_end; c += kTopkThreads / 32) {

@@ -166,7 +166,8 @@ class CudaEngine:
             cache = None
             ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
         _lib.check(fn(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"], cfg["m"],
-                      int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), int(cfg.get("flags", 0)), _stream()),
+                      int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats),
+                      int(cfg.get("flags", 0)) | (_lib.FWD_BLOCK_MAXIMA if cfg.get("want_top3") else 0), _stream()),
                    "arcb_shard_forward")
         if cache is not None:
             cache.valid = tag

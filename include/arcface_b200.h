@@ -44,6 +44,9 @@ extern "C" {
 #define ARCB_FWD_NORM_SEPARATE 0x1 /* always its own kernel before the GEMM */
 #define ARCB_FWD_NORM_FUSED 0x2    /* inside the GEMM kernel whenever the shape allows (D % 4 == 0, D <= 2048) */
 #define ARCB_FWD_PAIR 0x4          /* forward GEMM on CTA pairs (cta_group::2); default: one CTA per 128 x 256 tile */
+#define ARCB_FWD_STREAMING 0x8     /* never use the x_hat-resident schedule (default for Dp <= 512 and many classes: a
+                                      CTA keeps its 128 samples in shared memory and only w_hat streams) */
+#define ARCB_FWD_BLOCK_MAXIMA 0x200 /* keep the per-128-class block maxima: REQUIRED by a following arcb_shard_top3 */
 /* arcb_shard_backward: schedule.  Default: ONE persistent cooperative kernel whose CTA pairs (cta_group::2, 256 x 256
  * tile per pair of SMs) claim tiles from the global tile list as they go.  All schedules give the same gradients. */
 #define ARCB_BWD_PER_CHUNK 0x10    /* one launch per GEMM and class chunk (no co-residency needed) */
@@ -174,7 +177,8 @@ int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, 
                       int64_t ws_bytes, float* logits, int64_t ldl, void* stream);
 
 /* ---- exact top-3 / argmax of the logits: torch.max(out, 1) / out.topk(3), arc_main.py:338-345, :377-388 ----
- * Needs the workspace left by arcb_shard_forward for the same inputs.  Only the class blocks whose bf16
+ * Needs the workspace left by arcb_shard_forward (called with ARCB_FWD_BLOCK_MAXIMA) for the same inputs; after a
+ * forward without that flag the kernel traps rather than rank stale data.  Only the class blocks whose bf16
  * block maximum can still reach the top 3 are re-scored, in fp32 from the original x / w (margin value at
  * the label column).  top_val [B,3] = logits (descending), top_idx [B,3] = GLOBAL class ids (-1 if the shard
  * has fewer than 3 classes).  Class-sharded: all_gather the [B,3] pairs and keep the best 3. */

@@ -282,3 +282,44 @@ def test_exact_top3_vs_oracle_many_classes(shape):
     _sync_ok()
     assert torch.isfinite(loss)
     _check_top3(head.aux, ref, 30.0)
+
+
+@pytest.mark.parametrize("shape", [(1000, 512, 20000), (520, 192, 40003), (300, 64, 80000)])
+@pytest.mark.parametrize("fused_norm", [False, True])
+def test_resident_forward_matches_streaming_forward(shape, fused_norm):
+    """The x_hat-resident forward schedule (sample block kept in shared memory, one partial per row and CTA) against
+    the streaming one (a partial per row and class block + merge): same statistics, same loss, same exact top-3, and
+    both equal the oracle -- ragged class counts, ragged batch, with and without the in-kernel weight normalisation."""
+    B, D, C = shape
+    gen = torch.Generator().manual_seed(B + C)
+    w = ((torch.rand(C, D, generator=gen) * 2 - 1) * 0.05).cuda()
+    x = torch.randn(B, D, generator=gen).cuda()
+    y = torch.randint(0, C, (B,), generator=gen).cuda()
+    x[:8] = w[y[:8]] * 50 + 0.05 * x[:8]          # rows next to their class: large target logits, both branches
+    L = _lib.lib()
+    eng = CudaEngine()
+    norm = _lib.FWD_NORM_FUSED if fused_norm else _lib.FWD_NORM_SEPARATE
+    res = {}
+    for name, flags in (("resident", norm), ("streaming", norm | _lib.FWD_STREAMING)):
+        cfg = {"s": 30.0, "m": 0.5, "easy_margin": False, "class_offset": 0, "chunk_classes": 0, "flags": flags,
+               "want_top3": True}
+        n0 = L.arcb_launch_count()
+        stats, state = eng.shard_forward(x, w, y, cfg)
+        launches = L.arcb_launch_count() - n0
+        lse, zt, loss = eng.merge_loss(stats, 1, B)
+        val, idx = eng.shard_top3(x, w, state, cfg)
+        dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt)
+        _sync_ok()
+        res[name] = (lse.clone(), zt.clone(), loss.item(), val.clone(), idx.clone(), dw, dxhat, launches)
+    r, s_ = res["resident"], res["streaming"]
+    assert r[7] < s_[7]                                          # the two-level merge shrank to one launch
+    torch.testing.assert_close(r[0], s_[0], rtol=1e-5, atol=1e-5)  # lse: same bf16 cosines, other summation order
+    assert torch.equal(r[1], s_[1])                                # target logit: the same fp32 side path
+    assert r[2] == pytest.approx(s_[2], rel=1e-5)
+    assert torch.equal(r[4], s_[4])                                # exact top-3 from either set of block maxima
+    torch.testing.assert_close(r[3], s_[3], rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(r[5], s_[5], rtol=1e-3, atol=1e-7)
+    ref = orc.head_forward_backward(x.cpu().numpy(), w.cpu().numpy(), y.cpu().numpy(), 30.0, 0.5, False)
+    assert abs(r[2] - ref["loss"]) <= LOSS_RTOL * abs(ref["loss"])
+    np.testing.assert_allclose(r[0].cpu().numpy(), ref["lse"], rtol=2e-3)
+    assert cosine_similarity(r[5].cpu().numpy(), ref["dw"]) >= GRAD_COS

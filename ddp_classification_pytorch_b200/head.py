@@ -87,8 +87,8 @@ class _WeightCache:
         self.busy = 0
         self.generation = 0
 
-    def workspace(self, B, Cs, D, device):
-        need = _lib.lib().arcb_ws_bytes(B, Cs, D, 0)
+    def workspace(self, B, Cs, D, device, flags=0):
+        need = _lib.lib().arcb_ws_bytes(B, Cs, D, int(flags))
         if need <= 0:
             raise RuntimeError("arcb_ws_bytes rejected the sizes")
         if self.ws is None or self.key != (Cs, D, device) or need > self.ws_bytes:
@@ -134,8 +134,8 @@ class CudaEngine:
         return _canonical_inputs(x, w, label)
 
     @staticmethod
-    def _alloc_ws(B, Cs, D, device):
-        nbytes = _lib.lib().arcb_ws_bytes(B, Cs, D, 0)
+    def _alloc_ws(B, Cs, D, device, flags=0):
+        nbytes = _lib.lib().arcb_ws_bytes(B, Cs, D, int(flags))
         if nbytes <= 0:
             raise RuntimeError("arcb_ws_bytes rejected the sizes")
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
@@ -158,13 +158,13 @@ class CudaEngine:
         tag = cfg.get("w_tag")  # (data_ptr, version) of the parameter itself
         fn, gen = L.arcb_shard_forward, 0
         if cache is not None and cache.busy == 0 and tag is not None and tag[0] == wc.data_ptr():
-            ws, ws_bytes = cache.workspace(B, Cs, D, xc.device)
+            ws, ws_bytes = cache.workspace(B, Cs, D, xc.device, cfg.get("flags", 0))
             if cache.valid == tag:  # w_hat / inv_norm in the workspace belong to exactly this weight
                 fn = L.arcb_shard_forward_prenorm
             cache.valid = None  # until the call below has been enqueued
         else:
             cache = None
-            ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
+            ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device, cfg.get("flags", 0))
         _lib.check(fn(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"], cfg["m"],
                       int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats),
                       int(cfg.get("flags", 0)) | (_lib.FWD_BLOCK_MAXIMA if cfg.get("want_top3") else 0), _stream()),
@@ -179,7 +179,7 @@ class CudaEngine:
         L = _lib.lib()
         B, D = xc.shape
         Cs = wc.shape[0]
-        ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device)
+        ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device, cfg.get("flags", 0))
         out = torch.empty(B, Cs, dtype=torch.float32, device=xc.device)
         _lib.check(L.arcb_shard_logits(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"],
                                        cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(out), Cs,
@@ -218,7 +218,10 @@ class CudaEngine:
                                "construct the head with cache_normalized_weight=False for that pattern")
         dev = ws.device
         Dp = L.arcb_padded_dim(D)
-        scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
+        if grad_logits is None and L.arcb_keep_probs_active(B, Cs, D, cfg["s"], int(cfg.get("flags", 0))):
+            scratch, scratch_bytes = None, 0  # the forward kept the probabilities: nothing is recomputed
+        else:
+            scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
         dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
         dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
         _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),

@@ -130,7 +130,7 @@ def _declare(lib):
     lib.arcb_shard_forward_static.restype = i32
     lib.arcb_shard_forward_static.argtypes = fwd_args[:-2] + [vp, vp]
     lib.arcb_shard_top3.restype = i32
-    lib.arcb_shard_top3.argtypes = [vp, i64, vp, i64, i64, i64, i64, i64, f32, vp, i64, vp, vp, vp]
+    lib.arcb_shard_top3.argtypes = [vp, i64, vp, i64, i64, i64, i64, i64, f32, vp, i64, vp, vp, i32, vp]
     lib.arcb_merge_loss.restype = i32
     lib.arcb_merge_loss.argtypes = [vp, i64, i64, vp, vp, vp, vp]
     lib.arcb_shard_backward.restype = i32

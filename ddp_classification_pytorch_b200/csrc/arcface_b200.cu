@@ -148,6 +148,7 @@ struct Workspace {
   int64_t ldP;
   __nv_bfloat16* xc;       // ARCB_KEEP_PROBS: c (.) x_hat [B, Dp], the dW operand
   float* cvec;             // ARCB_KEEP_PROBS: c_i [Bp]
+  float* bmax_p;           // ARCB_KEEP_PROBS: block maxima [2 * tiles_n][Bp] (the partials carry a fixed reference there)
   float* bmax;             // resident forward: block maxima [2 * tiles_n][Bp], second half of the `part` region
   int* fwd_mode;           // which forward filled the workspace (kFwd*): tells arcb_shard_top3 where the block maxima are
   int64_t total;
@@ -157,9 +158,9 @@ struct Workspace {
 // row must span exactly two 256-column halves (bwd_probs.cuh), and with the fixed reference s2 = s log2(e) every P' must
 // stay a normal bf16 number: 2^(-2 s2) >= 2^-126.  Otherwise the flag is ignored and the backward recomputes.
 bool keep_probs_applies(int64_t B, int64_t Cs, int64_t D, float s, int flags) {
-  if (!(flags & ARCB_KEEP_PROBS) || (flags & (ARCB_FWD_STREAMING | ARCB_FWD_PAIR))) return false;
+  if (!(flags & ARCB_KEEP_PROBS) || (flags & ARCB_FWD_PAIR)) return false;
   if (D <= 256 || D > 512 || !(s > 0.f) || 2.f * s * 1.4426950408889634f > 120.f) return false;
-  return resident_forward_applies(B, Cs, (D + 63) / 64 * 64);
+  return B >= 128 && Cs >= 4096;  // small problems are launch bound either way: keep the default there
 }
 
 Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D, bool keep_probs = false) {
@@ -206,9 +207,11 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D, bool keep_probs = 
   w.fwd_mode = reinterpret_cast<int*>(take(4));
   w.probs = nullptr; w.xc = nullptr; w.cvec = nullptr;
   w.ldP = round_up(Cs, 64);
+  w.bmax_p = nullptr;
   if (keep_probs) {  // at the end: every other offset is the same with and without
     w.xc = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
     w.cvec = reinterpret_cast<float*>(take(w.Bp * 4));
+    w.bmax_p = reinterpret_cast<float*>(take(2 * tiles_n * w.Bp * 4));
     w.probs = reinterpret_cast<__nv_bfloat16*>(take(B * w.ldP * 2));
   }
   w.total = off;
@@ -744,19 +747,25 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
               (ldw % 4 == 0) && D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
   // x_hat-resident schedule (fwd_resident.cuh): the sample block stays in shared memory, one partial per row and CTA
   const bool want_bmax = (flags & ARCB_FWD_BLOCK_MAXIMA) != 0;
-  const bool resident = !(flags & ARCB_FWD_STREAMING) && !pair_gemm && resident_forward_applies(B, Cs, round_up(D, 64));
   // the workspace layout follows the flag and the shape (what arcb_ws_bytes sized); whether the probabilities are USED
   // also depends on the scale: too large an s falls back to the recompute backward on the same layout
   const bool probs_layout = keep_probs_applies(B, Cs, D, 1.f, flags);
   const bool keep_probs = keep_probs_applies(B, Cs, D, s, flags);
+  const bool resident = !keep_probs && !(flags & ARCB_FWD_STREAMING) && !pair_gemm &&
+                        resident_forward_applies(B, Cs, round_up(D, 64));
+  // which array arcb_shard_top3 finds the block maxima in: the partials themselves (streaming), or a separate array
+  const int fwd_mode = (resident || keep_probs) ? (want_bmax ? kFwdResidentBmax : kFwdResident) : kFwdStreaming;
   int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
-                          w_prenormalised ? 1 : (fuse ? 2 : 0),
-                          resident ? (want_bmax ? kFwdResidentBmax : kFwdResident) : kFwdStreaming, probs_layout);
+                          w_prenormalised ? 1 : (fuse ? 2 : 0), fwd_mode, probs_layout);
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
   cudaError_t e = cudaSuccess;
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
+  EpiFwdStatsP::Params epp{W.lbl_local, W.sub, W.part, want_bmax ? W.bmax_p : nullptr, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
+  CUtensorMap tmP;
+  if (keep_probs && !make_tmap_2d(&tmP, W.probs, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Cs, B, W.ldP * 2, 64, kBM))
+    return fail(ARCB_ERR_CUDA, "tensor map for the stored probabilities could not be encoded");
   NormArgs na_res{};
   if (fuse) {
     na_res.w = w; na_res.ldw = ldw; na_res.rows = Cs; na_res.D = (int)D; na_res.Dp = (int)W.Dp; na_res.what = W.what;
@@ -768,12 +777,11 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   }
   if (resident) {
     ResParams rp{W.lbl_local, W.sub, W.part, want_bmax ? W.bmax : nullptr, (int)W.Bp, (int)B, (int)Cs, s * kLog2e,
-                 keep_probs ? W.probs : nullptr, W.ldP};
+                 nullptr, W.ldP};
     if (fuse) {
       {
         LaunchScope ls(ARCB_K_FWD_GEMM, st);
-        e = keep_probs ? launch_fwd_resident<true, true>(a, b, B, Cs, W.Dp, rp, na_res, st)
-                       : launch_fwd_resident<true>(a, b, B, Cs, W.Dp, rp, na_res, st);
+        e = launch_fwd_resident<true>(a, b, B, Cs, W.Dp, rp, na_res, st);
       }
       if (e != cudaSuccess) {  // the grid cannot be made co-resident right now: normalise in a kernel of its own
         fuse = false;
@@ -783,8 +791,7 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
     }
     if (!fuse) {
       LaunchScope ls(ARCB_K_FWD_GEMM, st);
-      e = keep_probs ? launch_fwd_resident<false, true>(a, b, B, Cs, W.Dp, rp, NormArgs{}, st)
-                     : launch_fwd_resident<false>(a, b, B, Cs, W.Dp, rp, NormArgs{}, st);
+      e = launch_fwd_resident<false>(a, b, B, Cs, W.Dp, rp, NormArgs{}, st);
     }
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
     const int n_part = 2 * resident_lanes(B);
@@ -804,7 +811,8 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
     if (look > 0) na.lookahead = look > ahead ? look : ahead;
     {
       LaunchScope ls(ARCB_K_FWD_GEMM, st);
-      e = launch_gemm_norm<EpiFwdStats, 4>(a, b, B, Cs, W.Dp, ep, na, st);
+      e = keep_probs ? launch_gemm_norm<EpiFwdStatsP, 4>(a, b, B, Cs, W.Dp, epp, na, st, &tmP)
+                     : launch_gemm_norm<EpiFwdStats, 4>(a, b, B, Cs, W.Dp, ep, na, st);
     }
     if (e != cudaSuccess) {  // the grid cannot be made co-resident right now: two kernels instead
       fuse = false;
@@ -814,7 +822,8 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   }
   if (!fuse) {
     LaunchScope ls(ARCB_K_FWD_GEMM, st);
-    if (pair_gemm) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    if (keep_probs) e = launch_gemm<EpiFwdStatsP, kBNTile, 4, false, false>(a, b, &tmP, B, Cs, W.Dp, 1, epp, st);
+    else if (pair_gemm) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
     else e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
@@ -930,27 +939,30 @@ int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, 
 
 int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, int64_t B, int64_t Cs, int64_t D,
                     int64_t class_offset, float s, void* ws, int64_t ws_bytes, float* top_val, int64_t* top_idx,
-                    void* stream) {
+                    int flags, void* stream) {
   int rc = check_dims(B, Cs, D);
   if (rc) return rc;
   if (!x || !w || !ws || !top_val || !top_idx) return fail(ARCB_ERR_INVALID, "null pointer argument");
   if (D * 4 > 96 * 1024) return fail(ARCB_ERR_INVALID, "arcb_shard_top3 supports D <= 24576");
-  Workspace W = carve(ws, B, Cs, D);
+  flags = effective_flags(flags);
+  Workspace W = carve(ws, B, Cs, D, keep_probs_applies(B, Cs, D, 1.f, flags));
+  const bool probs_used = keep_probs_applies(B, Cs, D, s, flags);
   if (W.total > ws_bytes) return fail(ARCB_ERR_WORKSPACE, "workspace too small");
   const int nparts = 2 * static_cast<int>((Cs + kBNTile - 1) / kBNTile);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (D * 4 > 48 * 1024) {
-    static bool attr_set[64] = {false};
+    static std::atomic<bool> attr_set[64];
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    if (dev >= 0 && dev < 64 && !attr_set[dev].load(std::memory_order_acquire)) {
       ARCB_CUDA(cudaFuncSetAttribute(topk_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-      attr_set[dev] = true;
+      attr_set[dev].store(true, std::memory_order_release);
     }
   }
   LaunchScope ls(ARCB_K_TOP3, st);
   topk_rescore_kernel<<<static_cast<unsigned>(B), kTopkThreads, D * 4, st>>>(
-      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, W.bmax, W.fwd_mode, nparts, W.Bp, (int)B, (int)D,
+      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, probs_used ? W.bmax_p : W.bmax, W.fwd_mode, nparts, W.Bp,
+      (int)B, (int)D,
       Cs, class_offset, s, top_val, top_idx);
   ARCB_CUDA(cudaGetLastError());
   return ARCB_OK;

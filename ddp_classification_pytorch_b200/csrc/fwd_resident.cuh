@@ -175,25 +175,7 @@ fwd_resident_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (NORM && warp >= 4 + kEpiThreads / 32) {
     // ------------------ normaliser warps: F.normalize(weight) for the tiles still to come ------------------
-    const int nw = warp - (4 + kEpiThreads / 32);
-    const int64_t units = (static_cast<int64_t>(sc.tiles_n) * kResBN) / kNormUnitRows;
-    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
-      const int blk = static_cast<int>(u / (kResBN / kNormUnitRows));
-      while (blk > *reinterpret_cast<volatile int*>(&norm_progress) + na.lookahead) __nanosleep(200);
-      const int64_t row0 = u * kNormUnitRows + nw * (kNormUnitRows / kNormWarps);
-      int nrows = kNormUnitRows / kNormWarps;
-      if (row0 + nrows > na.rows) nrows = static_cast<int>(na.rows > row0 ? na.rows - row0 : 0);
-      if (nrows > 0) {
-        if (na.Dp <= 128) l2norm_rows_warp<1>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
-        else if (na.Dp <= 256) l2norm_rows_warp<2>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
-        else l2norm_rows_warp<4>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
-      }
-      __syncwarp();
-      if (lane == 0) {
-        __threadfence();
-        atomicAdd(na.done + blk, 1u);
-      }
-    }
+    normaliser_warp_loop(na, sc.tiles_n, warp - (4 + kEpiThreads / 32), lane, &norm_progress);
   } else if (warp >= 4 && warp < 4 + kEpiThreads / 32) {
     // -------------------------------- epilogue ----------------------------------
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access

@@ -193,7 +193,7 @@ class CudaEngine:
         val = torch.empty(B, 3, dtype=torch.float32, device=xc.device)
         idx = torch.empty(B, 3, dtype=torch.int64, device=xc.device)
         _lib.check(L.arcb_shard_top3(_ptr(xc), D, _ptr(wc), D, B, Cs, D, cfg["class_offset"], cfg["s"], _ptr(ws),
-                                     ws_bytes, _ptr(val), _ptr(idx), _stream()), "arcb_shard_top3")
+                                     ws_bytes, _ptr(val), _ptr(idx), int(cfg.get("flags", 0)), _stream()), "arcb_shard_top3")
         return val, idx
 
     def merge_loss(self, gathered, P, B):

@@ -188,14 +188,15 @@ int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, 
                       int64_t ws_bytes, float* logits, int64_t ldl, void* stream);
 
 /* ---- exact top-3 / argmax of the logits: torch.max(out, 1) / out.topk(3), arc_main.py:338-345, :377-388 ----
- * Needs the workspace left by arcb_shard_forward (called with ARCB_FWD_BLOCK_MAXIMA) for the same inputs; after a
+ * Needs the workspace left by arcb_shard_forward (called with ARCB_FWD_BLOCK_MAXIMA and otherwise the same flags as
+ * passed here) for the same inputs; after a
  * forward without that flag the kernel traps rather than rank stale data.  Only the class blocks whose bf16
  * block maximum can still reach the top 3 are re-scored, in fp32 from the original x / w (margin value at
  * the label column).  top_val [B,3] = logits (descending), top_idx [B,3] = GLOBAL class ids (-1 if the shard
  * has fewer than 3 classes).  Class-sharded: all_gather the [B,3] pairs and keep the best 3. */
 int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, int64_t B, int64_t Cs, int64_t D,
                     int64_t class_offset, float s, void* ws, int64_t ws_bytes, float* top_val, int64_t* top_idx,
-                    void* stream);
+                    int flags, void* stream);
 
 /* ---- merge shard records into the loss: nn.CrossEntropyLoss() mean, arc_main.py:245,:327 ----
  * stats [P, B, 4] (P shard records, e.g. after an all_gather; P = 1 unsharded)

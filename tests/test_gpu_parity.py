@@ -318,7 +318,7 @@ def test_resident_forward_matches_streaming_forward(shape, fused_norm):
     assert r[2] == pytest.approx(s_[2], rel=1e-5)
     assert torch.equal(r[4], s_[4])                                # exact top-3 from either set of block maxima
     torch.testing.assert_close(r[3], s_[3], rtol=1e-6, atol=1e-6)
-    torch.testing.assert_close(r[5], s_[5], rtol=1e-3, atol=1e-7)
+    torch.testing.assert_close(r[5], s_[5], rtol=1e-3, atol=1e-6)   # two backward runs: fp32 atomic order on tiny entries
     ref = orc.head_forward_backward(x.cpu().numpy(), w.cpu().numpy(), y.cpu().numpy(), 30.0, 0.5, False)
     assert abs(r[2] - ref["loss"]) <= LOSS_RTOL * abs(ref["loss"])
     np.testing.assert_allclose(r[0].cpu().numpy(), ref["lse"], rtol=2e-3)

@@ -504,6 +504,7 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.Cs = (int)Cs; ar.D = (int)D; ar.Dp = (int)W.Dp;
     ar.kb_total = (int)((B + kBK - 1) / kBK);
     ar.tiles_m = (int)((Cs + kBM - 1) / kBM);
+    ar.debug = env_knobs().debug_epi;
     static std::atomic<bool> attr_set[64];
     int dev = 0;
     cudaGetDevice(&dev);

@@ -49,6 +49,8 @@ struct PwArgs {
   int Cs, D, Dp;
   int kb_total;               // ceil(B / 64)
   int tiles_m;                // ceil(Cs / 128)
+  int debug;                  // ARCB_DEBUG_EPI (timing experiments, wrong results): 1 = no stores in pass 2, 2 = no pass 1 /
+                              // swap either, 3 = no epilogue work at all
 };
 
 // per-sample inputs of this backward: c_i, the dW operand c (.) x_hat, the exact label entries, and the zeroed dX_hat
@@ -224,10 +226,15 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P' [B, ldP] as MN
       const bool valid = cls < ar.Cs;
       const __nv_bfloat16* wrow = ar.what + static_cast<int64_t>(valid ? cls : 0) * ar.Dp + n_blk * kPwBN;
       const float inv = valid ? __ldg(ar.inv_nw + cls) : 0.f;
-      if (epi_tid == 0) mbar_arrive_expect_tx(&swap_bar[par], 2u * kEpiThreads * 4u);  // 2 CTAs x 256 threads x 4 B
+      if (epi_tid == 0 && ar.debug < 2) mbar_arrive_expect_tx(&swap_bar[par], 2u * kEpiThreads * 4u);  // 2 CTAs x 256 threads x 4 B
       // ---- pass 1: this thread's share of t_j ----
       float tpart = 0.f;
-      if (half_ok) {
+      if (ar.debug >= 2) {  // timing experiment: no projection, no swap
+        if (half_ok) {
+          mbar_wait(&tfull[acc], acc_phase, 0x400u + acc);
+          tc_fence_after();
+        }
+      } else if (half_ok) {
         mbar_wait(&tfull[acc], acc_phase, 0x400u + acc);
         tc_fence_after();
         const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * kPwBN) + (static_cast<uint32_t>(quad * 32) << 16);
@@ -253,7 +260,8 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P' [B, ldP] as MN
         }
       }
       // ---- swap: my partial goes to slot (rank * 2 + wg) of BOTH CTAs ----
-      {
+      float tj = 0.f;
+      if (ar.debug < 2) {
         const uint32_t off = ((par * 4u + static_cast<uint32_t>(rank * 2 + wg)) * kBM + static_cast<uint32_t>(row_in_tile)) * 4u;
 #pragma unroll
         for (uint32_t dst = 0; dst < 2; ++dst) {
@@ -262,18 +270,18 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P' [B, ldP] as MN
                        "r"(__float_as_uint(tpart)), "r"(b)
                        : "memory");
         }
+        mbar_wait(&swap_bar[par], use & 1u, 0xf00u + par);
+        const float* sp = swap + (par * 4u) * kBM + row_in_tile;
+        tj = (sp[0] + sp[kBM]) + (sp[2 * kBM] + sp[3 * kBM]);
+        if (!(inv < 0.5e12f)) tj = 0.f;  // clamped rows (||w|| <= eps) take no projection
       }
-      mbar_wait(&swap_bar[par], use & 1u, 0xf00u + par);
-      const float* sp = swap + (par * 4u) * kBM + row_in_tile;
-      float tj = (sp[0] + sp[kBM]) + (sp[2 * kBM] + sp[3 * kBM]);
-      if (!(inv < 0.5e12f)) tj = 0.f;  // clamped rows (||w|| <= eps) take no projection
       // ---- pass 2: dW = inv * (acc - t_j * w_hat) ----
       if (half_ok) {
         const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * kPwBN) + (static_cast<uint32_t>(quad * 32) << 16);
 #pragma unroll 1
         for (int c = c_begin; c < c_end; c += 32) {
           const int col0 = n_blk * kPwBN + c;
-          if (col0 >= ar.D) break;
+          if (col0 >= ar.D || ar.debug >= 3) break;
           uint4 wv[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) wv[q] = __ldg(reinterpret_cast<const uint4*>(wrow + c) + q);
@@ -289,7 +297,9 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P' [B, ldP] as MN
               r[q * 8 + 2 * e + 1] = inv * fmaf(-tj, __uint_as_float(wr[e] & 0xffff0000u), v[q * 8 + 2 * e + 1]);
             }
           }
-          if (use_tma) {
+          if (ar.debug >= 1) {
+            if (r[0] == 123.456f && r[31] == 654.321f) tj += 1.f;  // keep the arithmetic alive
+          } else if (use_tma) {
             chunk_out_tma<false, 2>(tmDw, epi_smem, wg, wg_tid, row_in_tile, it++, r, col0, t * kBM);
           } else if (valid) {
             float* o = ar.dw + static_cast<int64_t>(cls) * ar.D + col0;

@@ -170,119 +170,6 @@ struct EpiFwdStats {
 };
 
 // ------------------------------------------------------------------------------------
-// Forward statistics that also KEEP the softmax numerators (ARCB_KEEP_PROBS): P'[i, j] = bf16(2^(s2 (cos_ij - 1))), the
-// fixed reference s2 = s log2(e) (cos <= 1, so P' <= 1: no running maximum), written row-major [B, ldP] through a
-// 128B-swizzled staging box per warpgroup + bulk tensor stores (64 classes x 128 samples per box).  The partial of a
-// (tile column block, warpgroup) is (s2, sum of the ROUNDED P') -- the same (reference, sum) format the merge kernels
-// take -- so the softmax the backward reconstructs from P' sums to one.  Block maxima for the exact top-3 go to their
-// own array when asked for.
-struct EpiFwdStatsP {
-  static constexpr int kSmemBytes = 2 * kBM * 128;  // one [128 x 64] bf16 box per warpgroup
-  static constexpr bool kUsesTmC = true;            // tmC: P' [B, Cs] bf16 (pitch ldP), box [128 x 64]
-  struct Params {
-    const int* lbl_local;
-    const float* phi;
-    float2* part;
-    float* bmax;  // [2 * tiles_n][ldp] or nullptr
-    int ldp;
-    int B, C;
-    float s2;
-  };
-  using State = EpiNoState;
-  __device__ static void init(const Params&, State&) {}
-  __device__ static void drain(int epi_tid) {
-    if ((epi_tid & 127) == 0) tma_store_wait_all0();
-  }
-  template <int BN>
-  __device__ static void consume(const Params& p, State&, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
-                                 int row_in_tile, int epi_tid, uint8_t* smem) {
-    const int wg = epi_tid >> 7;
-    const int wg_tid = epi_tid & 127;
-    const int row = tc.m_blk * kBM + row_in_tile;
-    int lbl = -1;
-    float phi = 0.f;
-    if (row < p.B) {
-      lbl = __ldg(p.lbl_local + row);
-      phi = __ldg(p.phi + row);
-    }
-    float run_l = 0.f, blk_m = -INFINITY;
-    bool any = false;
-    const int col_base = tc.n_blk * BN;
-    uint8_t* buf = smem + wg * (kBM * 128);
-    const uint32_t srow = smem_u32(buf) + row_in_tile * 128;
-    const uint32_t sw = static_cast<uint32_t>(row_in_tile & 7);
-#pragma unroll 1
-    for (int bx = 0; bx < BN / 128; ++bx) {  // this warpgroup's two boxes of 64 classes
-      const int box_col0 = col_base + wg * (BN / 2) + bx * 64;
-      if (box_col0 >= p.C) break;  // warpgroup-uniform
-      // the bulk store that last used the staging box has finished reading it
-      if (wg_tid == 0) tma_store_wait_read0();
-      named_bar_sync(2 + wg, kWgThreads);
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        const int c = wg * (BN / 2) + bx * 64 + h * 32;
-        const int col0 = col_base + c;
-        float v[32];
-        if (col0 < p.C) {
-          tmem_ld32(taddr + c, v);
-          any = true;
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = -INFINITY;
-        }
-        if (col0 + 32 > p.C) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j >= p.C) v[j] = -INFINITY;
-        }
-        const unsigned d = static_cast<unsigned>(lbl - col0);
-        if (d < 32u) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j == static_cast<int>(d)) v[j] = phi;
-        }
-        if (p.bmax) {
-          float cm = v[0];
-#pragma unroll
-          for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
-          blk_m = fmaxf(blk_m, cm);
-        }
-        uint32_t pk[16];
-        float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          pk[j >> 1] = pack_bf16x2(ex2_approx(fmaf(v[j], p.s2, -p.s2)), ex2_approx(fmaf(v[j + 1], p.s2, -p.s2)));
-          a0 += __uint_as_float(pk[j >> 1] << 16);  // the rounded values: what the backward will use
-          a1 += __uint_as_float(pk[j >> 1] & 0xffff0000u);
-        }
-        run_l += a0 + a1;
-        const uint32_t q0 = static_cast<uint32_t>(h * 4);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t a = srow + (((q0 + q) ^ sw) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
-                       "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
-                       : "memory");
-        }
-      }
-      fence_proxy_async_smem();
-      named_bar_sync(2 + wg, kWgThreads);
-      if (wg_tid == 0) {
-        tma_store_2d(&tmC, buf, box_col0, tc.m_blk * kBM);  // rows >= B and classes >= C are clipped by the tensor map
-        tma_store_commit();
-      }
-    }
-    if (row < p.B) {
-      p.part[static_cast<int64_t>(tc.n_blk * 2 + wg) * p.ldp + row] =
-          any ? make_float2(p.s2, run_l) : make_float2(-INFINITY, 0.f);
-      if (p.bmax) p.bmax[static_cast<int64_t>(tc.n_blk * 2 + wg) * p.ldp + row] = blk_m * p.s2;
-    }
-  }
-  template <int BN>
-  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
-};
-
-// ------------------------------------------------------------------------------------
 struct EpiLogits {
   static constexpr int kSmemBytes = 0;
   static constexpr bool kUsesTmC = false;

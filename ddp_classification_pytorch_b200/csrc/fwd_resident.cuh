@@ -10,12 +10,7 @@
 //   * the online (max, sum-exp) of a row lives in the registers of the epilogue thread that owns it across ALL class
 //     tiles of the CTA: one partial per row and CTA leaves the kernel (2 * lanes per row instead of 2 * C / 256), so
 //     the merge is a single small launch;
-//   * the block maxima the exact top-3 re-score needs (arcb_shard_top3) are written only when asked for;
-//   * KEEP_P (ARCB_KEEP_PROBS): the epilogue also stores P'[i, j] = bf16(2^(s2 (cos_ij - 1))) -- the softmax numerators
-//     relative to the fixed reference s2 = s log2(e) (cos <= 1, so P' <= 1 and nothing needs a running maximum) -- as
-//     a row-major [B, ldP] matrix, straight from registers (each thread owns 64 contiguous bytes of its row per chunk).
-//     The backward then runs WITHOUT its recompute GEMM (bwd_probs.cuh): g_ij = c_i P'_ij with c_i = gscale 2^(s2 - lse2_i).
-//     The row sum is taken from the ROUNDED values, so the softmax the backward sees sums to one.
+//   * the block maxima the exact top-3 re-score needs (arcb_shard_top3) are written only when asked for.
 // CTA c works on sample block c % tiles_m and class tiles lane, lane + lanes, ... with lane = c / tiles_m and
 // lanes = grid / tiles_m: at any time the CTAs are on neighbouring class tiles, so a w_hat tile is fetched from HBM
 // once and found in L2 by the other sample blocks, and the in-kernel normaliser (NORM, see gemm_sm100.cuh) still
@@ -56,11 +51,9 @@ struct ResParams {
   int ldp;
   int B, C;
   float s2;
-  __nv_bfloat16* probs;  // KEEP_P: [B, ldP] row-major (ldP % 64 == 0), else nullptr
-  int64_t ldP;
 };
 
-template <bool NORM, bool KEEP_P = false>
+template <bool NORM>
 __global__ void __launch_bounds__(kGemmThreads + (NORM ? 32 * kNormWarps : 0), 1)
 fwd_resident_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const ResSched sc,
                     const ResParams ep, const NormArgs na) {
@@ -175,7 +168,25 @@ fwd_resident_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (NORM && warp >= 4 + kEpiThreads / 32) {
     // ------------------ normaliser warps: F.normalize(weight) for the tiles still to come ------------------
-    normaliser_warp_loop(na, sc.tiles_n, warp - (4 + kEpiThreads / 32), lane, &norm_progress);
+    const int nw = warp - (4 + kEpiThreads / 32);
+    const int64_t units = (static_cast<int64_t>(sc.tiles_n) * kResBN) / kNormUnitRows;
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+      const int blk = static_cast<int>(u / (kResBN / kNormUnitRows));
+      while (blk > *reinterpret_cast<volatile int*>(&norm_progress) + na.lookahead) __nanosleep(200);
+      const int64_t row0 = u * kNormUnitRows + nw * (kNormUnitRows / kNormWarps);
+      int nrows = kNormUnitRows / kNormWarps;
+      if (row0 + nrows > na.rows) nrows = static_cast<int>(na.rows > row0 ? na.rows - row0 : 0);
+      if (nrows > 0) {
+        if (na.Dp <= 128) l2norm_rows_warp<1>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 256) l2norm_rows_warp<2>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else l2norm_rows_warp<4>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+      }
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence();
+        atomicAdd(na.done + blk, 1u);
+      }
+    }
   } else if (warp >= 4 && warp < 4 + kEpiThreads / 32) {
     // -------------------------------- epilogue ----------------------------------
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
@@ -216,55 +227,23 @@ fwd_resident_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int j = 0; j < 32; ++j)
               if (j == static_cast<int>(d)) v[j] = phi;
           }
-          if constexpr (!KEEP_P) {
-            float cm = v[0];
+          float cm = v[0];
 #pragma unroll
-            for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
-            blk_m = fmaxf(blk_m, cm);
-            const float nm = fmaxf(run_m, cm);
-            run_l *= ex2_approx((run_m - nm) * ep.s2);
-            const float off = nm * ep.s2;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+          for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
+          blk_m = fmaxf(blk_m, cm);
+          const float nm = fmaxf(run_m, cm);
+          run_l *= ex2_approx((run_m - nm) * ep.s2);
+          const float off = nm * ep.s2;
+          float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              a0 += ex2_approx(fmaf(v[j + 0], ep.s2, -off));
-              a1 += ex2_approx(fmaf(v[j + 1], ep.s2, -off));
-              a2 += ex2_approx(fmaf(v[j + 2], ep.s2, -off));
-              a3 += ex2_approx(fmaf(v[j + 3], ep.s2, -off));
-            }
-            run_l += (a0 + a1) + (a2 + a3);
-            run_m = nm;
-          } else {
-            if (ep.bmax) {
-              float cm = v[0];
-#pragma unroll
-              for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
-              blk_m = fmaxf(blk_m, cm);
-            }
-            // P' = 2^(s2 cos - s2) <= 1, rounded to bf16; padded classes (cos = -inf) give exactly 0
-            uint32_t pk[16];
-            float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              pk[j >> 1] = pack_bf16x2(ex2_approx(fmaf(v[j], ep.s2, -ep.s2)), ex2_approx(fmaf(v[j + 1], ep.s2, -ep.s2)));
-              a0 += __uint_as_float(pk[j >> 1] << 16);           // the rounded values: what the backward will use
-              a1 += __uint_as_float(pk[j >> 1] & 0xffff0000u);
-            }
-            run_l += a0 + a1;
-            run_m = 1.f;  // the partial's reference: u = s2 * 1 (written as run_m * s2 below)
-            if (row < ep.B) {
-              __nv_bfloat16* prow = ep.probs + static_cast<int64_t>(row) * ep.ldP + col0;
-              if (col0 + 32 <= ep.C) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                  *reinterpret_cast<uint4*>(prow + q * 8) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-              } else {
-                const unsigned short* h = reinterpret_cast<const unsigned short*>(pk);
-                for (int j = 0; j < 32; ++j)
-                  if (col0 + j < ep.C) reinterpret_cast<unsigned short*>(prow)[j] = h[j];
-              }
-            }
+          for (int j = 0; j < 32; j += 4) {
+            a0 += ex2_approx(fmaf(v[j + 0], ep.s2, -off));
+            a1 += ex2_approx(fmaf(v[j + 1], ep.s2, -off));
+            a2 += ex2_approx(fmaf(v[j + 2], ep.s2, -off));
+            a3 += ex2_approx(fmaf(v[j + 3], ep.s2, -off));
           }
+          run_l += (a0 + a1) + (a2 + a3);
+          run_m = nm;
         }
         tc_fence_before();
         __syncwarp();
@@ -306,7 +285,7 @@ inline int resident_lanes(int64_t B) {
 
 // Launch.  NORM: the weight is normalised inside the kernel (cooperative launch: a tile may wait for rows normalised by
 // any other CTA, so the whole grid has to be resident; a refused launch returns the error with nothing enqueued).
-template <bool NORM, bool KEEP_P = false>
+template <bool NORM>
 inline cudaError_t launch_fwd_resident(const Operand& a, const Operand& b, int64_t M, int64_t N, int64_t K,
                                        const ResParams& ep, NormArgs na, cudaStream_t stream) {
   CUtensorMap tmA, tmB;
@@ -322,7 +301,7 @@ inline cudaError_t launch_fwd_resident(const Operand& a, const Operand& b, int64
   if (sc.lanes < 1) return cudaErrorInvalidValue;
   // NORM: every SM runs a CTA (the ones without class tiles still normalise); else only the CTAs that have tiles
   const int grid = NORM ? sms : sc.lanes * sc.tiles_m;
-  auto kern = fwd_resident_kernel<NORM, KEEP_P>;
+  auto kern = fwd_resident_kernel<NORM>;
   static std::atomic<bool> attr_set[64];
   int dev = 0;
   cudaGetDevice(&dev);

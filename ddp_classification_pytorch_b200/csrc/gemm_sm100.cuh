@@ -23,7 +23,6 @@
 #include <stdlib.h>
 
 #include <atomic>
-#include <type_traits>
 
 #include "ptx_sm100.cuh"
 #include "rowwise.cuh"
@@ -60,90 +59,6 @@ struct NormArgs {
 };
 constexpr int kNormUnitRows = 64;
 constexpr int kNormWarps = 8;  // normaliser warps per CTA (NORM kernels): 8 x 4 rows x 2 KB = 64 KB of loads in flight per SM
-
-// The normaliser warps of the forward kernels (NORM builds): F.normalize(self.weight) for the class tiles still to come.
-// Units of 64 rows, CTA c takes units c, c + grid, ...; warp nw owns 8 rows of a unit = 4 batches of 2 rows.  The loop is
-// software pipelined ACROSS batches and units: the next batch's loads (also the next unit's first batch) are issued
-// before the current batch is reduced / stored and before the unit's release fence, so the fence's wait for the stores
-// overlaps the latency of loads that are already in flight.  `progress` = class tile the CTA's TMA producer is on; the
-// warps stay at most na.lookahead tiles ahead of it (w_hat should still be in L2 when the bulk loads come for it).
-__device__ __forceinline__ void normaliser_warp_loop(const NormArgs& na, int tiles_n, int nw, int lane, const int* progress) {
-  constexpr int BN = 256;
-  const int64_t units = (static_cast<int64_t>(tiles_n) * BN) / kNormUnitRows;
-  constexpr int kRowsPerWarp = kNormUnitRows / kNormWarps;  // 8
-  constexpr int kBatches = kRowsPerWarp / 2;                // 4
-  auto allowed = [&](int64_t u) {
-    return static_cast<int>(u / (BN / kNormUnitRows)) <= *reinterpret_cast<const volatile int*>(progress) + na.lookahead;
-  };
-  auto rows_of = [&](int64_t u, int bt, int64_t& row0) {
-    row0 = u * kNormUnitRows + nw * kRowsPerWarp + bt * 2;
-    const int64_t left = na.rows - row0;
-    return left >= 2 ? 2 : (left > 0 ? static_cast<int>(left) : 0);
-  };
-  auto run = [&](auto nv_tag) {
-    constexpr int NV = decltype(nv_tag)::value;
-    RowPair<NV> cur, nxt;
-    int64_t u = blockIdx.x;
-    if (u >= units) return;
-    while (!allowed(u)) __nanosleep(200);
-    int64_t r0;
-    int n = rows_of(u, 0, r0);
-    rowpair_load<NV>(cur, na.w, na.ldw, r0, n, na.D, lane);
-    while (u < units) {
-      const int64_t un = u + gridDim.x;
-#pragma unroll
-      for (int bt = 0; bt < kBatches; ++bt) {
-        bool have_next = false;
-        if (bt + 1 < kBatches) {
-          n = rows_of(u, bt + 1, r0);
-          rowpair_load<NV>(nxt, na.w, na.ldw, r0, n, na.D, lane);
-          have_next = true;
-        } else if (un < units && allowed(un)) {  // the next unit's first batch, unless that would run too far ahead
-          n = rows_of(un, 0, r0);
-          rowpair_load<NV>(nxt, na.w, na.ldw, r0, n, na.D, lane);
-          have_next = true;
-        }
-        rowpair_finish<NV>(cur, na.what, na.Dp, na.inv_nw, lane);
-        if (bt + 1 == kBatches) {  // unit complete: publish (release) -- the loads issued above are still in flight
-          __syncwarp();
-          if (lane == 0) {
-            __threadfence();
-            atomicAdd(na.done + static_cast<int>(u / (BN / kNormUnitRows)), 1u);
-          }
-        }
-        if (have_next) {
-          cur = nxt;
-        } else if (bt + 1 == kBatches && un < units) {  // was not allowed to prefetch: wait, then load
-          while (!allowed(un)) __nanosleep(200);
-          n = rows_of(un, 0, r0);
-          rowpair_load<NV>(cur, na.w, na.ldw, r0, n, na.D, lane);
-        }
-      }
-      u = un;
-    }
-  };
-  if (na.Dp <= 128) run(std::integral_constant<int, 1>{});
-  else if (na.Dp <= 256) run(std::integral_constant<int, 2>{});
-  else if (na.Dp <= 512) run(std::integral_constant<int, 4>{});
-  else {
-    // wide rows: two batches in flight would not fit the register budget -- one unit at a time, as before
-    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
-      while (!allowed(u)) __nanosleep(200);
-      const int64_t row0 = u * kNormUnitRows + nw * kRowsPerWarp;
-      int nrows = kRowsPerWarp;
-      if (row0 + nrows > na.rows) nrows = static_cast<int>(na.rows > row0 ? na.rows - row0 : 0);
-      if (nrows > 0) {
-        if (na.Dp <= 1024) l2norm_rows_warp<8>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
-        else l2norm_rows_warp<16>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
-      }
-      __syncwarp();
-      if (lane == 0) {
-        __threadfence();
-        atomicAdd(na.done + static_cast<int>(u / (BN / kNormUnitRows)), 1u);
-      }
-    }
-  }
-}
 
 struct TileCoord {
   int m_blk, n_blk, kb0, kb1;
@@ -300,7 +215,27 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (NORM && warp >= 4 + kEpiThreads / 32) {
     // ------------------ normaliser warps: F.normalize(weight) for the tiles still to come ------------------
-    normaliser_warp_loop(na, sc.tiles_n, warp - (4 + kEpiThreads / 32), lane, &norm_progress);
+    const int nw = warp - (4 + kEpiThreads / 32);
+    const int64_t units = (static_cast<int64_t>(sc.tiles_n) * BN) / kNormUnitRows;
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+      const int blk = static_cast<int>(u / (BN / kNormUnitRows));
+      while (blk > *reinterpret_cast<volatile int*>(&norm_progress) + na.lookahead) __nanosleep(200);
+      const int64_t row0 = u * kNormUnitRows + nw * (kNormUnitRows / kNormWarps);
+      int nrows = kNormUnitRows / kNormWarps;
+      if (row0 + nrows > na.rows) nrows = static_cast<int>(na.rows > row0 ? na.rows - row0 : 0);
+      if (nrows > 0) {
+        if (na.Dp <= 128) l2norm_rows_warp<1>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 256) l2norm_rows_warp<2>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 512) l2norm_rows_warp<4>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else if (na.Dp <= 1024) l2norm_rows_warp<8>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+        else l2norm_rows_warp<16>(na.w, na.ldw, row0, nrows, na.D, na.what, na.Dp, na.inv_nw, lane);
+      }
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence();
+        atomicAdd(na.done + blk, 1u);
+      }
+    }
   } else if (warp >= 4) {
     // -------------------------------- epilogue ----------------------------------
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
@@ -469,8 +404,7 @@ inline cudaError_t launch_gemm(const Operand& a, const Operand& b, const CUtenso
 // path".  na.done must have been zeroed on `stream`.
 template <class Epi, int STAGES>
 inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t M, int64_t N, int64_t K,
-                                    const typename Epi::Params& ep, NormArgs na, cudaStream_t stream,
-                                    const CUtensorMap* tmC_opt = nullptr) {
+                                    const typename Epi::Params& ep, NormArgs na, cudaStream_t stream) {
   constexpr int BN = 256;
   using L = GemmSmem<Epi, BN, STAGES>;
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
@@ -507,7 +441,7 @@ inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t 
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC_opt ? *tmC_opt : tmA, sc, ep, na);
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmA, sc, ep, na);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e;
 }

@@ -126,58 +126,6 @@ __device__ __forceinline__ void l2norm_rows_warp(const float* __restrict__ x, in
   }
 }
 
-// Software-pipelined variant for the normaliser warps inside the forward kernels: rows are handled in batches of two;
-// the loads of batch k + 1 are issued BEFORE batch k is reduced and stored, so a warp always has 2 rows in flight and
-// never sits idle between "last load landed" and "next load issued" (the duty cycle, not the byte count, was what held
-// the in-kernel normalisation at ~2 TB/s).  Same arithmetic and summation order as l2norm_rows_kernel<NV>.
-template <int NV>
-struct RowPair {
-  float4 v[2][NV];
-  int64_t row0;
-  int n;  // rows that are real (0..2)
-};
-template <int NV>
-__device__ __forceinline__ void rowpair_load(RowPair<NV>& b, const float* __restrict__ x, int64_t ldx, int64_t row0, int n,
-                                             int D, int lane) {
-  b.row0 = row0;
-  b.n = n;
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {
-    const float* xr = x + (row0 + j) * ldx;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int e = (i * 32 + lane) * 4;
-      b.v[j][i] = (j < n && e < D) ? ld_stream_f4(xr + e) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  }
-}
-template <int NV>
-__device__ __forceinline__ void rowpair_finish(const RowPair<NV>& b, __nv_bfloat16* __restrict__ out, int Dp,
-                                               float* __restrict__ inv_norm, int lane) {
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {
-    if (j >= b.n) break;
-    float ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < NV; ++i)
-      ss += b.v[j][i].x * b.v[j][i].x + b.v[j][i].y * b.v[j][i].y + b.v[j][i].z * b.v[j][i].z + b.v[j][i].w * b.v[j][i].w;
-    ss = warp_sum(ss);
-    const float inv = 1.f / fmaxf(sqrtf(ss), kNormEps);
-    __nv_bfloat16* orow = out + (b.row0 + j) * Dp;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int e = (i * 32 + lane) * 4;
-      if (e < Dp) {
-        uint2 pk;
-        pk.x = pack_bf16x2(b.v[j][i].x * inv, b.v[j][i].y * inv);
-        pk.y = pack_bf16x2(b.v[j][i].z * inv, b.v[j][i].w * inv);
-        *reinterpret_cast<uint2*>(orow + e) = pk;
-      }
-    }
-    if (lane == 0) inv_norm[b.row0 + j] = inv;
-  }
-}
-
 // One warp per sample: exact fp32 target cosine and everything derived from it.
 
 //   lbl_local : label - class_offset when this shard owns the class, else -1

@@ -218,10 +218,7 @@ class CudaEngine:
                                "construct the head with cache_normalized_weight=False for that pattern")
         dev = ws.device
         Dp = L.arcb_padded_dim(D)
-        if grad_logits is None and L.arcb_keep_probs_active(B, Cs, D, cfg["s"], int(cfg.get("flags", 0))):
-            scratch, scratch_bytes = None, 0  # the forward kept the probabilities: nothing is recomputed
-        else:
-            scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
+        scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
         dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
         dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
         _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),

@@ -1,7 +1,7 @@
 set -x
 cd $GRAFT_REPO_ROOT
 nvidia-smi --query-gpu=index,name --format=csv
-timeout 600 python -m pytest tests/test_gpu_sharded.py tests/test_gpu_trainer.py -x -q > gpurun_out/r2m2_pytest.log 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/r2m2_pytest.log
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r2m2_pytest.log 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/r2m2_pytest.log
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 timeout 300 $TR --nproc-per-node 2 --master-port 29611 bench.py --gpus 2 --no-cpu-baseline > gpurun_out/r2m2_bench_cfg4_n2.log 2>&1; echo "rc=$?"; tail -c 1500 gpurun_out/r2m2_bench_cfg4_n2.log
 timeout 300 $TR --nproc-per-node 2 --master-port 29612 bench.py --gpus 2 --config cfg3 --no-cpu-baseline > gpurun_out/r2m2_bench_cfg3_n2.log 2>&1; echo "rc=$?"

@@ -34,8 +34,16 @@ EXPORTED = [
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
     "arcb_profile_collect", "arcb_shard_forward_static", "arcb_shard_top3",
     "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
-    "arcb_suggest_chunk_classes",
+    "arcb_suggest_chunk_classes", "arcb_shard_forward_peer", "arcb_merge_loss_peer",
 ]
+
+MAX_PEERS = 16
+
+
+class PeerExchange(ctypes.Structure):
+    """arcb_peer_exchange of include/arcface_b200.h."""
+    _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("epoch", ctypes.c_uint),
+                ("gather_bufs", ctypes.c_void_p * MAX_PEERS), ("flags", ctypes.c_void_p * MAX_PEERS)]
 
 # per-call flags of include/arcface_b200.h (0 = library defaults)
 FWD_NORM_SEPARATE = 0x1
@@ -116,6 +124,10 @@ def _declare(lib):
     lib.arcb_shard_forward.argtypes = fwd_args + [vp, i32, vp]
     lib.arcb_shard_forward_prenorm.restype = i32
     lib.arcb_shard_forward_prenorm.argtypes = fwd_args + [vp, i32, vp]
+    lib.arcb_shard_forward_peer.restype = i32
+    lib.arcb_shard_forward_peer.argtypes = fwd_args + [vp, i32, c.POINTER(PeerExchange), vp]
+    lib.arcb_merge_loss_peer.restype = i32
+    lib.arcb_merge_loss_peer.argtypes = [vp, vp, c.c_uint, i64, i64, vp, vp, vp, vp]
     lib.arcb_ws_weight_slots.restype = i32
     lib.arcb_ws_weight_slots.argtypes = [vp, i64, i64, c.POINTER(vp), c.POINTER(vp)]
     lib.arcb_sgd_step.restype = i32

@@ -618,10 +618,30 @@ int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes) {
 static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
                               int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
                               int easy_margin, void* ws, int64_t ws_bytes, float* stats, int flags, void* stream,
-                              bool w_prenormalised) {
+                              bool w_prenormalised, const arcb_peer_exchange* px = nullptr) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (!stats) return fail(ARCB_ERR_INVALID, "null stats pointer");
   flags = effective_flags(flags);
+  PeerTable peers;
+  if (px) {
+    if (px->world < 1 || px->world > ARCB_MAX_PEERS || px->rank < 0 || px->rank >= px->world)
+      return fail(ARCB_ERR_INVALID, "peer exchange: bad rank / world (%d / %d)", px->rank, px->world);
+    for (int p = 0; p < px->world; ++p) {
+      if (!px->gather_bufs[p] || !px->flags[p]) return fail(ARCB_ERR_INVALID, "peer exchange: null pointer for rank %d", p);
+      peers.buf[p] = static_cast<float*>(px->gather_bufs[p]);
+      peers.flag[p] = static_cast<unsigned int*>(px->flags[p]);
+    }
+  }
+  // last merge level: into `stats` only, or (px) also into every rank's gather buffer + flag
+  auto final_merge = [&](const float2* part, int n_part, const Workspace& Wk) -> int {
+    LaunchScope ls(ARCB_K_MERGE, st, 1);
+    if (px)
+      merge_publish_kernel<<<1, 1024, 0, st>>>(part, n_part, Wk.Bp, Wk.zt, (int)B, stats, peers, px->rank, px->world, px->epoch);
+    else
+      merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(part, n_part, Wk.Bp, Wk.zt, (int)B, stats);
+    ARCB_CUDA(cudaGetLastError());
+    return ARCB_OK;
+  };
   if ((flags & ARCB_FWD_NORM_SEPARATE) && (flags & ARCB_FWD_NORM_FUSED))
     return fail(ARCB_ERR_INVALID, "ARCB_FWD_NORM_SEPARATE and ARCB_FWD_NORM_FUSED exclude each other");
   const bool pair_gemm = (flags & ARCB_FWD_PAIR) != 0;
@@ -672,11 +692,7 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
       e = launch_fwd_resident<false>(a, b, B, Cs, W.Dp, rp, NormArgs{}, st);
     }
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
-    const int n_part = 2 * resident_lanes(B);
-    LaunchScope ls(ARCB_K_MERGE, st, 1);
-    merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(W.part, n_part, W.Bp, W.zt, (int)B, stats);
-    ARCB_CUDA(cudaGetLastError());
-    return ARCB_OK;
+    return final_merge(W.part, 2 * resident_lanes(B), W);
   }
   if (fuse) {
     NormArgs na;
@@ -706,15 +722,14 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   const int blocks = static_cast<int>((B + 255) / 256);
   const int n_part = 2 * tiles_n;
   if (n_part > 4 * kMergeSlices) {  // two levels: 64 slices in parallel, then the 64 results + the shard record
-    LaunchScope ls(ARCB_K_MERGE, st, 2);
-    merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, n_part, W.Bp, (int)B, W.rec2, W.Bp);
-    merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(W.rec2, kMergeSlices, W.Bp, W.zt, (int)B, stats);
-  } else {
-    LaunchScope ls(ARCB_K_MERGE, st, 1);
-    merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(W.part, n_part, W.Bp, W.zt, (int)B, stats);
+    {
+      LaunchScope ls(ARCB_K_MERGE, st, 1);
+      merge_stats_kernel<<<dim3(blocks, kMergeSlices), 256, 0, st>>>(W.part, n_part, W.Bp, (int)B, W.rec2, W.Bp);
+      ARCB_CUDA(cudaGetLastError());
+    }
+    return final_merge(W.rec2, kMergeSlices, W);
   }
-  ARCB_CUDA(cudaGetLastError());
-  return ARCB_OK;
+  return final_merge(W.part, n_part, W);
 }
 
 int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
@@ -722,6 +737,25 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
                        int64_t ws_bytes, float* stats, int flags, void* stream) {
   return shard_forward_impl(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, stats,
                             flags, stream, false);
+}
+
+int arcb_shard_forward_peer(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                            int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                            int64_t ws_bytes, float* stats, int flags, const arcb_peer_exchange* px, void* stream) {
+  if (!px) return fail(ARCB_ERR_INVALID, "null peer exchange descriptor");
+  return shard_forward_impl(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, stats,
+                            flags, stream, false, px);
+}
+
+int arcb_merge_loss_peer(const float* gathered, const void* own_flags, unsigned int epoch, int64_t P, int64_t B, float* lse,
+                         float* target_logit, float* loss, void* stream) {
+  if (!gathered || !own_flags || !lse || !loss) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (P <= 0 || P > ARCB_MAX_PEERS || B <= 0) return fail(ARCB_ERR_INVALID, "bad sizes for merge_loss_peer");
+  LaunchScope ls(ARCB_K_LOSS, static_cast<cudaStream_t>(stream));
+  loss_wait_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(gathered, static_cast<const unsigned int*>(own_flags),
+                                                                     epoch, (int)P, (int)B, lse, target_logit, loss);
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
 }
 
 int arcb_shard_forward_prenorm(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,

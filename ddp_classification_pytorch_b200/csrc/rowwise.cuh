@@ -300,6 +300,91 @@ loss_kernel(const float* __restrict__ stats, int P, int B, float* __restrict__ l
 }
 
 // ---------------------------------------------------------------------------------------------
+// Class-sharded forward exchange fused with its producer (stage 2).  Instead of "merge kernel -> NCCL
+// all_gather -> loss kernel", the merge kernel itself stores this rank's [B, 4] record into slot `rank` of EVERY rank's
+// gather buffer (plain stores through NVLink peer mappings: symmetric memory) and then raises flag[rank] on every rank to
+// the step's epoch (release, system scope); the loss kernel of each rank waits until all P flags have reached the epoch
+// (acquire, system scope) and reads its local buffer.  No collective launch sits on the forward's critical path.
+// Flags only grow (epoch = step number), the gather buffer is double buffered by the caller (slot = epoch & 1): a rank
+// can run at most one step ahead of its peers, because its loss kernel needs every peer's flag of the same step.
+// ---------------------------------------------------------------------------------------------
+struct PeerTable {
+  float* buf[16];          // [p] base of rank p's gather buffer slot for this step: [P, B, 4] fp32
+  unsigned int* flag[16];  // [p] base of rank p's flag array: [P] uint32
+};
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Last merge level + publication.  One block: every thread merges rows tid, tid + blockDim, ...; the record goes to the
+// local `stats` (kept for aux / tests) and to all P ranks.
+__global__ void __launch_bounds__(1024)
+merge_publish_kernel(const float2* __restrict__ part, int n, int64_t ldp, const float* __restrict__ zt, int B,
+                     float* __restrict__ stats, const PeerTable peers, int rank, int P, unsigned int epoch) {
+  for (int row = threadIdx.x; row < B; row += blockDim.x) {
+    const float2 r = merge_partials(part, 0, n, ldp, row);
+    const float4 rec = make_float4(r.x, r.y, zt[row], 0.f);
+    *reinterpret_cast<float4*>(stats + static_cast<int64_t>(row) * 4) = rec;
+    for (int p = 0; p < P; ++p)
+      *reinterpret_cast<float4*>(peers.buf[p] + (static_cast<int64_t>(rank) * B + row) * 4) = rec;
+  }
+  __threadfence_system();  // every thread's peer stores are performed system-wide ...
+  __syncthreads();         // ... before anybody raises a flag
+  if (threadIdx.x < P) st_release_sys_u32(peers.flag[threadIdx.x] + rank, epoch);
+}
+
+// loss_kernel that first waits for the P records of this step (see above).  `flags` is this rank's own flag array.
+__global__ void __launch_bounds__(1024)
+loss_wait_kernel(const float* __restrict__ stats, const unsigned int* __restrict__ flags, unsigned int epoch, int P, int B,
+                 float* __restrict__ lse, float* __restrict__ zt_out, float* __restrict__ loss) {
+  __shared__ double red[32];
+  if (threadIdx.x < P) {
+    const long long t0 = clock64();
+    unsigned int spins = 0;
+    // flags only grow; a peer that is a step ahead has a larger value (its data for THIS step sits in the other slot)
+    while (static_cast<int>(ld_acquire_sys_u32(flags + threadIdx.x) - epoch) < 0) {
+      __nanosleep(200);
+#if ARCB_WATCHDOG_CYCLES > 0
+      if ((++spins & 0xffu) == 0 && clock64() - t0 > ARCB_WATCHDOG_CYCLES) watchdog_abort(0x9e0u + threadIdx.x, epoch);
+#endif
+    }
+  }
+  __syncthreads();
+  double acc = 0.0;
+  for (int row = threadIdx.x; row < B; row += blockDim.x) {
+    float m = -INFINITY, zt = -INFINITY;
+    for (int p = 0; p < P; ++p) {
+      const float4 r = __ldcv(reinterpret_cast<const float4*>(stats + (static_cast<int64_t>(p) * B + row) * 4));
+      m = fmaxf(m, r.x);
+      zt = fmaxf(zt, r.z);
+    }
+    float l = 0.f;
+    for (int p = 0; p < P; ++p) {
+      const float4 r = __ldcv(reinterpret_cast<const float4*>(stats + (static_cast<int64_t>(p) * B + row) * 4));
+      l += r.y * exp2f(r.x - m);
+    }
+    const float v = (m + log2f(l)) * kLn2;
+    lse[row] = v;
+    if (zt_out) zt_out[row] = zt;
+    acc += static_cast<double>(v) - static_cast<double>(zt);
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double v = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) *loss = static_cast<float>(v / B);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Exact top-3 / argmax of the scaled logits (consumers at arc_main.py:338-345, :377-388) without
 // the logits: the forward GEMM left, per row, the bf16-accurate maximum of every 128-class block
 // (`part`).  |cos_bf16 - cos_fp32| <= 2^-8 (two operand roundings, |x_hat||w_hat| = 1), so every

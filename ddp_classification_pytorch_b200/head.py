@@ -122,6 +122,45 @@ class _Lease:
     __del__ = release
 
 
+class _PeerGather:
+    """Symmetric-memory buffers for the forward's statistics exchange (stage 2).
+
+    Every rank owns ``[2, P, B, 4]`` fp32 (two step slots) plus ``P`` flag words, mapped into every other rank's
+    address space (``torch.distributed._symmetric_memory``, NVLink peer access).  The merge kernel of each rank
+    stores its ``[B, 4]`` record into all P buffers and raises its flag there; the loss kernel waits for the P flags
+    of its own buffer (``arcb_shard_forward_peer`` / ``arcb_merge_loss_peer``).  torch only allocates and maps the
+    memory; the exchange itself is done by this package's kernels."""
+
+    def __init__(self, group, B, device):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.P = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.P > _lib.MAX_PEERS:
+            raise RuntimeError(f"peer exchange supports up to {_lib.MAX_PEERS} ranks")
+        self.B = B
+        self.slot_words = self.P * B * 4
+        self.buf = symm.empty(2 * self.slot_words + 64, dtype=torch.float32, device=device)
+        self.buf.zero_()  # flags start at 0; epochs count from 1
+        torch.cuda.synchronize(device)
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.hdl.barrier()  # every rank's flags are zero before anybody publishes
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.epoch = 0
+
+    def next_exchange(self):
+        """-> (descriptor for this step, local gathered view [P, B, 4], local flags ptr)."""
+        self.epoch += 1
+        slot = self.epoch & 1
+        px = _lib.PeerExchange()
+        px.rank, px.world, px.epoch = self.rank, self.P, self.epoch & 0xFFFFFFFF
+        for p in range(self.P):
+            px.gather_bufs[p] = self.ptrs[p] + slot * self.slot_words * 4
+            px.flags[p] = self.ptrs[p] + 2 * self.slot_words * 4
+        gathered = self.buf[slot * self.slot_words:(slot + 1) * self.slot_words].view(self.P * self.B, 4)
+        return px, gathered, self.ptrs[self.rank] + 2 * self.slot_words * 4
+
+
 class CudaEngine:
     """Every method is one call into libarcface_b200.so (include/arcface_b200.h)."""
 
@@ -157,18 +196,26 @@ class CudaEngine:
         cache = cfg.get("wcache")
         tag = cfg.get("w_tag")  # (data_ptr, version) of the parameter itself
         fn, gen = L.arcb_shard_forward, 0
+        px = cfg.get("peer_px")  # class-sharded: the merge kernel publishes the record to every rank itself
         if cache is not None and cache.busy == 0 and tag is not None and tag[0] == wc.data_ptr():
             ws, ws_bytes = cache.workspace(B, Cs, D, xc.device, cfg.get("flags", 0))
-            if cache.valid == tag:  # w_hat / inv_norm in the workspace belong to exactly this weight
+            if cache.valid == tag and px is None:  # w_hat / inv_norm in the workspace belong to exactly this weight
                 fn = L.arcb_shard_forward_prenorm
             cache.valid = None  # until the call below has been enqueued
         else:
             cache = None
             ws, ws_bytes = self._alloc_ws(B, Cs, D, xc.device, cfg.get("flags", 0))
-        _lib.check(fn(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"], cfg["m"],
-                      int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats),
-                      int(cfg.get("flags", 0)) | (_lib.FWD_BLOCK_MAXIMA if cfg.get("want_top3") else 0), _stream()),
-                   "arcb_shard_forward")
+        call_flags = int(cfg.get("flags", 0)) | (_lib.FWD_BLOCK_MAXIMA if cfg.get("want_top3") else 0)
+        if px is not None:
+            import ctypes
+            _lib.check(L.arcb_shard_forward_peer(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"],
+                                                 cfg["s"], cfg["m"], int(cfg["easy_margin"]), _ptr(ws), ws_bytes,
+                                                 _ptr(stats), call_flags, ctypes.byref(px), _stream()),
+                       "arcb_shard_forward_peer")
+        else:
+            _lib.check(fn(_ptr(xc), D, _ptr(wc), D, _ptr(lab), B, Cs, D, cfg["class_offset"], cfg["s"], cfg["m"],
+                          int(cfg["easy_margin"]), _ptr(ws), ws_bytes, _ptr(stats), call_flags, _stream()),
+                       "arcb_shard_forward")
         if cache is not None:
             cache.valid = tag
             cache.generation += 1
@@ -205,6 +252,17 @@ class CudaEngine:
         loss = torch.empty((), dtype=torch.float32, device=dev)
         _lib.check(L.arcb_merge_loss(_ptr(gathered), P, B, _ptr(lse), _ptr(zt), _ptr(loss), _stream()),
                    "arcb_merge_loss")
+        return lse, zt, loss
+
+    def merge_loss_peer(self, gathered, flags_ptr, epoch, P, B):
+        """Like merge_loss, but the kernel first waits until all P ranks have published this step's record."""
+        L = _lib.lib()
+        dev = gathered.device
+        lse = torch.empty(B, dtype=torch.float32, device=dev)
+        zt = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        _lib.check(L.arcb_merge_loss_peer(_ptr(gathered), flags_ptr, epoch, P, B, _ptr(lse), _ptr(zt), _ptr(loss), _stream()),
+                   "arcb_merge_loss_peer")
         return lse, zt, loss
 
     def shard_backward(self, state, cfg, lse=None, zt=None, grad_loss=None, grad_logits=None):
@@ -271,16 +329,23 @@ class _FusedLossFn(torch.autograd.Function):
         B = xc.shape[0]
         if cfg.get("wcache") is not None:
             cfg = dict(cfg, w_tag=(w.data_ptr(), w._version))
+        peer = cfg["peer_factory"](B, xc.device) if (P > 1 and cfg.get("peer_factory") is not None) else None
+        if peer is not None:  # the exchange is done by the merge / loss kernels themselves over NVLink peer memory
+            px, gathered, flags_ptr = peer.next_exchange()
+            cfg = dict(cfg, peer_px=px)
         stats, state = eng.shard_forward(xc, wc, lab, cfg)
         lease = None
         if len(state) > 5 and state[5] is not None and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]):
             lease = _Lease(state[5])  # the workspace now belongs to this graph until its backward has run
-        if P > 1:  # the only forward exchange: one [B, 4] record per rank
-            gathered = torch.empty(P * B, stats.shape[1], dtype=stats.dtype, device=stats.device)  # = [P, B, 4]
-            torch.distributed.all_gather_into_tensor(gathered, stats, group=group)
+        if peer is not None:
+            lse, zt, loss = eng.merge_loss_peer(gathered, flags_ptr, px.epoch, P, B)
         else:
-            gathered = stats
-        lse, zt, loss = eng.merge_loss(gathered, P, B)
+            if P > 1:  # the only forward exchange: one [B, 4] record per rank
+                gathered = torch.empty(P * B, stats.shape[1], dtype=stats.dtype, device=stats.device)  # = [P, B, 4]
+                torch.distributed.all_gather_into_tensor(gathered, stats, group=group)
+            else:
+                gathered = stats
+            lse, zt, loss = eng.merge_loss(gathered, P, B)
         ctx.save_for_backward(xc)
         ctx.held = (eng, state, lse, zt, cfg, w.dtype, x.dtype)
         ctx.lease = lease
@@ -371,13 +436,17 @@ class ArcMarginProduct(nn.Module):
         process_group (keyword-only): shard the classes over this ``torch.distributed`` group;
             ``weight`` then holds only this rank's rows and ``forward`` returns only its columns.
         cache_normalized_weight (keyword-only): see :meth:`cache_normalized_weight`.
+        peer_exchange (keyword-only): class-sharded mode only.  ``True`` / ``None`` (default: try): the ``[B, 4]``
+            statistics are exchanged by the merge / loss kernels themselves through symmetric (NVLink peer) memory
+            instead of an NCCL ``all_gather``; ``None`` falls back to NCCL when symmetric memory cannot be set up,
+            ``False`` always uses NCCL.  Same results either way.
         kernel_flags (keyword-only): ``ARCB_*`` bits of include/arcface_b200.h passed with every call of THIS head
             (kernel schedule selection for A/B runs and tests; 0 = library defaults).  Per head, not per process.
     """
 
     def __init__(self, in_features, out_features, s=30.0, m=0.50, easy_margin=False, *, process_group=None,
                  chunk_classes: Optional[int] = None, cache_normalized_weight: bool = False, kernel_flags: int = 0,
-                 _engine=None):
+                 peer_exchange: Optional[bool] = None, _engine=None):
         super().__init__()
         self.in_features = in_features
         self.out_features = out_features
@@ -406,6 +475,9 @@ class ArcMarginProduct(nn.Module):
         self.mm = math.sin(math.pi - m) * m
         self.chunk_classes = chunk_classes or DEFAULT_CHUNK_CLASSES  # 0: chosen per call by the library
         self.kernel_flags = int(kernel_flags)
+        self.peer_exchange = peer_exchange
+        self._peer = {}        # batch size -> _PeerGather
+        self._peer_off = peer_exchange is False or os.environ.get("ARCB_PEER_EXCHANGE", "1") == "0"
         self.aux = {}
         self._engine = _engine if _engine is not None else CudaEngine()
         self._wcache = _WeightCache() if cache_normalized_weight else None
@@ -433,7 +505,31 @@ class ArcMarginProduct(nn.Module):
             "class_offset": int(self.class_lo), "group": self.process_group,
             "chunk_classes": int(self.chunk_classes), "aux_out": self.aux, "engine": self._engine,
             "want_top3": False, "wcache": self._wcache, "flags": int(self.kernel_flags), "gather_batch": False,
+            "peer_factory": self._peer_gather if (self.world_size > 1 and not self._peer_off
+                                                  and isinstance(self._engine, CudaEngine)) else None,
         }
+
+    def _peer_gather(self, B, device):
+        """The symmetric-memory exchange buffers for batch size B (set up collectively on first use), or None."""
+        if self._peer_off:
+            return None
+        pg = self._peer.get(B)
+        if pg is None:
+            ok = torch.ones(1, device=device)
+            try:
+                pg = _PeerGather(self.process_group, B, device)
+            except Exception as ex:  # no peer access / symmetric memory on this system
+                if self.peer_exchange is True:
+                    raise
+                pg, ok[0] = None, 0.0
+                self._peer_error = f"{type(ex).__name__}: {ex}"
+            # every rank must take the same path: one rank without symmetric memory switches all of them to NCCL
+            torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN, group=self.process_group)
+            if ok.item() < 0.5:
+                self._peer_off, pg = True, None
+            else:
+                self._peer[B] = pg
+        return pg
 
     def forward(self, input, label, fused_loss=False, want_top3=False, gather_batch=False):
         """Scaled logits ``[B, classes of this rank]`` exactly as arc_main.py:157-176 returns them.

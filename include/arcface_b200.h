@@ -110,6 +110,30 @@ int arcb_shard_forward(const float* x, int64_t ldx, const float* w, int64_t ldw,
                        int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
                        int64_t ws_bytes, float* stats, int flags, void* stream);
 
+/* ---- fused forward whose shard record is exchanged by the kernels themselves (class-sharded mode) ----
+ * Replaces "arcb_shard_forward -> all_gather of stats -> arcb_merge_loss" (the DDP all-reduce of arc_main.py:243 is what
+ * class sharding removed; this is the exchange that took its place).  The kernel that merges the shard's
+ * statistics stores its [B, 4] record straight into slot `rank` of every rank's gather buffer -- `gather_bufs[p]` is rank
+ * p's buffer [world, B, 4] fp32 as mapped into THIS process (peer / symmetric memory; plain stores, no TMA) -- and then
+ * raises `flags[p][rank]` to `epoch`; arcb_merge_loss_peer on each rank waits until all `world` flags of its own array have
+ * reached the epoch and reduces its local buffer.  No collective launch, no host synchronisation.
+ *   - epoch must grow by one per call and start above the flags' initial value (zero them once, then use 1, 2, ...);
+ *   - alternate between TWO gather buffers (epoch & 1): a rank may be one step ahead of its peers, never two;
+ *   - world <= ARCB_MAX_PEERS; all pointers must stay valid until every rank has consumed the step. */
+#define ARCB_MAX_PEERS 16
+typedef struct arcb_peer_exchange {
+  int rank, world;
+  unsigned int epoch;
+  void* gather_bufs[ARCB_MAX_PEERS]; /* [p]: rank p's [world, B, 4] fp32 buffer of this step */
+  void* flags[ARCB_MAX_PEERS];       /* [p]: rank p's uint32 flags [world] */
+} arcb_peer_exchange;
+int arcb_shard_forward_peer(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
+                            int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy_margin, void* ws,
+                            int64_t ws_bytes, float* stats, int flags, const arcb_peer_exchange* px, void* stream);
+/* gathered: THIS rank's gather buffer [world, B, 4]; own_flags: THIS rank's flags [world]. */
+int arcb_merge_loss_peer(const float* gathered, const void* own_flags, unsigned int epoch, int64_t P, int64_t B, float* lse,
+                         float* target_logit, float* loss, void* stream);
+
 /* ---- fused forward without a caller workspace (no counterpart in the reference) ----
  * For hosts that are not allowed to obtain device memory when the call happens: a plugin living inside another
  * runtime whose allocator owns all of HBM, a serving loop that has frozen its memory plan, or a foreign-language

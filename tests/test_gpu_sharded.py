@@ -86,6 +86,21 @@ def _nccl_worker(rank, world, port, out):
               and torch.equal(head.full_weight().cpu(), w)
               and clear.mean() > 0.9
               and np.array_equal(head.aux["top3"].cpu().numpy()[clear], ref["top3"][clear]))
+        # the statistics exchange done by the kernels over symmetric (NVLink peer) memory must have been used, and
+        # must give exactly what the NCCL all_gather path gives (same records, same merge arithmetic)
+        peer_used = bool(head._peer) and not head._peer_off
+        nccl_head = ArcMarginProduct(D, C, s=30.0, m=0.5, easy_margin=True, process_group=dist.group.WORLD,
+                                     peer_exchange=False).cuda()
+        with torch.no_grad():
+            nccl_head.weight.copy_(w[lo:hi])
+        for _ in range(3):  # several steps: both slots of the double-buffered gather buffer, growing epochs
+            xn = x.cuda().requires_grad_(True)
+            ln = nccl_head.forward_loss(xn, y.cuda())
+            xp = x.cuda().requires_grad_(True)
+            lp = head.forward_loss(xp, y.cuda())
+            ok = ok and abs(lp.item() - ln.item()) <= 1e-6 * abs(ln.item()) and torch.equal(head.aux["lse"], nccl_head.aux["lse"])
+        out[f"peer{rank}"] = peer_used
+        head.weight.grad = None
         # data-parallel rows in, reduce_scatter of dX out: this rank's rows only
         b = B // world
         rows = slice(rank * b, (rank + 1) * b)
@@ -137,3 +152,7 @@ def test_nccl_ranks_equal_unsharded(world):
             p.join(300)
             assert p.exitcode == 0
         assert all(out.get(r) is True for r in range(world)), dict(out)
+        # symmetric memory is expected on an NVLink box; if torch could not set it up the NCCL path was tested instead
+        if not all(out.get(f"peer{r}") for r in range(world)):
+            import warnings
+            warnings.warn("peer-memory statistics exchange was not available: NCCL all_gather path used")

@@ -34,7 +34,7 @@ EXPORTED = [
     "arcb_merge_loss", "arcb_shard_backward", "arcb_padded_dim", "arcb_launch_count", "arcb_profile_enable",
     "arcb_profile_collect", "arcb_shard_forward_static", "arcb_shard_top3",
     "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
-    "arcb_suggest_chunk_classes", "arcb_shard_forward_peer", "arcb_merge_loss_peer",
+    "arcb_suggest_chunk_classes", "arcb_shard_forward_peer", "arcb_merge_loss_peer", "arcb_dx_peer_reduce",
 ]
 
 MAX_PEERS = 16
@@ -44,6 +44,14 @@ class PeerExchange(ctypes.Structure):
     """arcb_peer_exchange of include/arcface_b200.h."""
     _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("epoch", ctypes.c_uint),
                 ("gather_bufs", ctypes.c_void_p * MAX_PEERS), ("flags", ctypes.c_void_p * MAX_PEERS)]
+
+
+class PeerReduce(ctypes.Structure):
+    """arcb_peer_reduce of include/arcface_b200.h."""
+    _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("epoch", ctypes.c_uint), ("own_only", ctypes.c_int),
+                ("partials", ctypes.c_void_p * MAX_PEERS), ("slices", ctypes.c_void_p * MAX_PEERS),
+                ("ready", ctypes.c_void_p * MAX_PEERS), ("done", ctypes.c_void_p * MAX_PEERS),
+                ("counter", ctypes.c_void_p)]
 
 # per-call flags of include/arcface_b200.h (0 = library defaults)
 FWD_NORM_SEPARATE = 0x1
@@ -128,6 +136,8 @@ def _declare(lib):
     lib.arcb_shard_forward_peer.argtypes = fwd_args + [vp, i32, c.POINTER(PeerExchange), vp]
     lib.arcb_merge_loss_peer.restype = i32
     lib.arcb_merge_loss_peer.argtypes = [vp, vp, c.c_uint, i64, i64, vp, vp, vp, vp]
+    lib.arcb_dx_peer_reduce.restype = i32
+    lib.arcb_dx_peer_reduce.argtypes = [vp, i64, i64, i64, c.POINTER(PeerReduce), vp, i64, vp]
     lib.arcb_ws_weight_slots.restype = i32
     lib.arcb_ws_weight_slots.argtypes = [vp, i64, i64, c.POINTER(vp), c.POINTER(vp)]
     lib.arcb_sgd_step.restype = i32

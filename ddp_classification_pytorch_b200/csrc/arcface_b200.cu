@@ -758,6 +758,40 @@ int arcb_merge_loss_peer(const float* gathered, const void* own_flags, unsigned 
   return ARCB_OK;
 }
 
+int arcb_dx_peer_reduce(const float* x, int64_t ldx, int64_t B, int64_t D, const arcb_peer_reduce* pr, float* dx,
+                        int64_t ldo, void* stream) {
+  if (!x || !pr || !dx) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  if (B <= 0 || D <= 0 || D > 2048 || (D % 4) || ldx < D || ldo < D || (ldx % 4) || (ldo % 4) ||
+      (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(dx) & 15))
+    return fail(ARCB_ERR_INVALID, "arcb_dx_peer_reduce needs D %% 4 == 0, D <= 2048 and 16-byte aligned rows");
+  if (pr->world < 1 || pr->world > ARCB_MAX_PEERS || pr->rank < 0 || pr->rank >= pr->world || !pr->counter)
+    return fail(ARCB_ERR_INVALID, "peer reduce: bad rank / world (%d / %d)", pr->rank, pr->world);
+  PeerReduceArgs a;
+  for (int p = 0; p < pr->world; ++p) {
+    if (!pr->partials[p] || !pr->slices[p] || !pr->ready[p] || !pr->done[p])
+      return fail(ARCB_ERR_INVALID, "peer reduce: null pointer for rank %d", p);
+    a.partial[p] = static_cast<const float*>(pr->partials[p]);
+    a.slice[p] = static_cast<const float*>(pr->slices[p]);
+    a.ready[p] = static_cast<unsigned int*>(pr->ready[p]);
+    a.done[p] = static_cast<unsigned int*>(pr->done[p]);
+  }
+  a.my_slice = static_cast<float*>(pr->slices[pr->rank]);
+  a.counter = static_cast<unsigned int*>(pr->counter);
+  a.rank = pr->rank; a.P = pr->world; a.epoch = pr->epoch;
+  a.B = (int)B; a.D = (int)D; a.Dp = (int)round_up(D, 64);
+  a.rows_per = (int)((B + pr->world - 1) / pr->world);
+  a.own_only = pr->own_only ? 1 : 0;
+  // every block waits for other ranks: the whole grid must be resident -> at most two blocks per SM
+  int grid = a.rows_per;
+  if (grid > 2 * device_sm_count()) grid = 2 * device_sm_count();
+  if (grid < 1) grid = 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  LaunchScope ls(ARCB_K_L2NORM_BWD, st);
+  dx_peer_reduce_kernel<<<grid, 256, 0, st>>>(x, ldx, dx, ldo, a);
+  ARCB_CUDA(cudaGetLastError());
+  return ARCB_OK;
+}
+
 int arcb_shard_forward_prenorm(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels,
                                int64_t B, int64_t Cs, int64_t D, int64_t class_offset, float s, float m,
                                int easy_margin, void* ws, int64_t ws_bytes, float* stats, int flags, void* stream) {

@@ -385,6 +385,137 @@ loss_wait_kernel(const float* __restrict__ stats, const unsigned int* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------
+// Class-sharded backward exchange fused with its consumer (stage 2): the sum of the shards' dX_hat partials
+// and F.normalize's backward for the embeddings in ONE kernel over peer memory, instead of "NCCL all_reduce ->
+// l2norm_rows_bwd_kernel".  Every rank's partial [B, Dp] lives in symmetric memory.  Rank r owns the rows
+// [r * rows_per, (r + 1) * rows_per) of the batch:
+//   announce   raise ready[rank] on every rank (my partial is complete: the backward kernel ran before this one)
+//   reduce     wait for all ready flags; for my rows: sum the P partials (peer loads over NVLink), apply
+//              dx = (dxh - xh (xh . dxh)) / ||x|| and store the finished rows in my slice buffer (symmetric, local)
+//   publish    when all my blocks are done: raise done[rank] on every rank
+//   collect    wait for all done flags; copy every rank's slice into the local output dx [B, D]  (all-gather by pull)
+// own_only (data-parallel trainer, reduce_scatter semantics): the reduce step writes my rows straight to `dx` and the
+// kernel ends there.  Flags only grow (epoch = step number); partials and slices are double buffered by the caller.
+// ---------------------------------------------------------------------------------------------
+struct PeerReduceArgs {
+  const float* partial[16];   // [p] rank p's dX_hat partial of this step, [B, Dp] fp32
+  const float* slice[16];     // [p] rank p's finished rows of this step, [rows_per, D] fp32
+  unsigned int* ready[16];    // [p] rank p's ready flags [P]
+  unsigned int* done[16];     // [p] rank p's done flags [P]
+  float* my_slice;            // = slice[rank], writable
+  unsigned int* counter;      // local, zero between launches: blocks that have finished their rows
+  int rank, P;
+  unsigned int epoch;
+  int B, D, Dp, rows_per;     // rows_per = ceil(B / P)
+  int own_only;
+};
+
+__device__ __forceinline__ void wait_flags_sys(const unsigned int* flags, int P, unsigned int epoch, unsigned int tag) {
+  if (threadIdx.x < static_cast<unsigned>(P)) {
+    const long long t0 = clock64();
+    unsigned int spins = 0;
+    while (static_cast<int>(ld_acquire_sys_u32(flags + threadIdx.x) - epoch) < 0) {
+      __nanosleep(100);
+#if ARCB_WATCHDOG_CYCLES > 0
+      if ((++spins & 0xffu) == 0 && clock64() - t0 > ARCB_WATCHDOG_CYCLES) watchdog_abort(tag + threadIdx.x, epoch);
+#endif
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+dx_peer_reduce_kernel(const float* __restrict__ x, int64_t ldx, float* __restrict__ dx, int64_t ldo, const PeerReduceArgs a) {
+  const int lane = threadIdx.x & 31;
+  // announce: the backward kernel that wrote my partial completed before this launch; make it visible system-wide
+  if (blockIdx.x == 0 && threadIdx.x < a.P) {
+    __threadfence_system();
+    st_release_sys_u32(a.ready[threadIdx.x] + a.rank, a.epoch);
+  }
+  wait_flags_sys(a.ready[a.rank], a.P, a.epoch, 0x9f00u);
+  // reduce + normalise-backward for my rows: one row per block at a time, one float4 (x P peer loads, all in flight at
+  // once: a single NVLink round trip per row) per thread; D <= 2048, D % 4 == 0 (checked by the launcher)
+  __shared__ float red_ss[8], red_dot[8];
+  const int r0 = a.rank * a.rows_per;
+  const int r1 = min(a.B, r0 + a.rows_per);
+  const int n4 = a.D >> 2;
+  for (int row = r0 + blockIdx.x; row < r1; row += gridDim.x) {
+    const float4* xr = reinterpret_cast<const float4*>(x + static_cast<int64_t>(row) * ldx);
+    float4* out = reinterpret_cast<float4*>(a.own_only ? dx + static_cast<int64_t>(row - r0) * ldo
+                                                        : a.my_slice + static_cast<int64_t>(row - r0) * a.D);
+    float4 sum[2], xv[2];
+    float ss = 0.f, dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int idx = threadIdx.x + k * 256;
+      sum[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      xv[k] = sum[k];
+      if (idx < n4) {
+        for (int p = 0; p < a.P; ++p) {
+          const float4 v = __ldcv(reinterpret_cast<const float4*>(a.partial[p] + static_cast<int64_t>(row) * a.Dp) + idx);
+          sum[k].x += v.x; sum[k].y += v.y; sum[k].z += v.z; sum[k].w += v.w;
+        }
+        xv[k] = xr[idx];
+        ss += xv[k].x * xv[k].x + xv[k].y * xv[k].y + xv[k].z * xv[k].z + xv[k].w * xv[k].w;
+        dot += xv[k].x * sum[k].x + xv[k].y * sum[k].y + xv[k].z * sum[k].z + xv[k].w * sum[k].w;
+      }
+    }
+    ss = warp_sum(ss);
+    dot = warp_sum(dot);
+    __syncthreads();  // the previous row's readers of red_* are done
+    if (lane == 0) {
+      red_ss[threadIdx.x >> 5] = ss;
+      red_dot[threadIdx.x >> 5] = dot;
+    }
+    __syncthreads();
+    ss = 0.f;
+    dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      ss += red_ss[i];
+      dot += red_dot[i];
+    }
+    const float nrm = sqrtf(ss);
+    const bool ok = nrm > kNormEps;  // same arithmetic as l2norm_rows_bwd_kernel
+    const float inv = ok ? 1.f / nrm : 1.f / kNormEps;
+    const float proj = ok ? dot * inv * inv : 0.f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int idx = threadIdx.x + k * 256;
+      if (idx < n4)
+        out[idx] = make_float4(inv * (sum[k].x - xv[k].x * proj), inv * (sum[k].y - xv[k].y * proj),
+                               inv * (sum[k].z - xv[k].z * proj), inv * (sum[k].w - xv[k].w * proj));
+    }
+  }
+  if (a.own_only) return;
+  // publish: all of this rank's blocks have finished their rows -> done[rank] on every rank
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(a.counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *a.counter = 0u;  // for the next launch (stream order: it starts after this kernel has ended)
+      __threadfence_system();
+      for (int p = 0; p < a.P; ++p) st_release_sys_u32(a.done[p] + a.rank, a.epoch);
+    }
+  }
+  // collect: every rank's finished rows -> local dx
+  wait_flags_sys(a.done[a.rank], a.P, a.epoch, 0x9f40u);
+  for (int p = 0; p < a.P; ++p) {
+    const int p0 = p * a.rows_per;
+    const int rows = min(a.B, p0 + a.rows_per) - p0;
+    if (rows <= 0) continue;
+    const float4* src = reinterpret_cast<const float4*>(a.slice[p]);
+    const int total = rows * n4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+      const int r = i / n4, c = i - r * n4;
+      const float4 v = __ldcv(src + i);
+      *reinterpret_cast<float4*>(dx + static_cast<int64_t>(p0 + r) * ldo + c * 4) = v;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Exact top-3 / argmax of the scaled logits (consumers at arc_main.py:338-345, :377-388) without
 // the logits: the forward GEMM left, per row, the bf16-accurate maximum of every 128-class block
 // (`part`).  |cos_bf16 - cos_fp32| <= 2^-8 (two operand roundings, |x_hat||w_hat| = 1), so every

@@ -161,6 +161,49 @@ class _PeerGather:
         return px, gathered, self.ptrs[self.rank] + 2 * self.slot_words * 4
 
 
+class _PeerReduce:
+    """Symmetric-memory buffers for the backward's dX exchange (stage 2): every rank's ``[B, Dp]`` partial
+    of dX_hat (two step slots), its ``[ceil(B / P), D]`` slice of finished rows (two slots), ``P`` ready + ``P`` done flags
+    and a block counter.  ``arcb_dx_peer_reduce`` sums the partials over NVLink peer loads, applies F.normalize's backward
+    and gathers the rows -- one kernel instead of an NCCL all_reduce plus a row kernel."""
+
+    def __init__(self, group, B, D, Dp, device):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.P = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.P > _lib.MAX_PEERS:
+            raise RuntimeError(f"peer exchange supports up to {_lib.MAX_PEERS} ranks")
+        self.B, self.D, self.Dp = B, D, Dp
+        self.rows_per = (B + self.P - 1) // self.P
+        self.part_words = B * Dp
+        self.slice_words = self.rows_per * D
+        self.flag_off = 2 * self.part_words + 2 * self.slice_words  # then: ready [P], done [P], counter (64-word fields)
+        self.buf = symm.empty(self.flag_off + 192, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.hdl.barrier()
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.epoch = 0
+
+    def next_exchange(self, own_only):
+        """-> (descriptor of this step, this rank's partial buffer [B, Dp] to hand to the backward kernel)."""
+        self.epoch += 1
+        slot = self.epoch & 1
+        pr = _lib.PeerReduce()
+        pr.rank, pr.world, pr.epoch, pr.own_only = self.rank, self.P, self.epoch & 0xFFFFFFFF, int(bool(own_only))
+        for p in range(self.P):
+            base = self.ptrs[p]
+            pr.partials[p] = base + 4 * slot * self.part_words
+            pr.slices[p] = base + 4 * (2 * self.part_words + slot * self.slice_words)
+            pr.ready[p] = base + 4 * self.flag_off
+            pr.done[p] = base + 4 * (self.flag_off + 64)
+        pr.counter = self.ptrs[self.rank] + 4 * (self.flag_off + 128)
+        partial = self.buf[slot * self.part_words:(slot + 1) * self.part_words].view(self.B, self.Dp)
+        return pr, partial
+
+
 class CudaEngine:
     """Every method is one call into libarcface_b200.so (include/arcface_b200.h)."""
 
@@ -265,8 +308,17 @@ class CudaEngine:
                    "arcb_merge_loss_peer")
         return lse, zt, loss
 
-    def shard_backward(self, state, cfg, lse=None, zt=None, grad_loss=None, grad_logits=None):
-        """-> (dw [Cs,D], dxhat partial [B,Dp])."""
+    def dx_peer_reduce(self, xc, pr, rows):
+        """Sum of all ranks' dX_hat partials + F.normalize backward, exchanged by the kernel itself -> dx [rows, D]."""
+        import ctypes
+        L = _lib.lib()
+        B, D = xc.shape
+        dx = torch.empty(rows, D, dtype=torch.float32, device=xc.device)
+        _lib.check(L.arcb_dx_peer_reduce(_ptr(xc), D, B, D, ctypes.byref(pr), _ptr(dx), D, _stream()), "arcb_dx_peer_reduce")
+        return dx
+
+    def shard_backward(self, state, cfg, lse=None, zt=None, grad_loss=None, grad_logits=None, dxhat_out=None):
+        """-> (dw [Cs,D], dxhat partial [B,Dp]).  ``dxhat_out``: write the partial there (peer-mapped memory)."""
         L = _lib.lib()
         B, Cs, D, ws, ws_bytes = state[:5]
         cache, gen = state[5], state[6]
@@ -278,7 +330,7 @@ class CudaEngine:
         Dp = L.arcb_padded_dim(D)
         scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
         dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
-        dxhat = torch.empty(B, Dp, dtype=torch.float32, device=dev)
+        dxhat = dxhat_out if dxhat_out is not None else torch.empty(B, Dp, dtype=torch.float32, device=dev)
         _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),
                                          _ptr(grad_logits), Cs if grad_logits is not None else 0, _ptr(scratch),
                                          scratch_bytes, _ptr(dw), _ptr(dxhat), int(cfg.get("flags", 0)), _stream()),
@@ -370,9 +422,27 @@ class _FusedLossFn(torch.autograd.Function):
         (xc,) = ctx.saved_tensors
         eng, state, lse, zt, cfg, w_dtype, x_dtype = ctx.held
         g = grad_loss.detach().to(torch.float32).contiguous()
-        dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt, grad_loss=g)
         group = cfg["group"]
         P = _world(group)
+        B, D = xc.shape
+        reducer = None
+        if P > 1 and cfg.get("peer_reduce_factory") is not None and D % 4 == 0 and D <= 2048:
+            reducer = cfg["peer_reduce_factory"](B, D, xc.device)
+        if reducer is not None:
+            # the partial goes straight into peer-mapped memory; ONE kernel then sums all ranks' partials over NVLink,
+            # applies F.normalize's backward and collects the rows (or keeps only this rank's rows): no NCCL call
+            own = ctx.local_rows is not None
+            pr, partial = reducer.next_exchange(own)
+            dw, _ = eng.shard_backward(state, cfg, lse=lse, zt=zt, grad_loss=g, dxhat_out=partial)
+            if own and ctx.local_rows != (reducer.rank * reducer.rows_per, reducer.rows_per):
+                raise RuntimeError("gather_batch needs the same number of rows on every rank")
+            dx = eng.dx_peer_reduce(xc, pr, reducer.rows_per if own else B)
+            if own:
+                dx = dx * float(P)  # see below: the backbone's DDP reducer averages over the ranks
+            if ctx.lease is not None:
+                ctx.lease.release()
+            return dx.to(x_dtype), dw.to(w_dtype), None, None
+        dw, dxhat = eng.shard_backward(state, cfg, lse=lse, zt=zt, grad_loss=g)
         if ctx.local_rows is not None:
             # each rank only needs the gradient of its own rows: reduce_scatter of the class shards' partials
             #  instead of an all_reduce of all B rows, then F.normalize backward on those rows.
@@ -477,6 +547,7 @@ class ArcMarginProduct(nn.Module):
         self.kernel_flags = int(kernel_flags)
         self.peer_exchange = peer_exchange
         self._peer = {}        # batch size -> _PeerGather
+        self._peer_red = {}    # batch size -> _PeerReduce
         self._peer_off = peer_exchange is False or os.environ.get("ARCB_PEER_EXCHANGE", "1") == "0"
         self.aux = {}
         self._engine = _engine if _engine is not None else CudaEngine()
@@ -507,7 +578,30 @@ class ArcMarginProduct(nn.Module):
             "want_top3": False, "wcache": self._wcache, "flags": int(self.kernel_flags), "gather_batch": False,
             "peer_factory": self._peer_gather if (self.world_size > 1 and not self._peer_off
                                                   and isinstance(self._engine, CudaEngine)) else None,
+            "peer_reduce_factory": self._peer_reducer if (self.world_size > 1 and not self._peer_off
+                                                          and isinstance(self._engine, CudaEngine)) else None,
         }
+
+    def _peer_reducer(self, B, D, device):
+        """The symmetric-memory buffers of the backward's dX exchange for batch size B, or None (-> NCCL)."""
+        if self._peer_off:
+            return None
+        pr = self._peer_red.get(B)
+        if pr is None:
+            ok = torch.ones(1, device=device)
+            try:
+                pr = _PeerReduce(self.process_group, B, D, _lib.lib().arcb_padded_dim(D), device)
+            except Exception as ex:
+                if self.peer_exchange is True:
+                    raise
+                pr, ok[0] = None, 0.0
+                self._peer_error = f"{type(ex).__name__}: {ex}"
+            torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN, group=self.process_group)
+            if ok.item() < 0.5:
+                self._peer_off, pr = True, None
+            else:
+                self._peer_red[B] = pr
+        return pr
 
     def _peer_gather(self, B, device):
         """The symmetric-memory exchange buffers for batch size B (set up collectively on first use), or None."""

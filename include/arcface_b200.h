@@ -134,6 +134,29 @@ int arcb_shard_forward_peer(const float* x, int64_t ldx, const float* w, int64_t
 int arcb_merge_loss_peer(const float* gathered, const void* own_flags, unsigned int epoch, int64_t P, int64_t B, float* lse,
                          float* target_logit, float* loss, void* stream);
 
+/* ---- sum of the class shards' dX_hat partials + F.normalize backward, exchanged by the kernel itself ----
+ * Replaces "all_reduce(dxhat) -> arcb_l2norm_rows_bwd" of the class-sharded backward (autograd behind arc_main.py:329).
+ * Every rank's partial (the `dxhat` it passed to arcb_shard_backward) must live in peer-mapped (symmetric) memory:
+ * partials[p] = rank p's [B, arcb_padded_dim(D)] fp32 of this step as mapped into THIS process.  Rank r reduces the rows
+ * [r * ceil(B / world), ...) over all partials (peer loads), applies dx = (dxh - xh (xh . dxh)) / ||x|| and keeps the
+ * finished rows in slices[r] ([ceil(B / world), D] fp32, symmetric); then every rank copies all slices into its local
+ * dx [B, ldo].  own_only = 1 (data-parallel trainer, reduce_scatter semantics): dx receives only this rank's rows
+ * ([rows, ldo]) and nothing is collected.  ready / done: per rank `world` uint32 flags each, zeroed once; counter: one
+ * zeroed uint32 in local memory; epoch grows by one per call from 1; alternate between two sets of partial / slice
+ * buffers (epoch & 1).  D % 4 == 0, D <= 2048, 16-byte aligned rows.  No collective launch, no host synchronisation. */
+typedef struct arcb_peer_reduce {
+  int rank, world;
+  unsigned int epoch;
+  int own_only;
+  void* partials[ARCB_MAX_PEERS];
+  void* slices[ARCB_MAX_PEERS];
+  void* ready[ARCB_MAX_PEERS];
+  void* done[ARCB_MAX_PEERS];
+  void* counter;
+} arcb_peer_reduce;
+int arcb_dx_peer_reduce(const float* x, int64_t ldx, int64_t B, int64_t D, const arcb_peer_reduce* pr, float* dx,
+                        int64_t ldo, void* stream);
+
 /* ---- fused forward without a caller workspace (no counterpart in the reference) ----
  * For hosts that are not allowed to obtain device memory when the call happens: a plugin living inside another
  * runtime whose allocator owns all of HBM, a serving loop that has frozen its memory plan, or a foreign-language

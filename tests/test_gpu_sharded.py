@@ -99,6 +99,14 @@ def _nccl_worker(rank, world, port, out):
             xp = x.cuda().requires_grad_(True)
             lp = head.forward_loss(xp, y.cuda())
             ok = ok and abs(lp.item() - ln.item()) <= 1e-6 * abs(ln.item()) and torch.equal(head.aux["lse"], nccl_head.aux["lse"])
+            # backward: partial sums of dX_hat reduced by the kernel over peer memory vs NCCL all_reduce + row kernel
+            head.weight.grad = None
+            nccl_head.weight.grad = None
+            lp.backward()
+            ln.backward()
+            torch.cuda.synchronize()
+            ok = (ok and torch.allclose(xp.grad, xn.grad, rtol=1e-4, atol=1e-9)       # other summation order over ranks
+                  and torch.allclose(head.weight.grad, nccl_head.weight.grad, rtol=1e-3, atol=1e-7))
         out[f"peer{rank}"] = peer_used
         head.weight.grad = None
         # data-parallel rows in, reduce_scatter of dX out: this rank's rows only

@@ -189,7 +189,7 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
   }
   // the resident forward leaves only 2 * lanes partials per row (lanes <= tiles_n / 4) in the first half of `part`
   w.bmax = w.part ? reinterpret_cast<float*>(w.part + tiles_n * w.Bp) : nullptr;
-  w.fwd_mode = reinterpret_cast<int*>(take(4));
+  w.fwd_mode = reinterpret_cast<int*>(take(8));  // [0] forward schedule, [1] block counter of the publishing merge
   w.total = off;
   return w;
 }
@@ -636,7 +636,9 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   auto final_merge = [&](const float2* part, int n_part, const Workspace& Wk) -> int {
     LaunchScope ls(ARCB_K_MERGE, st, 1);
     if (px)
-      merge_publish_kernel<<<1, 1024, 0, st>>>(part, n_part, Wk.Bp, Wk.zt, (int)B, stats, peers, px->rank, px->world, px->epoch);
+      merge_publish_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(
+          part, n_part, Wk.Bp, Wk.zt, (int)B, stats, peers, px->rank, px->world, px->epoch,
+          reinterpret_cast<unsigned int*>(Wk.fwd_mode) + 1);
     else
       merge_pack_kernel<<<static_cast<int>((B + 127) / 128), 128, 0, st>>>(part, n_part, Wk.Bp, Wk.zt, (int)B, stats);
     ARCB_CUDA(cudaGetLastError());

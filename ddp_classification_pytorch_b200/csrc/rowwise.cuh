@@ -147,7 +147,10 @@ target_prep_kernel(const float* __restrict__ x, int64_t ldx, const float* __rest
   // (also clears the per-tile counters of the forward kernel that normalises the weight itself, and records which
   //  forward schedule is about to fill this workspace)
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n_zero; k += gridDim.x * blockDim.x) zero[k] = 0u;
-  if (blockIdx.x == 0 && threadIdx.x == 0) *mode_out = mode;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    mode_out[0] = mode;
+    mode_out[1] = 0;  // block counter of merge_publish_kernel
+  }
   const int lane = threadIdx.x & 31;
   const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (i >= Bp) return;
@@ -322,12 +325,16 @@ __device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p
   return v;
 }
 
-// Last merge level + publication.  One block: every thread merges rows tid, tid + blockDim, ...; the record goes to the
-// local `stats` (kept for aux / tests) and to all P ranks.
-__global__ void __launch_bounds__(1024)
+// Last merge level + publication: one thread per row (like merge_pack_kernel); the record goes to the local `stats`
+// (kept for aux / tests) and to all P ranks; the block that finishes last raises the flags.  `counter`: zero before the
+// launch (target_prep_kernel clears it).
+__global__ void __launch_bounds__(128)
 merge_publish_kernel(const float2* __restrict__ part, int n, int64_t ldp, const float* __restrict__ zt, int B,
-                     float* __restrict__ stats, const PeerTable peers, int rank, int P, unsigned int epoch) {
-  for (int row = threadIdx.x; row < B; row += blockDim.x) {
+                     float* __restrict__ stats, const PeerTable peers, int rank, int P, unsigned int epoch,
+                     unsigned int* __restrict__ counter) {
+  __shared__ unsigned int is_last;
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row < B) {
     const float2 r = merge_partials(part, 0, n, ldp, row);
     const float4 rec = make_float4(r.x, r.y, zt[row], 0.f);
     *reinterpret_cast<float4*>(stats + static_cast<int64_t>(row) * 4) = rec;
@@ -335,8 +342,13 @@ merge_publish_kernel(const float2* __restrict__ part, int n, int64_t ldp, const 
       *reinterpret_cast<float4*>(peers.buf[p] + (static_cast<int64_t>(rank) * B + row) * 4) = rec;
   }
   __threadfence_system();  // every thread's peer stores are performed system-wide ...
-  __syncthreads();         // ... before anybody raises a flag
-  if (threadIdx.x < P) st_release_sys_u32(peers.flag[threadIdx.x] + rank, epoch);
+  __syncthreads();         // ... before this block is counted as done
+  if (threadIdx.x == 0) is_last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (is_last && threadIdx.x < P) {
+    __threadfence_system();
+    st_release_sys_u32(peers.flag[threadIdx.x] + rank, epoch);
+  }
 }
 
 // loss_kernel that first waits for the P records of this step (see above).  `flags` is this rank's own flag array.
@@ -451,10 +463,16 @@ dx_peer_reduce_kernel(const float* __restrict__ x, int64_t ldx, float* __restric
       sum[k] = make_float4(0.f, 0.f, 0.f, 0.f);
       xv[k] = sum[k];
       if (idx < n4) {
-        for (int p = 0; p < a.P; ++p) {
-          const float4 v = __ldcv(reinterpret_cast<const float4*>(a.partial[p] + static_cast<int64_t>(row) * a.Dp) + idx);
-          sum[k].x += v.x; sum[k].y += v.y; sum[k].z += v.z; sum[k].w += v.w;
-        }
+        // all P loads are issued before the first one is used: one NVLink round trip, not P of them
+        float4 v[16];
+#pragma unroll
+        for (int p = 0; p < 16; ++p)
+          if (p < a.P) v[p] = __ldcv(reinterpret_cast<const float4*>(a.partial[p] + static_cast<int64_t>(row) * a.Dp) + idx);
+#pragma unroll
+        for (int p = 0; p < 16; ++p)
+          if (p < a.P) {
+            sum[k].x += v[p].x; sum[k].y += v[p].y; sum[k].z += v[p].z; sum[k].w += v[p].w;
+          }
         xv[k] = xr[idx];
         ss += xv[k].x * xv[k].x + xv[k].y * xv[k].y + xv[k].z * xv[k].z + xv[k].w * xv[k].w;
         dot += xv[k].x * sum[k].x + xv[k].y * sum[k].y + xv[k].z * sum[k].z + xv[k].w * sum[k].w;

@@ -22,6 +22,7 @@ collective plumbing can be exercised by CPU ``gloo`` tests with a checker engine
 """
 from __future__ import annotations
 
+import functools
 import math
 import os
 from typing import Optional
@@ -36,6 +37,27 @@ from . import _lib
 # together with the matching w_hat rows must stay inside the 126 MB L2.  0 = ask the library
 # (arcb_suggest_chunk_classes: e.g. 256 * 19 at B=1024, D=512); ARCB_CHUNK_CLASSES overrides it for tuning runs.
 DEFAULT_CHUNK_CLASSES = int(os.environ.get("ARCB_CHUNK_CLASSES", 0))
+_SCRATCH_BUFS = int(os.environ.get("ARCB_SCRATCH_BUFS", 4))
+
+
+@functools.lru_cache(maxsize=256)
+def _ws_bytes(B, Cs, D, flags):
+    return _lib.lib().arcb_ws_bytes(B, Cs, D, flags)
+
+
+@functools.lru_cache(maxsize=256)
+def _scratch_bytes_for(B, Cs, D, chunk_classes, nbuf):
+    """Pure size arithmetic of the backward scratch (cached: it sits on the per-step host path)."""
+    L = _lib.lib()
+    if chunk_classes <= 0:
+        chunk_classes = L.arcb_suggest_chunk_classes(B, Cs, D)
+    chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
+    return L.arcb_scratch_bytes(B, nbuf * chunk)
+
+
+@functools.lru_cache(maxsize=64)
+def _padded_dim(D):
+    return _lib.lib().arcb_padded_dim(D)
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -88,7 +110,7 @@ class _WeightCache:
         self.generation = 0
 
     def workspace(self, B, Cs, D, device, flags=0):
-        need = _lib.lib().arcb_ws_bytes(B, Cs, D, int(flags))
+        need = _ws_bytes(B, Cs, D, int(flags))
         if need <= 0:
             raise RuntimeError("arcb_ws_bytes rejected the sizes")
         if self.ws is None or self.key != (Cs, D, device) or need > self.ws_bytes:
@@ -147,18 +169,23 @@ class _PeerGather:
         self.hdl.barrier()  # every rank's flags are zero before anybody publishes
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.epoch = 0
+        self._slots = []  # per step slot: (descriptor, local gathered view); only the epoch changes from step to step
+        for slot in range(2):
+            px = _lib.PeerExchange()
+            px.rank, px.world = self.rank, self.P
+            for p in range(self.P):
+                px.gather_bufs[p] = self.ptrs[p] + slot * self.slot_words * 4
+                px.flags[p] = self.ptrs[p] + 2 * self.slot_words * 4
+            gathered = self.buf[slot * self.slot_words:(slot + 1) * self.slot_words].view(self.P * self.B, 4)
+            self._slots.append((px, gathered))
+        self._flags_ptr = self.ptrs[self.rank] + 2 * self.slot_words * 4
 
     def next_exchange(self):
         """-> (descriptor for this step, local gathered view [P, B, 4], local flags ptr)."""
         self.epoch += 1
-        slot = self.epoch & 1
-        px = _lib.PeerExchange()
-        px.rank, px.world, px.epoch = self.rank, self.P, self.epoch & 0xFFFFFFFF
-        for p in range(self.P):
-            px.gather_bufs[p] = self.ptrs[p] + slot * self.slot_words * 4
-            px.flags[p] = self.ptrs[p] + 2 * self.slot_words * 4
-        gathered = self.buf[slot * self.slot_words:(slot + 1) * self.slot_words].view(self.P * self.B, 4)
-        return px, gathered, self.ptrs[self.rank] + 2 * self.slot_words * 4
+        px, gathered = self._slots[self.epoch & 1]
+        px.epoch = self.epoch & 0xFFFFFFFF
+        return px, gathered, self._flags_ptr
 
 
 class _PeerReduce:
@@ -186,21 +213,25 @@ class _PeerReduce:
         self.hdl.barrier()
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.epoch = 0
+        self._slots = []
+        for slot in range(2):
+            pr = _lib.PeerReduce()
+            pr.rank, pr.world = self.rank, self.P
+            for p in range(self.P):
+                base = self.ptrs[p]
+                pr.partials[p] = base + 4 * slot * self.part_words
+                pr.slices[p] = base + 4 * (2 * self.part_words + slot * self.slice_words)
+                pr.ready[p] = base + 4 * self.flag_off
+                pr.done[p] = base + 4 * (self.flag_off + 64)
+            pr.counter = self.ptrs[self.rank] + 4 * (self.flag_off + 128)
+            partial = self.buf[slot * self.part_words:(slot + 1) * self.part_words].view(self.B, self.Dp)
+            self._slots.append((pr, partial))
 
     def next_exchange(self, own_only):
         """-> (descriptor of this step, this rank's partial buffer [B, Dp] to hand to the backward kernel)."""
         self.epoch += 1
-        slot = self.epoch & 1
-        pr = _lib.PeerReduce()
-        pr.rank, pr.world, pr.epoch, pr.own_only = self.rank, self.P, self.epoch & 0xFFFFFFFF, int(bool(own_only))
-        for p in range(self.P):
-            base = self.ptrs[p]
-            pr.partials[p] = base + 4 * slot * self.part_words
-            pr.slices[p] = base + 4 * (2 * self.part_words + slot * self.slice_words)
-            pr.ready[p] = base + 4 * self.flag_off
-            pr.done[p] = base + 4 * (self.flag_off + 64)
-        pr.counter = self.ptrs[self.rank] + 4 * (self.flag_off + 128)
-        partial = self.buf[slot * self.part_words:(slot + 1) * self.part_words].view(self.B, self.Dp)
+        pr, partial = self._slots[self.epoch & 1]
+        pr.epoch, pr.own_only = self.epoch & 0xFFFFFFFF, int(bool(own_only))
         return pr, partial
 
 
@@ -217,17 +248,14 @@ class CudaEngine:
 
     @staticmethod
     def _alloc_ws(B, Cs, D, device, flags=0):
-        nbytes = _lib.lib().arcb_ws_bytes(B, Cs, D, int(flags))
+        nbytes = _ws_bytes(B, Cs, D, int(flags))
         if nbytes <= 0:
             raise RuntimeError("arcb_ws_bytes rejected the sizes")
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
     @staticmethod
     def _scratch_for(B, Cs, D, device, chunk_classes):
-        if chunk_classes <= 0:
-            chunk_classes = _lib.lib().arcb_suggest_chunk_classes(B, Cs, D)
-        chunk = min(max(128, chunk_classes), (Cs + 127) // 128 * 128)
-        nbytes = _lib.lib().arcb_scratch_bytes(B, int(os.environ.get("ARCB_SCRATCH_BUFS", 4)) * chunk)  # four buffers by default
+        nbytes = _scratch_bytes_for(B, Cs, D, int(chunk_classes), _SCRATCH_BUFS)  # four chunk buffers by default
         return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
     def shard_forward(self, xc, wc, lab, cfg):
@@ -327,7 +355,7 @@ class CudaEngine:
                                "forward before its backward ran (second backward through a retained graph?); "
                                "construct the head with cache_normalized_weight=False for that pattern")
         dev = ws.device
-        Dp = L.arcb_padded_dim(D)
+        Dp = _padded_dim(D)
         scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
         dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
         dxhat = dxhat_out if dxhat_out is not None else torch.empty(B, Dp, dtype=torch.float32, device=dev)

@@ -64,6 +64,10 @@ def test_full_size_against_eager_fp32_port_on_gpu(name, easy):
     # argmax / top-3: identical wherever the fp32 logits are separated by more than SGEMM summation-order noise
     top = port.last_logits.topk(4, dim=1)
     clear = ((top.values[:, :-1] - top.values[:, 1:]) > 1e-3).all(dim=1)
+    # rows excluded from the exact top-3 assertion: the fp32 reference itself is ambiguous there
+    print(f"[fullsize {name} easy={easy}] rows with all top-4 fp32 gaps > 1e-3: {clear.float().mean().item():.4f}; "
+          f"top-3 identical on ALL rows: {(head.aux['top3'] == top.indices[:, :3]).all(dim=1).float().mean().item():.4f}; "
+          f"argmax identical on ALL rows: {(head.aux['argmax'] == port.last_logits.argmax(1)).float().mean().item():.4f}")
     assert clear.float().mean() > 0.85
     assert torch.equal(head.aux["top3"][clear], top.indices[clear][:, :3])
     assert torch.equal(head.aux["argmax"][clear], port.last_logits.argmax(1)[clear])

@@ -19,7 +19,7 @@ _SRC = os.path.join(_PKG_DIR, "csrc", "arcface_b200.cu")
 _HDRS = [
     os.path.join(_PKG_DIR, "csrc", n)
     for n in ("ptx_sm100.cuh", "gemm_sm100.cuh", "gemm2_sm100.cuh", "epilogues.cuh", "rowwise.cuh", "bwd_persistent.cuh",
-              "optim_rows.cuh", "fwd_resident.cuh")
+              "optim_rows.cuh", "fwd_resident.cuh", "bwd_probs.cuh")
 ] + [os.path.join(_ROOT, "include", "arcface_b200.h")]
 
 NVCC_FLAGS = [
@@ -35,6 +35,7 @@ EXPORTED = [
     "arcb_profile_collect", "arcb_shard_forward_static", "arcb_shard_top3",
     "arcb_shard_forward_prenorm", "arcb_ws_weight_slots", "arcb_sgd_step", "arcb_adam_step",
     "arcb_suggest_chunk_classes", "arcb_shard_forward_peer", "arcb_merge_loss_peer", "arcb_dx_peer_reduce",
+    "arcb_keep_probs_active",
 ]
 
 MAX_PEERS = 16
@@ -64,6 +65,7 @@ BWD_PER_CHUNK = 0x10
 BWD_SINGLE_CTA = 0x20
 BWD_STATIC_SHARE = 0x40
 BWD_NO_COOP = 0x80  # profiling only
+KEEP_PROBS = 0x100
 
 KERNEL_KINDS = [
     "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",
@@ -125,6 +127,8 @@ def _declare(lib):
     lib.arcb_ws_bytes.argtypes = [i64, i64, i64, i32]
     lib.arcb_suggest_chunk_classes.restype = i64
     lib.arcb_suggest_chunk_classes.argtypes = [i64, i64, i64]
+    lib.arcb_keep_probs_active.restype = i32
+    lib.arcb_keep_probs_active.argtypes = [i64, i64, i64, f32, i32]
     lib.arcb_scratch_bytes.restype = i64
     lib.arcb_scratch_bytes.argtypes = [i64, i64]
     fwd_args = [vp, i64, vp, i64, vp, i64, i64, i64, i64, f32, f32, i32, vp, i64]

@@ -16,6 +16,7 @@
 #include <string.h>
 
 #include "bwd_persistent.cuh"
+#include "bwd_probs.cuh"
 #include "epilogues.cuh"
 #include "gemm2_sm100.cuh"
 #include "gemm_sm100.cuh"
@@ -143,12 +144,25 @@ struct Workspace {
   unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
   int4* items;             // [items_cap][2] tile list of the persistent backward (bwd_items_kernel)
   int64_t items_cap;
+  __nv_bfloat16* probs;    // ARCB_KEEP_PROBS: P'^T [Cs, Bp] class-major, else nullptr
+  __nv_bfloat16* xc;       // ARCB_KEEP_PROBS: c (.) x_hat [B, Dp], the dW operand
+  float* cvec;             // ARCB_KEEP_PROBS: c_i [Bp]
+  float* bmax_p;           // ARCB_KEEP_PROBS: block maxima [2 * tiles_n][Bp] (the partials carry a fixed reference there)
   float* bmax;             // resident forward: block maxima [2 * tiles_n][Bp], second half of the `part` region
   int* fwd_mode;           // which forward filled the workspace (kFwd*): tells arcb_shard_top3 where the block maxima are
   int64_t total;
 };
 
-Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
+// Stored-probabilities schedule (ARCB_KEEP_PROBS): when it applies.  The forward must be the resident one, the feature
+// row must span exactly two 256-column halves (bwd_probs.cuh), and with the fixed reference s2 = s log2(e) every P' must
+// stay a normal bf16 number: 2^(-2 s2) >= 2^-126.  Otherwise the flag is ignored and the backward recomputes.
+bool keep_probs_applies(int64_t B, int64_t Cs, int64_t D, float s, int flags) {
+  if (!(flags & ARCB_KEEP_PROBS) || (flags & ARCB_FWD_PAIR)) return false;
+  if (D <= 256 || D > 512 || !(s > 0.f) || 2.f * s * 1.4426950408889634f > 120.f) return false;
+  return B >= 128 && Cs >= 4096;  // small problems are launch bound either way: keep the default there
+}
+
+Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D, bool keep_probs = false) {
   Workspace w;
   w.B = B; w.Cs = Cs; w.D = D;
   w.Bp = round_up(B, kBNTile);
@@ -190,6 +204,14 @@ Workspace carve(void* base, int64_t B, int64_t Cs, int64_t D) {
   // the resident forward leaves only 2 * lanes partials per row (lanes <= tiles_n / 4) in the first half of `part`
   w.bmax = w.part ? reinterpret_cast<float*>(w.part + tiles_n * w.Bp) : nullptr;
   w.fwd_mode = reinterpret_cast<int*>(take(8));  // [0] forward schedule, [1] block counter of the publishing merge
+  w.probs = nullptr; w.xc = nullptr; w.cvec = nullptr;
+  w.bmax_p = nullptr;
+  if (keep_probs) {  // at the end: every other offset is the same with and without
+    w.xc = reinterpret_cast<__nv_bfloat16*>(take(B * w.Dp * 2));
+    w.cvec = reinterpret_cast<float*>(take(w.Bp * 4));
+    w.bmax_p = reinterpret_cast<float*>(take(2 * tiles_n * w.Bp * 4));
+    w.probs = reinterpret_cast<__nv_bfloat16*>(take(round_up(Cs, 128) * w.Bp * 2));  // P'^T [Cs, Bp]: class-major
+  }
   w.total = off;
   return w;
 }
@@ -227,7 +249,8 @@ int launch_l2norm(const float* x, int64_t rows, int64_t D, int64_t ldx, __nv_bfl
 // Steps shared by the fused and the materialising forward: normalise, target preparation.
 int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,
                    int64_t Cs, int64_t D, int64_t class_offset, float s, float m, int easy, void* ws_ptr,
-                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, int w_mode = 0, int fwd_mode = kFwdStreaming) {
+                   int64_t ws_bytes, Workspace* out_ws, cudaStream_t st, int w_mode = 0, int fwd_mode = kFwdStreaming,
+                   bool keep_probs = false) {
   // w_mode: 0 = normalise the weight here, 1 = the workspace already holds w_hat / inv_norm of this weight,
   //         2 = the forward GEMM kernel normalises it on the fly (launch_gemm_norm)
   int rc = check_dims(B, Cs, D);
@@ -236,7 +259,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   if (ldx < D || ldw < D) return fail(ARCB_ERR_INVALID, "leading dimension smaller than D");
   if (!(s > 0.f)) return fail(ARCB_ERR_INVALID, "scale s must be positive (got %g)", (double)s);
   if (reinterpret_cast<uintptr_t>(ws_ptr) & 255) return fail(ARCB_ERR_INVALID, "workspace must be 256-byte aligned");
-  Workspace W = carve(ws_ptr, B, Cs, D);
+  Workspace W = carve(ws_ptr, B, Cs, D, keep_probs);
   if (W.total > ws_bytes)
     return fail(ARCB_ERR_WORKSPACE, "workspace too small: need %lld bytes, got %lld", (long long)W.total,
                 (long long)ws_bytes);
@@ -428,6 +451,89 @@ int static_ws_address(void** out) {
 }  // namespace
 
 namespace {
+// Backward from the probabilities the forward kept (ARCB_KEEP_PROBS, bwd_probs.cuh): set-up, dX GEMM, dW kernel.
+int backward_from_probs(const Workspace& W, float s, const float* lse, const float* zt, const float* grad_loss, float* dw,
+                        float* dxhat, int flags, cudaStream_t st) {
+  const int64_t B = W.B, Cs = W.Cs, D = W.D;
+  {
+    ProbsSetup su;
+    su.lse = lse; su.zt = zt; su.grad_loss = grad_loss; su.dphi = W.dphi; su.lbl_local = W.lbl_local; su.xhat = W.xhat;
+    su.xc = W.xc; su.cvec = W.cvec; su.probs = W.probs; su.ldB = W.Bp; su.s = s; su.B = (int)B; su.Bp = (int)W.Bp;
+    su.Dp = (int)W.Dp; su.zero = dxhat; su.n_zero = B * W.Dp;
+    LaunchScope ls(ARCB_K_BWD_PREP, st);
+    probs_setup_kernel<<<2 * device_sm_count(), 256, 0, st>>>(su);
+    ARCB_CUDA(cudaGetLastError());
+  }
+  const int sms = device_sm_count();
+  CUtensorMap tmDx, tmDw;
+  if (!make_tmap_2d(&tmDx, dxhat, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, B, W.Dp * 4, 32, kBM))
+    return fail(ARCB_ERR_CUDA, "tensor map for dxhat could not be encoded (16-byte alignment?)");
+  {
+    // dX_hat[B, D] = diag(c) P'[B, Cs] w_hat[Cs, D]: every CTA keeps ONE output tile in TMEM for its whole slice of the
+    // classes and reduce-adds it once at the end
+    // A = P' as an MN-major operand: stored [k = classes, m = samples] with the samples contiguous
+    Operand a{W.probs, W.Bp, Cs, W.Bp}, b{W.what, W.Dp, Cs, W.Dp};
+    const int tiles = static_cast<int>(((B + kBM - 1) / kBM) * ((D + kBNTile - 1) / kBNTile));
+    int split = sms / (tiles > 0 ? tiles : 1);
+    if (split < 1) split = 1;
+    EpiRedAdd::Params ep{(int)B, (int)D, W.cvec};
+    LaunchScope ls(ARCB_K_DX_GEMM, st);
+    cudaError_t e;
+    if (flags & ARCB_BWD_SINGLE_CTA) {
+      e = launch_gemm<EpiRedAdd, kBNTile, 3, true, true>(a, b, &tmDx, B, D, Cs, split, ep, st);
+    } else {
+      b.mn_extent = W.Dp;
+      const int ptiles = static_cast<int>(((B + 2 * kBM - 1) / (2 * kBM)) * ((D + kBNTile - 1) / kBNTile));
+      int psplit = (sms / 2) / (ptiles > 0 ? ptiles : 1);
+      if (psplit < 1) psplit = 1;
+      e = launch_gemm_pair<EpiRedAdd, kBNTile, 5, true, true>(a, b, &tmDx, B, D, Cs, psplit, ep, st);
+    }
+    if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
+  }
+  {
+    // dW[Cs, D] = inv_norm (P'^T (c.x_hat) - t w_hat): clusters of two CTAs, one feature half each
+    CUtensorMap tmPt, tmXc;
+    bool ok = make_tmap_2d(&tmPt, W.probs, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W.Bp, Cs, W.Bp * 2, kBK, kBM);
+    ok = ok && make_tmap_mn3(&tmXc, W.xc, W.Dp, B, W.Dp * 2, kPwBN / 64);
+    if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the dW kernel could not be encoded");
+    const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
+                        make_tmap_2d(&tmDw, dw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, Cs, D * 4, 32, kBM);
+    if (!dw_tma) tmDw = tmDx;
+    PwArgs ar;
+    ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.Cs = (int)Cs; ar.D = (int)D; ar.Dp = (int)W.Dp;
+    ar.kb_total = (int)((B + kBK - 1) / kBK);
+    ar.tiles_m = (int)((Cs + kBM - 1) / kBM);
+    ar.debug = env_knobs().debug_epi;
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!attr_set[dev].load(std::memory_order_acquire)) {
+      ARCB_CUDA(cudaFuncSetAttribute(dw_probs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PwSmem::kTotal));
+      attr_set[dev].store(true, std::memory_order_release);
+    }
+    int clusters = sms / 2;
+    if (clusters > ar.tiles_m) clusters = ar.tiles_m;
+    if (clusters < 1) clusters = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = PwSmem::kTotal;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;  // the two CTAs only wait for each other: cluster scheduling suffices
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    LaunchScope ls(ARCB_K_DW_GEMM, st);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, dw_probs_kernel, tmPt, tmXc, tmDw, ar, dw_tma ? 1 : 0);
+    if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW kernel launch: %s", cudaGetErrorString(e));
+  }
+  return ARCB_OK;
+}
+
 // ---- optimizer step on the weight shard (+ the next forward's normalised copy) -- optim_rows.cuh ----
 template <class Rule>
 int launch_optim(float* w, int64_t ldw, const float* dw, int64_t ldg, float* s0, float* s1, int64_t lds,
@@ -572,9 +678,10 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
 }
 
 int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D, int flags) {
-  (void)flags;  // no flag changes the layout today; the argument keeps the query a pure function if one ever does
   if (B <= 0 || Cs <= 0 || D <= 0) return -1;
-  return carve(nullptr, B, Cs, D).total;
+  // ARCB_KEEP_PROBS adds the stored probabilities when the schedule applies to the shape (for ANY scale s: the query
+  // has no s, so it sizes for the case that the forward uses them)
+  return carve(nullptr, B, Cs, D, keep_probs_applies(B, Cs, D, 1.f, effective_flags(flags))).total;
 }
 
 // Classes per backward chunk for this problem.  Four chunks of bf16 G^T must stay well inside L2, short chunks pay
@@ -608,6 +715,11 @@ int64_t arcb_suggest_chunk_classes(int64_t B, int64_t Cs, int64_t D) {
   }
   if (best_r > r_cap) best_r = r_cap;
   return best_r * 256;
+}
+
+int arcb_keep_probs_active(int64_t B, int64_t Cs, int64_t D, float s, int flags) {
+  if (B <= 0 || Cs <= 0 || D <= 0) return 0;
+  return keep_probs_applies(B, Cs, D, s, effective_flags(flags)) ? 1 : 0;
 }
 
 int64_t arcb_scratch_bytes(int64_t B, int64_t chunk_classes) {
@@ -657,16 +769,25 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
               (ldw % 4 == 0) && D <= 2048 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
   // x_hat-resident schedule (fwd_resident.cuh): the sample block stays in shared memory, one partial per row and CTA
   const bool want_bmax = (flags & ARCB_FWD_BLOCK_MAXIMA) != 0;
-  const bool resident = !(flags & ARCB_FWD_STREAMING) && !pair_gemm && resident_forward_applies(B, Cs, round_up(D, 64));
+  // the workspace layout follows the flag and the shape (what arcb_ws_bytes sized); whether the probabilities are USED
+  // also depends on the scale: too large an s falls back to the recompute backward on the same layout
+  const bool probs_layout = keep_probs_applies(B, Cs, D, 1.f, flags);
+  const bool keep_probs = keep_probs_applies(B, Cs, D, s, flags);
+  const bool resident = !keep_probs && !(flags & ARCB_FWD_STREAMING) && !pair_gemm &&
+                        resident_forward_applies(B, Cs, round_up(D, 64));
   // which array arcb_shard_top3 finds the block maxima in: the partials themselves (streaming), or a separate array
-  const int fwd_mode = resident ? (want_bmax ? kFwdResidentBmax : kFwdResident) : kFwdStreaming;
+  const int fwd_mode = (resident || keep_probs) ? (want_bmax ? kFwdResidentBmax : kFwdResident) : kFwdStreaming;
   int rc = forward_common(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, ws_bytes, &W, st,
-                          w_prenormalised ? 1 : (fuse ? 2 : 0), fwd_mode);
+                          w_prenormalised ? 1 : (fuse ? 2 : 0), fwd_mode, probs_layout);
   if (rc) return rc;
   Operand a{W.xhat, B, W.Dp, W.Dp}, b{W.what, Cs, W.Dp, W.Dp};
   EpiFwdStats::Params ep{W.lbl_local, W.sub, W.part, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
   cudaError_t e = cudaSuccess;
   const int tiles_n = static_cast<int>((Cs + kBNTile - 1) / kBNTile);
+  EpiFwdStatsP::Params epp{W.lbl_local, W.sub, W.part, want_bmax ? W.bmax_p : nullptr, (int)W.Bp, (int)B, (int)Cs, s * kLog2e};
+  CUtensorMap tmP;
+  if (keep_probs && !make_tmap_2d(&tmP, W.probs, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W.Bp, Cs, W.Bp * 2, 64, 64))
+    return fail(ARCB_ERR_CUDA, "tensor map for the stored probabilities could not be encoded");
   NormArgs na_res{};
   if (fuse) {
     na_res.w = w; na_res.ldw = ldw; na_res.rows = Cs; na_res.D = (int)D; na_res.Dp = (int)W.Dp; na_res.what = W.what;
@@ -707,7 +828,8 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
     if (look > 0) na.lookahead = look > ahead ? look : ahead;
     {
       LaunchScope ls(ARCB_K_FWD_GEMM, st);
-      e = launch_gemm_norm<EpiFwdStats, 4>(a, b, B, Cs, W.Dp, ep, na, st);
+      e = keep_probs ? launch_gemm_norm<EpiFwdStatsP, 4>(a, b, B, Cs, W.Dp, epp, na, st, &tmP)
+                     : launch_gemm_norm<EpiFwdStats, 4>(a, b, B, Cs, W.Dp, ep, na, st);
     }
     if (e != cudaSuccess) {  // the grid cannot be made co-resident right now: two kernels instead
       fuse = false;
@@ -717,7 +839,8 @@ static int shard_forward_impl(const float* x, int64_t ldx, const float* w, int64
   }
   if (!fuse) {
     LaunchScope ls(ARCB_K_FWD_GEMM, st);
-    if (pair_gemm) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
+    if (keep_probs) e = launch_gemm<EpiFwdStatsP, kBNTile, 4, false, false>(a, b, &tmP, B, Cs, W.Dp, 1, epp, st);
+    else if (pair_gemm) e = launch_gemm_pair<EpiFwdStats, kBNTile, 6, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
     else e = launch_gemm<EpiFwdStats, kBNTile, 4, false, false>(a, b, nullptr, B, Cs, W.Dp, 1, ep, st);
   }
   if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "forward GEMM launch: %s", cudaGetErrorString(e));
@@ -891,7 +1014,8 @@ int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, in
   if (!x || !w || !ws || !top_val || !top_idx) return fail(ARCB_ERR_INVALID, "null pointer argument");
   if (D * 4 > 96 * 1024) return fail(ARCB_ERR_INVALID, "arcb_shard_top3 supports D <= 24576");
   flags = effective_flags(flags);
-  Workspace W = carve(ws, B, Cs, D);
+  Workspace W = carve(ws, B, Cs, D, keep_probs_applies(B, Cs, D, 1.f, flags));
+  const bool probs_used = keep_probs_applies(B, Cs, D, s, flags);
   if (W.total > ws_bytes) return fail(ARCB_ERR_WORKSPACE, "workspace too small");
   const int nparts = 2 * static_cast<int>((Cs + kBNTile - 1) / kBNTile);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -906,7 +1030,7 @@ int arcb_shard_top3(const float* x, int64_t ldx, const float* w, int64_t ldw, in
   }
   LaunchScope ls(ARCB_K_TOP3, st);
   topk_rescore_kernel<<<static_cast<unsigned>(B), kTopkThreads, D * 4, st>>>(
-      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, W.bmax, W.fwd_mode, nparts, W.Bp,
+      x, ldx, w, ldw, W.inv_nx, W.inv_nw, W.lbl_local, W.sub, W.part, probs_used ? W.bmax_p : W.bmax, W.fwd_mode, nparts, W.Bp,
       (int)B, (int)D,
       Cs, class_offset, s, top_val, top_idx);
   ARCB_CUDA(cudaGetLastError());
@@ -931,7 +1055,8 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   if (rc) return rc;
   flags = effective_flags(flags);
   const bool ext = grad_logits != nullptr;
-  if (!ws || !scratch || !dw || !dxhat) return fail(ARCB_ERR_INVALID, "null pointer argument");
+  const bool use_probs = !ext && keep_probs_applies(B, Cs, D, s, flags);  // the forward kept P': no recompute, no scratch
+  if (!ws || (!scratch && !use_probs) || !dw || !dxhat) return fail(ARCB_ERR_INVALID, "null pointer argument");
   const bool persistent = !(flags & ARCB_BWD_PER_CHUNK);
   const bool pair_bwd = !(flags & ARCB_BWD_SINGLE_CTA);
   const bool dyn_feed = !(flags & ARCB_BWD_STATIC_SHARE);
@@ -939,8 +1064,9 @@ int arcb_shard_backward(int64_t B, int64_t Cs, int64_t D, float s, void* ws, int
   if (!ext && (!lse || !target_logit)) return fail(ARCB_ERR_INVALID, "lse / target_logit required");
   if (ext && ldgl < Cs) return fail(ARCB_ERR_INVALID, "grad_logits leading dimension smaller than Cs");
   if (reinterpret_cast<uintptr_t>(scratch) & 255) return fail(ARCB_ERR_INVALID, "scratch must be 256-byte aligned");
-  Workspace W = carve(ws, B, Cs, D);
+  Workspace W = carve(ws, B, Cs, D, keep_probs_applies(B, Cs, D, 1.f, flags));
   if (W.total > ws_bytes) return fail(ARCB_ERR_WORKSPACE, "workspace too small");
+  if (use_probs) return backward_from_probs(W, s, lse, target_logit, grad_loss, dw, dxhat, flags, st);
   int64_t chunk = scratch_bytes / (W.Bp * 2) / 128 * 128;
   if (chunk < 128)
     return fail(ARCB_ERR_WORKSPACE, "scratch too small: need at least %lld bytes", (long long)(128 * W.Bp * 2));

@@ -170,6 +170,126 @@ struct EpiFwdStats {
 };
 
 // ------------------------------------------------------------------------------------
+// Forward statistics that also KEEP the softmax numerators (ARCB_KEEP_PROBS): P'[j, i] = bf16(2^(s2 (cos_ij - 1))), the
+// fixed reference s2 = s log2(e) (cos <= 1, so P' <= 1: no running maximum), written CLASS-major, P'^T [Cs, Bp] -- a class
+// row holds the whole batch (2 KB at B = 1024), which is what both backward GEMMs want to stream: dW reads [128 classes x
+// all samples] as one contiguous 256 KB region, dX reads 256-byte pieces of rows that its eight sample-block CTAs consume
+// together.  The tile's accumulator is [128 samples x 256 classes] with one SAMPLE per thread, so the store is a
+// transpose through shared memory: thread s writes its 2-byte values down column s of a [64 classes x 128 samples]
+// staging tile (two 128B-swizzled boxes of 64 samples; the 32 lanes of a warp fill 64 contiguous bytes of one class row:
+// no bank conflicts), one bulk tensor store per box.  The partial of a (tile column block, warpgroup) is
+// (s2, sum of the ROUNDED P') -- the (reference, sum) format the merge kernels take -- so the softmax the backward
+// reconstructs from P' sums to one.  Block maxima for the exact top-3 go to their own array when asked for.
+struct EpiFwdStatsP {
+  static constexpr int kSmemBytes = 2 * 64 * 256;   // per warpgroup: [64 classes x 128 samples] bf16 = 16 KB
+  static constexpr bool kUsesTmC = true;            // tmC: P'^T [Cs, Bp] bf16 (pitch Bp), box [64 classes x 64 samples]
+  struct Params {
+    const int* lbl_local;
+    const float* phi;
+    float2* part;
+    float* bmax;  // [2 * tiles_n][ldp] or nullptr
+    int ldp;
+    int B, C;
+    float s2;
+  };
+  using State = EpiNoState;
+  __device__ static void init(const Params&, State&) {}
+  __device__ static void drain(int epi_tid) {
+    if ((epi_tid & 127) == 0) tma_store_wait_all0();
+  }
+  template <int BN>
+  __device__ static void consume(const Params& p, State&, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t* smem) {
+    const int wg = epi_tid >> 7;
+    const int wg_tid = epi_tid & 127;
+    const int row = tc.m_blk * kBM + row_in_tile;  // sample
+    const bool row_ok = row < p.B;
+    int lbl = -1;
+    float phi = 0.f;
+    if (row_ok) {
+      lbl = __ldg(p.lbl_local + row);
+      phi = __ldg(p.phi + row);
+    }
+    float run_l = 0.f, blk_m = -INFINITY;
+    bool any = false;
+    const int col_base = tc.n_blk * BN;
+    uint8_t* buf = smem + wg * (64 * 256);
+    // my column inside the staging tile: box (64 samples) and the 2 bytes inside a 128-byte class row
+    const uint32_t sbox = smem_u32(buf) + static_cast<uint32_t>(row_in_tile >> 6) * (64 * 128);
+    const uint32_t scol = static_cast<uint32_t>(row_in_tile & 63) * 2;  // byte inside the row
+    const uint32_t chunk16 = scol >> 4, within = scol & 15;
+#pragma unroll 1
+    for (int bx = 0; bx < BN / 128; ++bx) {  // this warpgroup's two groups of 64 classes
+      const int cls0 = col_base + wg * (BN / 2) + bx * 64;
+      if (cls0 >= p.C) break;  // warpgroup-uniform
+      // the bulk stores that last used the staging tile have finished reading it
+      if (wg_tid == 0) tma_store_wait_read0();
+      named_bar_sync(2 + wg, kWgThreads);
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int c = wg * (BN / 2) + bx * 64 + h * 32;
+        const int col0 = col_base + c;
+        float v[32];
+        if (col0 < p.C) {
+          tmem_ld32(taddr + c, v);
+          any = true;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = -INFINITY;
+        }
+        if (col0 + 32 > p.C) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j >= p.C) v[j] = -INFINITY;
+        }
+        const unsigned d = static_cast<unsigned>(lbl - col0);
+        if (d < 32u) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j == static_cast<int>(d)) v[j] = phi;
+        }
+        if (p.bmax) {
+          float cm = v[0];
+#pragma unroll
+          for (int j = 1; j < 32; ++j) cm = fmaxf(cm, v[j]);
+          blk_m = fmaxf(blk_m, cm);
+        }
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          // padding samples (row >= B) must contribute nothing to dW: their column of P'^T is zero
+          const uint32_t pk = row_ok ? pack_bf16x2(ex2_approx(fmaf(v[j], p.s2, -p.s2)), ex2_approx(fmaf(v[j + 1], p.s2, -p.s2))) : 0u;
+          a0 += __uint_as_float(pk << 16);  // the rounded values: what the backward will use
+          a1 += __uint_as_float(pk & 0xffff0000u);
+          // class rows (h * 32 + j) and (h * 32 + j + 1) of the staging tile, my column
+          const uint32_t r0 = static_cast<uint32_t>(h * 32 + j), r1 = r0 + 1;
+          const uint32_t a_lo = sbox + r0 * 128 + ((chunk16 ^ (r0 & 7)) << 4) + within;
+          const uint32_t a_hi = sbox + r1 * 128 + ((chunk16 ^ (r1 & 7)) << 4) + within;
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_lo), "h"(static_cast<unsigned short>(pk & 0xffffu)) : "memory");
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_hi), "h"(static_cast<unsigned short>(pk >> 16)) : "memory");
+        }
+        run_l += a0 + a1;
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(2 + wg, kWgThreads);
+      if (wg_tid == 0) {
+        // rows (classes) >= Cs are clipped by the tensor map; sample columns always lie inside [0, Bp)
+        tma_store_2d(&tmC, buf, tc.m_blk * kBM, cls0);
+        tma_store_2d(&tmC, buf + 64 * 128, tc.m_blk * kBM + 64, cls0);
+        tma_store_commit();
+      }
+    }
+    if (row_ok) {
+      p.part[static_cast<int64_t>(tc.n_blk * 2 + wg) * p.ldp + row] =
+          any ? make_float2(p.s2, run_l) : make_float2(-INFINITY, 0.f);
+      if (p.bmax) p.bmax[static_cast<int64_t>(tc.n_blk * 2 + wg) * p.ldp + row] = blk_m * p.s2;
+    }
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
+// ------------------------------------------------------------------------------------
 struct EpiLogits {
   static constexpr int kSmemBytes = 0;
   static constexpr bool kUsesTmC = false;

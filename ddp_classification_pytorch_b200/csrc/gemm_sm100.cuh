@@ -404,7 +404,8 @@ inline cudaError_t launch_gemm(const Operand& a, const Operand& b, const CUtenso
 // path".  na.done must have been zeroed on `stream`.
 template <class Epi, int STAGES>
 inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t M, int64_t N, int64_t K,
-                                    const typename Epi::Params& ep, NormArgs na, cudaStream_t stream) {
+                                    const typename Epi::Params& ep, NormArgs na, cudaStream_t stream,
+                                    const CUtensorMap* tmC_opt = nullptr) {
   constexpr int BN = 256;
   using L = GemmSmem<Epi, BN, STAGES>;
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
@@ -441,7 +442,7 @@ inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t 
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmA, sc, ep, na);
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC_opt ? *tmC_opt : tmA, sc, ep, na);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e;
 }

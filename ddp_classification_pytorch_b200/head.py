@@ -356,7 +356,10 @@ class CudaEngine:
                                "construct the head with cache_normalized_weight=False for that pattern")
         dev = ws.device
         Dp = _padded_dim(D)
-        scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
+        if grad_logits is None and L.arcb_keep_probs_active(B, Cs, D, cfg["s"], int(cfg.get("flags", 0))):
+            scratch, scratch_bytes = None, 0  # the forward kept the probabilities: nothing is recomputed
+        else:
+            scratch, scratch_bytes = self._scratch_for(B, Cs, D, dev, cfg["chunk_classes"])
         dw = torch.empty(Cs, D, dtype=torch.float32, device=dev)
         dxhat = dxhat_out if dxhat_out is not None else torch.empty(B, Dp, dtype=torch.float32, device=dev)
         _lib.check(L.arcb_shard_backward(B, Cs, D, cfg["s"], _ptr(ws), ws_bytes, _ptr(lse), _ptr(zt), _ptr(grad_loss),

@@ -55,6 +55,13 @@ extern "C" {
 #define ARCB_BWD_NO_COOP 0x80      /* PROFILING ONLY: default kernel launched without the cooperative attribute (ncu cannot
                                       replay cooperative + cluster launches).  Safe only on an otherwise idle GPU, where
                                       one CTA per SM is co-resident anyway; never set it in production. */
+/* arcb_ws_bytes + arcb_shard_forward* + arcb_shard_backward (the SAME flag in all three): the forward keeps the softmax
+ * numerators P' = bf16(2^(s log2e (cos - 1))) of the whole shard in the workspace ([B, Cs] bf16: 2 GB at B = 1024,
+ * Cs = 1M) and the backward runs as two plain GEMMs on them instead of recomputing the logits tile by tile: 6 B C D
+ * executed flops instead of 8 B C D, paid for with 2 B C bytes of HBM per pass.  Applies where the resident forward does,
+ * for 256 < D <= 512 and s <= 41 (arcb_keep_probs_active tells); elsewhere the flag is ignored and the default
+ * recompute backward runs.  Same gradients within the parity tolerance either way. */
+#define ARCB_KEEP_PROBS 0x100
 /* arcb_gemm_bf16 (unit tests of the GEMM core) */
 #define ARCB_GEMM_PAIR 0x4         /* CTA-pair core (same bit as ARCB_FWD_PAIR) */
 
@@ -91,6 +98,10 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
 
 /* Bytes of persistent workspace a shard needs between forward and backward, for calls made with `flags`. */
 int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D, int flags);
+
+/* 1 when calls with these sizes, scale and flags use the stored-probabilities schedule (ARCB_KEEP_PROBS), else 0.
+ * In that case arcb_shard_backward needs no scratch (scratch may be NULL / scratch_bytes 0). */
+int arcb_keep_probs_active(int64_t B, int64_t Cs, int64_t D, float s, int flags);
 
 /* Bytes of backward scratch that hold `chunk_classes` classes of bf16 dLoss/dcos for batch B.
  * arcb_shard_backward accepts any scratch >= arcb_scratch_bytes(B, 128); its default persistent

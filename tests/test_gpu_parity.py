@@ -324,3 +324,46 @@ def test_resident_forward_matches_streaming_forward(shape, fused_norm):
     np.testing.assert_allclose(r[0].cpu().numpy(), ref["lse"], rtol=2e-3)
     assert cosine_similarity(r[5].cpu().numpy(), ref["dw"]) >= GRAD_COS
 
+
+@pytest.mark.parametrize("shape,easy", [((1000, 512, 20000), False), ((520, 320, 40003), True), ((1024, 512, 150000), False)])
+def test_backward_from_stored_probabilities_matches_recompute_and_oracle(shape, easy):
+    """ARCB_KEEP_PROBS: the forward keeps bf16 softmax numerators and the backward runs as two plain GEMMs (no recompute
+    GEMM).  Same loss, gradients within the parity bar of the oracle and of the default recompute path, planted rows on
+    both sides of the margin branches, ragged class counts and feature sizes."""
+    B, D, C = shape
+    gen = torch.Generator().manual_seed(B * 7 + C)
+    w = ((torch.rand(C, D, generator=gen) * 2 - 1) * 0.05)
+    x = torch.randn(B, D, generator=gen)
+    y = torch.randint(0, C, (B,), generator=gen)
+    for r, c in zip(range(0, 64, 4), [-0.99, -0.9, -0.86, -0.3, -0.01, 0.01, 0.4, 0.9] * 2):  # target cosines to plant
+        wy = w[y[r]] / w[y[r]].norm()
+        n = torch.randn(D, generator=gen); n = n - (n @ wy) * wy; n = n / n.norm()
+        x[r] = 2.0 * (c * wy + (1 - c * c) ** 0.5 * n)
+    L = _lib.lib()
+    assert L.arcb_keep_probs_active(B, C, D, 30.0, _lib.KEEP_PROBS) == 1
+    assert L.arcb_keep_probs_active(B, C, D, 30.0, 0) == 0 and L.arcb_keep_probs_active(B, C, D, 64.0, _lib.KEEP_PROBS) == 0
+    out = {}
+    for name, flags in (("probs", _lib.KEEP_PROBS), ("recompute", 0)):
+        head = _module(w.numpy(), 30.0, 0.5, easy, kernel_flags=flags)
+        xg = x.cuda().requires_grad_(True)
+        loss = head.forward_loss(xg, y.cuda(), want_top3=(name == "probs"))
+        (loss * 1.5).backward()
+        _sync_ok()
+        out[name] = (loss.item(), xg.grad.clone(), head.weight.grad.clone(), head.aux["lse"].clone())
+    p, r = out["probs"], out["recompute"]
+    assert p[0] == pytest.approx(r[0], rel=1e-4)
+    torch.testing.assert_close(p[3], r[3], rtol=1e-4, atol=1e-4)
+    assert cosine_similarity(p[1].cpu().numpy(), r[1].cpu().numpy()) >= 0.9995
+    assert cosine_similarity(p[2].cpu().numpy(), r[2].cpu().numpy()) >= 0.9995
+    if C <= 50000:  # the fp64 oracle finishes in seconds up to here
+        ref = orc.head_forward_backward(x.numpy(), w.numpy(), y.numpy(), 30.0, 0.5, easy, grad_scale=1.5)
+        assert abs(p[0] - ref["loss"]) <= LOSS_RTOL * abs(ref["loss"])
+        assert cosine_similarity(p[1].cpu().numpy(), ref["dx"]) >= GRAD_COS
+        assert cosine_similarity(p[2].cpu().numpy(), ref["dw"]) >= GRAD_COS
+        assert np.linalg.norm(p[2].cpu().numpy()) == pytest.approx(np.linalg.norm(ref["dw"]), rel=2e-2)
+        assert np.linalg.norm(p[1].cpu().numpy()) == pytest.approx(np.linalg.norm(ref["dx"]), rel=2e-2)
+        # F.normalize backward: every gradient row is orthogonal to its own input row (the t_j swap got the projection right)
+        wn = torch.nn.functional.normalize(w.cuda().double(), dim=1)
+        gw = p[2].double()
+        rel = (wn * gw).sum(1).abs() / (gw.norm(dim=1) + 1e-30)
+        assert rel.median().item() < 2e-2

@@ -300,6 +300,10 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P'^T [Cs, Bp] as 
               r[q * 8 + 2 * e + 1] = inv * fmaf(-tj, __uint_as_float(wr[e] & 0xffff0000u), v[q * 8 + 2 * e + 1]);
             }
           }
+          if (ar.debug >= 5) {  // debugging aids: 5 = constant, 6 = raw accumulator, 7 = the swapped projection t_j
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = ar.debug == 5 ? 1.f : (ar.debug == 6 ? v[j] : tj);
+          }
           if (ar.debug >= 1 && ar.debug <= 3) {
             if (r[0] == 123.456f && r[31] == 654.321f) tj += 1.f;  // keep the arithmetic alive
           } else if (use_tma) {

@@ -1,0 +1,37 @@
+"""Debug aid: dW kernel of the stored-probabilities backward under ARCB_DEBUG_EPI=5/6/7 (constant / raw accumulator / t_j)."""
+import math, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+import torch
+from ddp_classification_pytorch_b200 import ArcMarginProduct, _lib
+mode = int(os.environ.get("ARCB_DEBUG_EPI", "0"))
+B, D, C = 1000, 512, 20000
+g = torch.Generator().manual_seed(1)
+w = ((torch.rand(C, D, generator=g) * 2 - 1) * 0.05); x = torch.randn(B, D, generator=g); y = torch.randint(0, C, (B,), generator=g)
+head = ArcMarginProduct(D, C, kernel_flags=_lib.KEEP_PROBS).cuda()
+with torch.no_grad(): head.weight.copy_(w)
+xg = x.cuda().requires_grad_(True)
+loss = head.forward_loss(xg, y.cuda()); loss.backward(); torch.cuda.synchronize()
+dw = head.weight.grad
+print(f"mode {mode}: loss {loss.item():.5f}  NaN rows {torch.isnan(dw).any(1).sum().item()}  zero rows {(dw == 0).all(1).sum().item()}  "
+      f"rows==1 {(dw == 1).all(1).sum().item()}  mean|dw| {dw[~torch.isnan(dw).any(1)].abs().mean().item():.3e}")
+xd, wd, yd = x.cuda().double(), w.cuda().double(), y.cuda()
+xh = torch.nn.functional.normalize(xd, dim=1); wn = wd.norm(dim=1); wh = wd / wn[:, None]
+cos = xh @ wh.t(); sine = torch.sqrt((1 - cos ** 2).clamp(0, 1)); phi = cos * math.cos(0.5) - sine * math.sin(0.5)
+th, mm = math.cos(math.pi - 0.5), math.sin(math.pi - 0.5) * 0.5
+hot = torch.zeros_like(cos).scatter_(1, yd.view(-1, 1), 1.0)
+z = 30.0 * (hot * torch.where(cos > th, phi, cos - mm) + (1 - hot) * cos)
+p_ = torch.softmax(z, dim=1)
+dphi = torch.where(cos > th, math.cos(0.5) + math.sin(0.5) * cos / sine.clamp_min(1e-30), torch.ones_like(cos))
+G = (p_ - hot) * 30.0 / B * (hot * dphi + (1 - hot))
+dwh = G.t() @ xh                       # raw accumulator the kernel should hold
+tj = (wh * dwh).sum(1)                 # projection
+def cmp(name, got, ref):
+    ok = ~torch.isnan(got).any(1)
+    c = torch.nn.functional.cosine_similarity(got[ok].double().flatten(), ref[ok].flatten(), dim=0).item()
+    print(f"   vs {name}: cos {c:.6f}  norm ratio {(got[ok].double().norm() / ref[ok].norm()).item():.4f}")
+    for t in (0, 1, 73, 74, 75, 147, 148, 155, 156):
+        sl = slice(t * 128, min(C, (t + 1) * 128)); gg, rr = got[sl].double(), ref[sl]
+        print(f"      tile {t}: nan {torch.isnan(gg).any().item()}  cos {torch.nn.functional.cosine_similarity(torch.nan_to_num(gg).flatten(), rr.flatten(), dim=0).item():.4f}  |got| {torch.nan_to_num(gg).norm().item():.3e} |ref| {rr.norm().item():.3e}")
+if mode == 6: cmp("raw accumulator G^T x_hat", dw, dwh)
+if mode == 7: cmp("t_j broadcast", dw, tj[:, None].expand(-1, D))
+if mode in (0, 4): cmp("final dW" if mode == 0 else "dW without projection", dw, ((dwh - (tj[:, None] * wh if mode == 0 else 0)) / wn[:, None]))

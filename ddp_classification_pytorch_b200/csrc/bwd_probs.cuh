@@ -284,7 +284,7 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P'^T [Cs, Bp] as 
 #pragma unroll 1
         for (int c = c_begin; c < c_end; c += 32) {
           const int col0 = n_blk * kPwBN + c;
-          if (col0 >= ar.D || ar.debug >= 3) break;
+          if (col0 >= ar.D || ar.debug == 3) break;
           uint4 wv[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) wv[q] = __ldg(reinterpret_cast<const uint4*>(wrow + c) + q);

@@ -32,6 +32,23 @@ def cmp(name, got, ref):
     for t in (0, 1, 73, 74, 75, 147, 148, 155, 156):
         sl = slice(t * 128, min(C, (t + 1) * 128)); gg, rr = got[sl].double(), ref[sl]
         print(f"      tile {t}: nan {torch.isnan(gg).any().item()}  cos {torch.nn.functional.cosine_similarity(torch.nan_to_num(gg).flatten(), rr.flatten(), dim=0).item():.4f}  |got| {torch.nan_to_num(gg).norm().item():.3e} |ref| {rr.norm().item():.3e}")
-if mode == 6: cmp("raw accumulator G^T x_hat", dw, dwh)
+def chunks(name, got, ref, t):
+    sl = slice(t * 128, min(C, (t + 1) * 128)); gg, rr = torch.nan_to_num(got[sl].double()), ref[sl]
+    cs = [torch.nn.functional.cosine_similarity(gg[:, c:c + 32].flatten(), rr[:, c:c + 32].flatten(), dim=0).item() for c in range(0, D, 32)]
+    rs = [torch.nn.functional.cosine_similarity(gg[r:r + 16].flatten(), rr[r:r + 16].flatten(), dim=0).item() for r in range(0, gg.shape[0], 16)]
+    print(f"   {name} tile {t}: cos per 32-col chunk", [round(c, 2) for c in cs])
+    print(f"   {name} tile {t}: cos per 16-row group", [round(c, 2) for c in rs])
+    # rows with a label: is the row a multiple of SOME x_hat row?
+    rows_l = [int(j) for j in torch.unique(yd) if t * 128 <= int(j) < (t + 1) * 128][:6]
+    for j in rows_l:
+        gvec = torch.nan_to_num(got[j].double()); sims = (xh @ gvec) / (gvec.norm() + 1e-30)
+        best = int(sims.abs().argmax()); want = (yd == j).nonzero().flatten().tolist()
+        print(f"      class {j}: labelled samples {want}, row is most parallel to x_hat[{best}] (|cos| {sims[best].abs().item():.3f}); cos with reference row {torch.nn.functional.cosine_similarity(gvec, ref[j], dim=0).item():.3f}")
+if mode == 6:
+    cmp("raw accumulator G^T x_hat", dw, dwh)
+    for t in (0, 1, 74): chunks("raw acc", dw, dwh, t)
 if mode == 7: cmp("t_j broadcast", dw, tj[:, None].expand(-1, D))
-if mode in (0, 4): cmp("final dW" if mode == 0 else "dW without projection", dw, ((dwh - (tj[:, None] * wh if mode == 0 else 0)) / wn[:, None]))
+if mode in (0, 4):
+    ref = ((dwh - (tj[:, None] * wh if mode == 0 else 0)) / wn[:, None])
+    cmp("final dW" if mode == 0 else "dW without projection", dw, ref)
+    for t in (0, 74): chunks("dW", dw, ref, t)

@@ -124,7 +124,7 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P'^T [Cs, Bp] as 
   const int rank = static_cast<int>(cluster_ctarank());   // = feature half this CTA computes
   const int cluster = static_cast<int>(blockIdx.x >> 1);
   const int n_clusters = static_cast<int>(gridDim.x >> 1);
-  const int n_blk = rank;
+  const int n_blk = (ar.debug == 8 || ar.debug == 9) ? 1 - rank : rank;  // debug 8 / 9: feature halves swapped between the CTAs
   const bool half_ok = n_blk * kPwBN < ar.D;              // D <= 256: the second CTA has no columns, it only swaps zeros
 
   if (warp == 0 && lane == 0) {
@@ -302,7 +302,7 @@ dw_probs_kernel(const __grid_constant__ CUtensorMap tmPt,   // P'^T [Cs, Bp] as 
           }
           if (ar.debug >= 5) {  // debugging aids: 5 = constant, 6 = raw accumulator, 7 = the swapped projection t_j
 #pragma unroll
-            for (int j = 0; j < 32; ++j) r[j] = ar.debug == 5 ? 1.f : (ar.debug == 6 ? v[j] : tj);
+            for (int j = 0; j < 32; ++j) r[j] = ar.debug == 5 ? 1.f : ((ar.debug == 6 || ar.debug == 8) ? v[j] : tj);
           }
           if (ar.debug >= 1 && ar.debug <= 3) {
             if (r[0] == 123.456f && r[31] == 654.321f) tj += 1.f;  // keep the arithmetic alive

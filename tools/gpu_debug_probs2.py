@@ -44,7 +44,7 @@ def chunks(name, got, ref, t):
         gvec = torch.nan_to_num(got[j].double()); sims = (xh @ gvec) / (gvec.norm() + 1e-30)
         best = int(sims.abs().argmax()); want = (yd == j).nonzero().flatten().tolist()
         print(f"      class {j}: labelled samples {want}, row is most parallel to x_hat[{best}] (|cos| {sims[best].abs().item():.3f}); cos with reference row {torch.nn.functional.cosine_similarity(gvec, ref[j], dim=0).item():.3f}")
-if mode == 6:
+if mode in (6, 8):
     cmp("raw accumulator G^T x_hat", dw, dwh)
     for t in (0, 1, 74): chunks("raw acc", dw, dwh, t)
 if mode == 7: cmp("t_j broadcast", dw, tj[:, None].expand(-1, D))

@@ -47,6 +47,18 @@ def chunks(name, got, ref, t):
 if mode in (6, 8):
     cmp("raw accumulator G^T x_hat", dw, dwh)
     for t in (0, 1, 74): chunks("raw acc", dw, dwh, t)
+    # which reference 64-column block (of which tile) does each 64-column block of tile 0 / 74 hold?
+    for t in (0, 74):
+        gg = torch.nan_to_num(dw[t * 128:(t + 1) * 128].double(), posinf=0.0, neginf=0.0)
+        for b in range(8):
+            gb = gg[:, b * 64:(b + 1) * 64]
+            best = (0.0, None)
+            for t2 in (t, t + 1, (t + 74) % 156, max(t - 74, 0)):
+                rr = dwh[t2 * 128:(t2 + 1) * 128]
+                for b2 in range(8):
+                    c = torch.nn.functional.cosine_similarity(gb.flatten(), rr[:, b2 * 64:(b2 + 1) * 64].flatten(), dim=0).item()
+                    if abs(c) > abs(best[0]): best = (c, (t2, b2))
+            print(f"   tile {t} block {b}: best match ref (tile, block) {best[1]} cos {best[0]:.3f}  |got| {gb.norm().item():.3e}")
 if mode == 7: cmp("t_j broadcast", dw, tj[:, None].expand(-1, D))
 if mode in (0, 4):
     ref = ((dwh - (tj[:, None] * wh if mode == 0 else 0)) / wn[:, None])

@@ -460,6 +460,7 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     su.lse = lse; su.zt = zt; su.grad_loss = grad_loss; su.dphi = W.dphi; su.lbl_local = W.lbl_local; su.xhat = W.xhat;
     su.xc = W.xc; su.cvec = W.cvec; su.probs = W.probs; su.ldB = W.Bp; su.s = s; su.B = (int)B; su.Bp = (int)W.Bp;
     su.Dp = (int)W.Dp; su.zero = dxhat; su.n_zero = B * W.Dp;
+    su.zero_t = W.tproj; su.n_t = Cs; su.zero_c = W.counters; su.n_c = (Cs + kBM - 1) / kBM;
     LaunchScope ls(ARCB_K_BWD_PREP, st);
     probs_setup_kernel<<<2 * device_sm_count(), 256, 0, st>>>(su);
     ARCB_CUDA(cudaGetLastError());
@@ -491,45 +492,19 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
   }
   {
-    // dW[Cs, D] = inv_norm (P'^T (c.x_hat) - t w_hat): clusters of two CTAs, one feature half each
-    CUtensorMap tmPt, tmXc;
-    bool ok = make_tmap_2d(&tmPt, W.probs, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W.Bp, Cs, W.Bp * 2, kBK, kBM);
-    ok = ok && make_tmap_mn3(&tmXc, W.xc, W.Dp, B, W.Dp * 2, kPwBN / 64);
-    if (!ok) return fail(ARCB_ERR_CUDA, "tensor maps for the dW kernel could not be encoded");
+    // dW[Cs, D] = inv_norm (P'^T (c.x_hat) - t w_hat): A = P'^T [Cs, Bp] K-major, B = c.x_hat [B, Dp] MN-major
     const bool dw_tma = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(dw) & 15) == 0) &&
                         make_tmap_2d(&tmDw, dw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, Cs, D * 4, 32, kBM);
     if (!dw_tma) tmDw = tmDx;
-    PwArgs ar;
-    ar.dw = dw; ar.what = W.what; ar.inv_nw = W.inv_nw; ar.Cs = (int)Cs; ar.D = (int)D; ar.Dp = (int)W.Dp;
-    ar.kb_total = (int)((B + kBK - 1) / kBK);
-    ar.tiles_m = (int)((Cs + kBM - 1) / kBM);
-    ar.debug = env_knobs().debug_epi;
-    static std::atomic<bool> attr_set[64];
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64) dev = 0;
-    if (!attr_set[dev].load(std::memory_order_acquire)) {
-      ARCB_CUDA(cudaFuncSetAttribute(dw_probs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PwSmem::kTotal));
-      attr_set[dev].store(true, std::memory_order_release);
-    }
-    int clusters = sms / 2;
-    if (clusters > ar.tiles_m) clusters = ar.tiles_m;
-    if (clusters < 1) clusters = 1;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * clusters);
-    cfg.blockDim = dim3(kGemmThreads);
-    cfg.dynamicSmemBytes = PwSmem::kTotal;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;  // the two CTAs only wait for each other: cluster scheduling suffices
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    Operand a{W.probs, Cs, B, W.Bp}, b{W.xc, W.Dp, B, W.Dp};
+    EpiDWT::Params ep;
+    ep.base = EpiDW::Params{dw, W.what, W.tproj, W.inv_nw, 0, (int)Cs, (int)D, (int)W.Dp, dw_tma ? 1 : 0};
+    ep.t_acc = W.tproj;
+    ep.arrivals = W.counters;
+    ep.slices = static_cast<int>((D + kBNTile - 1) / kBNTile);
     LaunchScope ls(ARCB_K_DW_GEMM, st);
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, dw_probs_kernel, tmPt, tmXc, tmDw, ar, dw_tma ? 1 : 0);
-    if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW kernel launch: %s", cudaGetErrorString(e));
+    const cudaError_t e = launch_gemm_row_slices<EpiDWT, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st);
+    if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
   }
   return ARCB_OK;
 }

@@ -657,4 +657,76 @@ struct EpiDW {
   __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
 };
 
+// Epilogue of the dW GEMM of the stored-probabilities backward (ARCB_KEEP_PROBS): the accumulator is
+//   dW_hat[j, n_blk * BN ..) = sum_i P'^T[j, i] (c_i x_hat_i)        (one BN-wide slice of the feature row)
+// and t_j = <w_hat_j, dW_hat_j> (the F.normalize backward, arc_main.py:159) is NOT known before this GEMM, unlike in
+// EpiDW.  The tiles run n-fastest (GemmSched::n_fastest) on a cooperative grid that is a multiple of tiles_n, so the
+// tiles_n slices of one class tile are in flight on neighbouring CTAs at the same time.  Pass 1 reduces this slice's
+// share of t_j and adds it to t[j] in global memory; the class tile's arrival counter tells when all slices have
+// contributed; pass 2 is EpiDW's.  A CTA waits only for its neighbours' pass 1 of the SAME tile index, which never
+// depends on this CTA's pass 2: no cycle.
+struct EpiDWT {
+  static constexpr int kSmemBytes = EpiDW::kSmemBytes;
+  static constexpr bool kUsesTmC = true;
+  struct Params {
+    EpiDW::Params base;      // base.t == t_acc
+    float* t_acc;            // [Cs] accumulators of t_j, zeroed before the launch
+    unsigned int* arrivals;  // [tiles_m], zeroed before the launch
+    int slices;              // tiles_n
+  };
+  using State = EpiOutState;
+  __device__ static void init(const Params&, State& st) { st.it = 0; }
+  __device__ static void drain(int epi_tid) { EpiDW::drain(epi_tid); }
+  template <int BN>
+  __device__ static void consume(const Params& q, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
+                                 int row_in_tile, int epi_tid, uint8_t* smem) {
+    const EpiDW::Params& p = q.base;
+    const int wg = epi_tid >> 7;
+    const int row_local = tc.m_blk * kBM + row_in_tile;
+    const bool valid = row_local < p.rows_valid;
+    const int cls = p.row_off + row_local;
+    const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
+    const int c_begin = wg * (BN / 2), c_end = (wg + 1) * (BN / 2);
+    EpiDW::RowData rd;
+    rd.inv = valid ? __ldg(p.inv_norm + cls) : 0.f;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) rd.w0[e] = make_uint4(0u, 0u, 0u, 0u);
+    float tpart = 0.f;
+    for (int c = c_begin; c < c_end; c += 32) {
+      const int col0 = tc.n_blk * BN + c;
+      if (col0 >= p.D) break;
+      uint4 wcur[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) wcur[e] = __ldg(reinterpret_cast<const uint4*>(wrow + col0) + e);
+      if (c == c_begin) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) rd.w0[e] = wcur[e];
+      }
+      float v[32];
+      tmem_ld32(taddr + c, v);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const uint32_t wr[4] = {wcur[e].x, wcur[e].y, wcur[e].z, wcur[e].w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          tpart = fmaf(v[e * 8 + 2 * h + 0], __uint_as_float(wr[h] << 16), tpart);
+          tpart = fmaf(v[e * 8 + 2 * h + 1], __uint_as_float(wr[h] & 0xffff0000u), tpart);
+        }
+      }
+    }
+    if (valid) atomicAdd(q.t_acc + cls, tpart);
+    named_bar_sync(1, kEpiThreads);  // every epilogue thread of the CTA has added its share
+    if (epi_tid == 0) {
+      __threadfence();
+      atomicAdd(q.arrivals + tc.m_blk, 1u);
+      wait_counter(q.arrivals + tc.m_blk, static_cast<unsigned>(q.slices), 0xd00u);
+    }
+    named_bar_sync(1, kEpiThreads);
+    rd.tj = valid ? __ldcg(p.t + cls) : 0.f;
+    EpiDW::consume_with<BN, 2>(p, st, tc, tmC, taddr, row_in_tile, epi_tid, smem, rd);
+  }
+  template <int BN>
+  __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
+};
+
 }  // namespace arcb

@@ -224,6 +224,7 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
   if (split_k > sc.kb_total) split_k = sc.kb_total;
   sc.kb_per_split = (sc.kb_total + split_k - 1) / split_k;
   sc.k_splits = (sc.kb_total + sc.kb_per_split - 1) / sc.kb_per_split;
+  sc.n_fastest = 0;
   const int total = ((sc.tiles_m + 1) / 2) * sc.tiles_n * sc.k_splits;
   if (total <= 0) return cudaSuccess;
   int pairs = device_sm_count() / 2;

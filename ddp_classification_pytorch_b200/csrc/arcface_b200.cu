@@ -460,7 +460,7 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     su.lse = lse; su.zt = zt; su.grad_loss = grad_loss; su.dphi = W.dphi; su.lbl_local = W.lbl_local; su.xhat = W.xhat;
     su.xc = W.xc; su.cvec = W.cvec; su.probs = W.probs; su.ldB = W.Bp; su.s = s; su.B = (int)B; su.Bp = (int)W.Bp;
     su.Dp = (int)W.Dp; su.zero = dxhat; su.n_zero = B * W.Dp;
-    su.zero_t = W.tproj; su.n_t = Cs; su.zero_c = W.counters; su.n_c = (Cs + kBM - 1) / kBM;
+    su.zero_t = W.tproj; su.n_t = Cs; su.zero_c = W.counters; su.n_c = (Cs + kBM - 1) / kBM + 1;
     LaunchScope ls(ARCB_K_BWD_PREP, st);
     probs_setup_kernel<<<2 * device_sm_count(), 256, 0, st>>>(su);
     ARCB_CUDA(cudaGetLastError());
@@ -497,13 +497,32 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
                         make_tmap_2d(&tmDw, dw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, Cs, D * 4, 32, kBM);
     if (!dw_tma) tmDw = tmDx;
     Operand a{W.probs, Cs, B, W.Bp}, b{W.xc, W.Dp, B, W.Dp};
-    EpiDWT::Params ep;
+    EpiDWT<true>::Params ep;
     ep.base = EpiDW::Params{dw, W.what, W.tproj, W.inv_nw, 0, (int)Cs, (int)D, (int)W.Dp, dw_tma ? 1 : 0};
     ep.t_acc = W.tproj;
     ep.arrivals = W.counters;
     ep.slices = static_cast<int>((D + kBNTile - 1) / kBNTile);
+    ep.debug = env_knobs().debug_epi;
+    // a CTA's next tile: the pair core walks the class tiles with a stride of (CTAs / slices) 128-row blocks
+    const int64_t blocks = (Cs + kBM - 1) / kBM;
+    int pairs = sms / 2;
+    if (pairs > ((blocks + 1) / 2) * ep.slices) pairs = static_cast<int>(((blocks + 1) / 2) * ep.slices);
+    pairs -= pairs % ep.slices;
+    ep.next_tile_blocks = 2 * pairs / ep.slices;
+    ep.m_blocks = static_cast<int>(2 * ((blocks + 1) / 2));
+    ep.pair = 1;
+    const bool direct = !dw_tma;
+    ep.debug &= 7;
     LaunchScope ls(ARCB_K_DW_GEMM, st);
-    const cudaError_t e = launch_gemm_row_slices<EpiDWT, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st);
+    cudaError_t e;
+    if (direct) {
+      EpiDWT<false>::Params ed;
+      static_assert(sizeof(ed) == sizeof(ep), "same parameter block");
+      memcpy(&ed, &ep, sizeof(ed));
+      e = launch_gemm_pair_row_slices<EpiDWT<false>, kBNTile, 5, false, true>(a, b, &tmDw, Cs, D, B, ed, st);
+    } else {
+      e = launch_gemm_pair_row_slices<EpiDWT<true>, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st);
+    }
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
   }
   return ARCB_OK;

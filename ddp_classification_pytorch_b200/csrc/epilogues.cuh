@@ -665,48 +665,102 @@ struct EpiDW {
 // share of t_j and adds it to t[j] in global memory; the class tile's arrival counter tells when all slices have
 // contributed; pass 2 is EpiDW's.  A CTA waits only for its neighbours' pass 1 of the SAME tile index, which never
 // depends on this CTA's pass 2: no cycle.
+// STAGED: dW leaves through swizzled staging buffers and bulk tensor stores (64 KB of shared memory); otherwise every
+// thread stores its 512 contiguous bytes of the row itself and the shared memory goes to two more operand stages.
+template <bool STAGED>
 struct EpiDWT {
-  static constexpr int kSmemBytes = EpiDW::kSmemBytes;
+  // w_hat slice of a tile, one row per class: 128 rows of up to 512 B, pitch 528 B (bank-conflict-free 16 B row reads)
+  static constexpr int kWPitch = 528;
+  static constexpr int kWOff = STAGED ? kChunkOutSmem : 0;
+  static constexpr int kWBarOff = kWOff + kBM * kWPitch;
+  static constexpr int kSmemBytes = kWBarOff + 16;
   static constexpr bool kUsesTmC = true;
   struct Params {
     EpiDW::Params base;      // base.t == t_acc
     float* t_acc;            // [Cs] accumulators of t_j, zeroed before the launch
     unsigned int* arrivals;  // [tiles_m], zeroed before the launch
     int slices;              // tiles_n
+    int next_tile_blocks;    // 128-row blocks between a CTA's consecutive tiles
+    int m_blocks;            // 128-row blocks the launch walks over (pair launches: rounded up to even)
+    int pair;                // 1: launched on the pair core (m_blk parity = CTA rank)
+    int debug;               // ARCB_DEBUG_EPI timing experiments (wrong results): 1 no stores, 2 no exchange, 3 neither, 4 no epilogue
   };
-  using State = EpiOutState;
-  __device__ static void init(const Params&, State& st) { st.it = 0; }
-  __device__ static void drain(int epi_tid) { EpiDW::drain(epi_tid); }
+  struct State {
+    int it;
+    int primed;
+    uint32_t wphase;
+  };
+  __device__ static void init(const Params&, State& st) {
+    st.it = 0;
+    st.primed = 0;
+    st.wphase = 0;
+  }
+  __device__ static void drain(int epi_tid) {
+    if (STAGED) EpiDW::drain(epi_tid);
+  }
+  // Bulk copies of the w_hat rows of class block `m_blk` into shared memory: the first warpgroup's thread r fetches row r.
+  // The barrier counts 128 arrivals; valid rows add their bytes to the transaction count.
+  template <int BN>
+  __device__ static void fetch_w(const Params& q, int m_blk, int n_blk, int epi_tid, uint8_t* smem) {
+    if (epi_tid >= kBM) return;
+    const EpiDW::Params& p = q.base;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + kWBarOff);
+    const int row_local = m_blk * kBM + epi_tid;
+    const int cols = min(BN, p.Dp - n_blk * BN);
+    if (row_local < p.rows_valid && cols > 0) {
+      mbar_arrive_expect_tx(bar, static_cast<uint32_t>(cols * 2));
+      bulk_load_1d(smem + kWOff + epi_tid * kWPitch,
+                   p.what + static_cast<int64_t>(p.row_off + row_local) * p.Dp + n_blk * BN, static_cast<uint32_t>(cols * 2),
+                   bar);
+    } else {
+      mbar_arrive(bar);
+    }
+  }
   template <int BN>
   __device__ static void consume(const Params& q, State& st, const TileCoord& tc, const CUtensorMap& tmC, uint32_t taddr,
                                  int row_in_tile, int epi_tid, uint8_t* smem) {
+    static_assert(BN == 256, "each epilogue thread keeps its 128 columns of w_hat in registers");
     const EpiDW::Params& p = q.base;
+    if (q.debug == 4) return;
     const int wg = epi_tid >> 7;
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const bool valid = row_local < p.rows_valid;
     const int cls = p.row_off + row_local;
-    const __nv_bfloat16* wrow = p.what + static_cast<int64_t>(valid ? cls : 0) * p.Dp;
-    const int c_begin = wg * (BN / 2), c_end = (wg + 1) * (BN / 2);
-    EpiDW::RowData rd;
-    rd.inv = valid ? __ldg(p.inv_norm + cls) : 0.f;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) rd.w0[e] = make_uint4(0u, 0u, 0u, 0u);
-    float tpart = 0.f;
-    for (int c = c_begin; c < c_end; c += 32) {
-      const int col0 = tc.n_blk * BN + c;
-      if (col0 >= p.D) break;
-      uint4 wcur[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) wcur[e] = __ldg(reinterpret_cast<const uint4*>(wrow + col0) + e);
-      if (c == c_begin) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) rd.w0[e] = wcur[e];
+    const int col_base = tc.n_blk * BN + wg * (BN / 2);  // first of this thread's 128 columns
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + kWBarOff);
+    if (!st.primed) {  // first tile of this CTA: nobody has fetched its w_hat rows yet
+      if (epi_tid == 0) {
+        mbar_init(wbar, kBM);
+        fence_mbar_init();
       }
+      named_bar_sync(1, kEpiThreads);
+      fetch_w<BN>(q, tc.m_blk, tc.n_blk, epi_tid, smem);
+      st.primed = 1;
+    }
+    const float inv = valid ? __ldg(p.inv_norm + cls) : 0.f;
+    mbar_wait(wbar, st.wphase, 0xd10u);
+    st.wphase ^= 1u;
+    uint4 w[16];
+    {
+      const uint4* ws = reinterpret_cast<const uint4*>(smem + kWOff + row_in_tile * kWPitch + wg * (BN / 2) * 2);
+#pragma unroll
+      for (int e = 0; e < 16; ++e) w[e] = (valid && col_base + e * 8 < p.Dp) ? ws[e] : make_uint4(0u, 0u, 0u, 0u);
+    }
+    named_bar_sync(1, kEpiThreads);  // the buffer has been read out: refill it with the rows of this CTA's NEXT tile
+    {
+      const int next_blk = tc.m_blk + q.next_tile_blocks;
+      if (next_blk - (q.pair ? (tc.m_blk & 1) : 0) < q.m_blocks) fetch_w<BN>(q, next_blk, tc.n_blk, epi_tid, smem);
+    }
+    float tpart = 0.f;
+#pragma unroll
+    for (int c = 0; c < BN / 2; c += 32) {
+      if (col_base + c >= p.D) break;
       float v[32];
-      tmem_ld32(taddr + c, v);
+      tmem_ld32(taddr + wg * (BN / 2) + c, v);
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const uint32_t wr[4] = {wcur[e].x, wcur[e].y, wcur[e].z, wcur[e].w};
+        const uint4 we = w[(c >> 3) + e];
+        const uint32_t wr[4] = {we.x, we.y, we.z, we.w};
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
           tpart = fmaf(v[e * 8 + 2 * h + 0], __uint_as_float(wr[h] << 16), tpart);
@@ -716,14 +770,53 @@ struct EpiDWT {
     }
     if (valid) atomicAdd(q.t_acc + cls, tpart);
     named_bar_sync(1, kEpiThreads);  // every epilogue thread of the CTA has added its share
-    if (epi_tid == 0) {
+    if (epi_tid == 0 && !(q.debug & 2)) {
       __threadfence();
       atomicAdd(q.arrivals + tc.m_blk, 1u);
       wait_counter(q.arrivals + tc.m_blk, static_cast<unsigned>(q.slices), 0xd00u);
     }
     named_bar_sync(1, kEpiThreads);
-    rd.tj = valid ? __ldcg(p.t + cls) : 0.f;
-    EpiDW::consume_with<BN, 2>(p, st, tc, tmC, taddr, row_in_tile, epi_tid, smem, rd);
+    float tj = valid ? __ldcg(q.t_acc + cls) : 0.f;
+    if (!(inv < 0.5e12f)) tj = 0.f;  // clamped rows take no projection
+#pragma unroll
+    for (int c = 0; c < BN / 2; c += 32) {
+      const int col0 = col_base + c;
+      if (col0 >= p.D) break;
+      float v[32];
+      tmem_ld32(taddr + wg * (BN / 2) + c, v);
+      float r[32];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const uint4 we = w[(c >> 3) + e];
+        const uint32_t wr[4] = {we.x, we.y, we.z, we.w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          r[e * 8 + 2 * h + 0] = inv * fmaf(-tj, __uint_as_float(wr[h] << 16), v[e * 8 + 2 * h + 0]);
+          r[e * 8 + 2 * h + 1] = inv * fmaf(-tj, __uint_as_float(wr[h] & 0xffff0000u), v[e * 8 + 2 * h + 1]);
+        }
+      }
+      if (q.debug & 1) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j2 = 0; j2 < 32; ++j2) acc += r[j2];
+        if (acc == 123.456f) p.dw[0] = acc;
+      } else if (STAGED && p.use_tma) {
+        chunk_out_tma<false, 2>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, r, col0, p.row_off + tc.m_blk * kBM);
+      } else if (valid) {
+        float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;
+        if ((p.D & 3) == 0 && col0 + 32 <= p.D) {
+#pragma unroll
+          for (int j2 = 0; j2 < 32; j2 += 4)
+            asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j2), "f"(r[j2]), "f"(r[j2 + 1]),
+                         "f"(r[j2 + 2]), "f"(r[j2 + 3])
+                         : "memory");
+        } else {
+#pragma unroll
+          for (int j2 = 0; j2 < 32; ++j2)
+            if (col0 + j2 < p.D) o[j2] = r[j2];
+        }
+      }
+    }
   }
   template <int BN>
   __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}

@@ -37,10 +37,19 @@ struct Gemm2Smem {
 __device__ __forceinline__ TileCoord decode_tile_pair(const GemmSched& sc, int t, int rank) {
   const int pairs_m = (sc.tiles_m + 1) >> 1;
   TileCoord c;
-  c.m_blk = (t % pairs_m) * 2 + rank;
-  int r = t / pairs_m;
-  c.n_blk = r % sc.tiles_n;
-  int ks = r / sc.tiles_n;
+  int r;
+  if (sc.n_fastest) {
+    c.n_blk = t % sc.tiles_n;
+    r = t / sc.tiles_n;
+    c.m_blk = (r % pairs_m) * 2 + rank;
+    r /= pairs_m;
+  } else {
+    c.m_blk = (t % pairs_m) * 2 + rank;
+    r = t / pairs_m;
+    c.n_blk = r % sc.tiles_n;
+    r /= sc.tiles_n;
+  }
+  const int ks = r;
   c.kb0 = ks * sc.kb_per_split;
   c.kb1 = min(c.kb0 + sc.kb_per_split, sc.kb_total);
   return c;
@@ -253,6 +262,65 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, sc, ep);
+}
+
+// Pair GEMM whose tiles_n column slices of one 256-row tile must be in flight TOGETHER on neighbouring pairs (EpiDWT
+// exchanges a per-row reduction between them): n-fastest tile order, a number of pairs that is a multiple of tiles_n,
+// no split-K, and a cooperative launch (on top of the cluster) so that every CTA a tile may wait for is resident.
+// cudaErrorCooperativeLaunchTooLarge & co.: nothing was enqueued.
+template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
+inline cudaError_t launch_gemm_pair_row_slices(const Operand& a, const Operand& b, const CUtensorMap* tmC_opt, int64_t M,
+                                               int64_t N, int64_t K, const typename Epi::Params& ep,
+                                               cudaStream_t stream) {
+  using L = Gemm2Smem<Epi, BN, STAGES>;
+  static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
+  CUtensorMap tmA, tmB, tmC;
+  bool ok = A_MN ? make_tmap_mn3(&tmA, a.ptr, a.mn_extent, a.k_extent, a.pitch_elems * 2, kBM / 64)
+                 : make_operand_tmap<false>(&tmA, a, kBM);
+  ok = ok && (B_MN ? make_tmap_mn3(&tmB, b.ptr, b.mn_extent, b.k_extent, b.pitch_elems * 2, BN / 128)
+                   : make_operand_tmap<false>(&tmB, b, BN / 2));
+  if (!ok) return cudaErrorInvalidValue;
+  if (tmC_opt) tmC = *tmC_opt; else tmC = tmA;
+  GemmSched sc;
+  sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
+  sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
+  sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
+  sc.kb_per_split = sc.kb_total;
+  sc.k_splits = 1;
+  sc.n_fastest = 1;
+  const int total = ((sc.tiles_m + 1) / 2) * sc.tiles_n;
+  if (total <= 0) return cudaSuccess;
+  int pairs = device_sm_count() / 2;
+  if (pairs > total) pairs = total;
+  pairs -= pairs % sc.tiles_n;
+  if (pairs < sc.tiles_n) return cudaErrorInvalidValue;
+  auto kern = gemm2_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN>;
+  static std::atomic<bool> attr_set[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!attr_set[dev].load(std::memory_order_acquire)) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+    if (e != cudaSuccess) return e;
+    attr_set[dev].store(true, std::memory_order_release);
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeCooperative;
+  attr[1].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, sc, ep);
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e;
 }
 
 }  // namespace arcb

@@ -40,7 +40,7 @@ struct GemmSched {
   int k_splits;
   int kb_total;      // number of kBK-blocks over the whole K extent
   int kb_per_split;  // ceil(kb_total / k_splits)
-  int n_fastest;     // tile order: 0 = m fastest (default), 1 = n fastest (EpiDWT: the slices of a row tile run side by side)
+  int n_fastest;     // pair core only: 1 = n fastest (EpiDWT: the column slices of a row tile run side by side)
 };
 
 // Work of the optional normaliser warps (NORM = true: warps 12..15, forward GEMM only): F.normalize(self.weight)
@@ -67,19 +67,10 @@ struct TileCoord {
 
 __device__ __forceinline__ TileCoord decode_tile(const GemmSched& sc, int t) {
   TileCoord c;
-  int r;
-  if (sc.n_fastest) {
-    c.n_blk = t % sc.tiles_n;
-    r = t / sc.tiles_n;
-    c.m_blk = r % sc.tiles_m;
-    r /= sc.tiles_m;
-  } else {
-    c.m_blk = t % sc.tiles_m;  // m fastest: CTAs running side by side share the same B tile via L2
-    r = t / sc.tiles_m;
-    c.n_blk = r % sc.tiles_n;
-    r /= sc.tiles_n;
-  }
-  const int ks = r;
+  c.m_blk = t % sc.tiles_m;  // m fastest: CTAs running side by side share the same B tile via L2
+  int r = t / sc.tiles_m;
+  c.n_blk = r % sc.tiles_n;
+  int ks = r / sc.tiles_n;
   c.kb0 = ks * sc.kb_per_split;
   c.kb1 = min(c.kb0 + sc.kb_per_split, sc.kb_total);
   return c;
@@ -455,55 +446,6 @@ inline cudaError_t launch_gemm_norm(const Operand& a, const Operand& b, int64_t 
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC_opt ? *tmC_opt : tmA, sc, ep, na);
-  if (e != cudaSuccess) (void)cudaGetLastError();
-  return e;
-}
-
-// GEMM whose tiles_n column slices of one row tile must be in flight TOGETHER (EpiDWT exchanges a per-row reduction
-// between them): n-fastest tile order, a grid that is a multiple of tiles_n, no split-K, and a cooperative launch so
-// that every CTA a tile may wait for is resident.  cudaErrorCooperativeLaunchTooLarge & co.: nothing was enqueued.
-template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
-inline cudaError_t launch_gemm_row_slices(const Operand& a, const Operand& b, const CUtensorMap* tmC_opt, int64_t M,
-                                          int64_t N, int64_t K, const typename Epi::Params& ep, cudaStream_t stream) {
-  using L = GemmSmem<Epi, BN, STAGES>;
-  static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
-  CUtensorMap tmA, tmB;
-  if (!make_operand_tmap<A_MN>(&tmA, a, kBM)) return cudaErrorInvalidValue;
-  if (!make_operand_tmap<B_MN>(&tmB, b, BN)) return cudaErrorInvalidValue;
-  GemmSched sc;
-  sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
-  sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
-  sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
-  sc.kb_per_split = sc.kb_total;
-  sc.k_splits = 1;
-  sc.n_fastest = 1;
-  const int total = sc.tiles_m * sc.tiles_n;
-  if (total <= 0) return cudaSuccess;
-  int grid = device_sm_count();
-  if (grid > total) grid = total;
-  grid -= grid % sc.tiles_n;
-  if (grid < sc.tiles_n) return cudaErrorInvalidValue;
-  auto kern = gemm_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN>;
-  static std::atomic<bool> attr_set[64];
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64) dev = 0;
-  if (!attr_set[dev].load(std::memory_order_acquire)) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
-    if (e != cudaSuccess) return e;
-    attr_set[dev].store(true, std::memory_order_release);
-  }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kGemmThreads);
-  cfg.dynamicSmemBytes = L::kTotal;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeCooperative;
-  attr[0].val.cooperative = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC_opt ? *tmC_opt : tmA, sc, ep, NormArgs{});
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e;
 }

@@ -343,7 +343,7 @@ def test_backward_from_stored_probabilities_matches_recompute_and_oracle(shape, 
     assert L.arcb_keep_probs_active(B, C, D, 30.0, _lib.KEEP_PROBS) == 1
     assert L.arcb_keep_probs_active(B, C, D, 30.0, 0) == 0 and L.arcb_keep_probs_active(B, C, D, 64.0, _lib.KEEP_PROBS) == 0
     out = {}
-    for name, flags in (("probs", _lib.KEEP_PROBS), ("recompute", 0)):
+    for name, flags in (("probs", _lib.KEEP_PROBS), ("probs1", _lib.KEEP_PROBS | _lib.BWD_SINGLE_CTA), ("recompute", 0)):
         head = _module(w.numpy(), 30.0, 0.5, easy, kernel_flags=flags)
         xg = x.cuda().requires_grad_(True)
         loss = head.forward_loss(xg, y.cuda(), want_top3=(name == "probs"))
@@ -351,6 +351,9 @@ def test_backward_from_stored_probabilities_matches_recompute_and_oracle(shape, 
         _sync_ok()
         out[name] = (loss.item(), xg.grad.clone(), head.weight.grad.clone(), head.aux["lse"].clone())
     p, r = out["probs"], out["recompute"]
+    assert out["probs1"][0] == p[0]  # the 1-CTA GEMM cores (ARCB_BWD_SINGLE_CTA) compute the same tiles
+    assert cosine_similarity(out["probs1"][2].cpu().numpy(), p[2].cpu().numpy()) >= 0.99999
+    assert cosine_similarity(out["probs1"][1].cpu().numpy(), p[1].cpu().numpy()) >= 0.99999
     assert p[0] == pytest.approx(r[0], rel=1e-4)
     torch.testing.assert_close(p[3], r[3], rtol=1e-4, atol=1e-4)
     assert cosine_similarity(p[1].cpu().numpy(), r[1].cpu().numpy()) >= 0.9995

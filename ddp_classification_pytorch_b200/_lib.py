@@ -65,7 +65,7 @@ BWD_PER_CHUNK = 0x10
 BWD_SINGLE_CTA = 0x20
 BWD_STATIC_SHARE = 0x40
 BWD_NO_COOP = 0x80  # profiling only
-KEEP_PROBS = 0x100
+BWD_RECOMPUTE = 0x100
 
 KERNEL_KINDS = [
     "l2norm_x", "l2norm_w", "target_prep", "fwd_gemm", "merge", "loss", "bwd_prep", "bwd_g_gemm", "dx_gemm",

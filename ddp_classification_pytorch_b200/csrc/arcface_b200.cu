@@ -144,20 +144,23 @@ struct Workspace {
   unsigned int* counters;  // [2 * ceil(Cs / 128)] chunk completion counters of the persistent backward
   int4* items;             // [items_cap][2] tile list of the persistent backward (bwd_items_kernel)
   int64_t items_cap;
-  __nv_bfloat16* probs;    // ARCB_KEEP_PROBS: P'^T [Cs, Bp] class-major, else nullptr
-  __nv_bfloat16* xc;       // ARCB_KEEP_PROBS: c (.) x_hat [B, Dp], the dW operand
-  float* cvec;             // ARCB_KEEP_PROBS: c_i [Bp]
-  float* bmax_p;           // ARCB_KEEP_PROBS: block maxima [2 * tiles_n][Bp] (the partials carry a fixed reference there)
+  __nv_bfloat16* probs;    // stored probabilities: P'^T [Cs, Bp] class-major, else nullptr
+  __nv_bfloat16* xc;       // stored probabilities: c (.) x_hat [B, Dp], the dW operand
+  float* cvec;             // stored probabilities: c_i [Bp]
+  float* bmax_p;           // stored probabilities: block maxima [2 * tiles_n][Bp] (the partials carry a fixed reference there)
   float* bmax;             // resident forward: block maxima [2 * tiles_n][Bp], second half of the `part` region
   int* fwd_mode;           // which forward filled the workspace (kFwd*): tells arcb_shard_top3 where the block maxima are
   int64_t total;
 };
 
-// Stored-probabilities schedule (ARCB_KEEP_PROBS): when it applies.  The forward must be the resident one, the feature
-// row must span exactly two 256-column halves (bwd_probs.cuh), and with the fixed reference s2 = s log2(e) every P' must
-// stay a normal bf16 number: 2^(-2 s2) >= 2^-126.  Otherwise the flag is ignored and the backward recomputes.
+// Stored-probabilities schedule (bwd_probs.cuh): when it applies.  The feature row must span exactly two 256-column
+// slices (EpiDWT), and with the fixed reference s2 = s log2(e) every P' must stay a normal bf16 number:
+// 2^(-2 s2) >= 2^-126.  Otherwise, or when a recompute schedule is asked for by flag, the backward recomputes.
+constexpr int kRecomputeFlags =
+    ARCB_BWD_RECOMPUTE | ARCB_BWD_PER_CHUNK | ARCB_BWD_SINGLE_CTA | ARCB_BWD_STATIC_SHARE | ARCB_FWD_PAIR;
+constexpr int kFwdKeptProbs = 0x100;  // OR-ed into the workspace's forward-schedule word: P'^T was stored
 bool keep_probs_applies(int64_t B, int64_t Cs, int64_t D, float s, int flags) {
-  if (!(flags & ARCB_KEEP_PROBS) || (flags & ARCB_FWD_PAIR)) return false;
+  if (flags & kRecomputeFlags) return false;
   if (D <= 256 || D > 512 || !(s > 0.f) || 2.f * s * 1.4426950408889634f > 120.f) return false;
   return B >= 128 && Cs >= 4096;  // small problems are launch bound either way: keep the default there
 }
@@ -279,7 +282,7 @@ int forward_common(const float* x, int64_t ldx, const float* w, int64_t ldw, con
   target_prep_kernel<<<blocks, 256, 0, st>>>(x, ldx, w, ldw, labels, W.xhat, (int)W.Dp, W.inv_nx, xvec, (int)B,
                                              (int)W.Bp, (int)D, Cs, class_offset, s, cos_m, sin_m, th, mm, easy,
                                              W.lbl_local, W.sub, W.zt, W.dphi, W.cos_t, W.counters, n_zero, W.fwd_mode,
-                                             fwd_mode);
+                                             fwd_mode | (keep_probs ? kFwdKeptProbs : 0));
   ARCB_CUDA(cudaGetLastError());
   *out_ws = W;
   return ARCB_OK;
@@ -451,7 +454,7 @@ int static_ws_address(void** out) {
 }  // namespace
 
 namespace {
-// Backward from the probabilities the forward kept (ARCB_KEEP_PROBS, bwd_probs.cuh): set-up, dX GEMM, dW kernel.
+// Backward from the probabilities the forward kept (bwd_probs.cuh): set-up, dX GEMM, dW kernel.
 int backward_from_probs(const Workspace& W, float s, const float* lse, const float* zt, const float* grad_loss, float* dw,
                         float* dxhat, int flags, cudaStream_t st) {
   const int64_t B = W.B, Cs = W.Cs, D = W.D;
@@ -460,7 +463,7 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     su.lse = lse; su.zt = zt; su.grad_loss = grad_loss; su.dphi = W.dphi; su.lbl_local = W.lbl_local; su.xhat = W.xhat;
     su.xc = W.xc; su.cvec = W.cvec; su.probs = W.probs; su.ldB = W.Bp; su.s = s; su.B = (int)B; su.Bp = (int)W.Bp;
     su.Dp = (int)W.Dp; su.zero = dxhat; su.n_zero = B * W.Dp;
-    su.zero_t = W.tproj; su.n_t = Cs; su.zero_c = W.counters; su.n_c = (Cs + kBM - 1) / kBM + 1;
+    su.zero_t = W.tproj; su.n_t = Cs; su.zero_c = W.counters; su.n_c = (Cs + kBM - 1) / kBM + 1; su.fwd_mode = W.fwd_mode;
     LaunchScope ls(ARCB_K_BWD_PREP, st);
     probs_setup_kernel<<<2 * device_sm_count(), 256, 0, st>>>(su);
     ARCB_CUDA(cudaGetLastError());
@@ -470,25 +473,16 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
   if (!make_tmap_2d(&tmDx, dxhat, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, D, B, W.Dp * 4, 32, kBM))
     return fail(ARCB_ERR_CUDA, "tensor map for dxhat could not be encoded (16-byte alignment?)");
   {
-    // dX_hat[B, D] = diag(c) P'[B, Cs] w_hat[Cs, D]: every CTA keeps ONE output tile in TMEM for its whole slice of the
-    // classes and reduce-adds it once at the end
+    // dX_hat[B, D] = diag(c) P'[B, Cs] w_hat[Cs, D] on the pair core: every CTA pair keeps ONE output tile in TMEM for
+    // its whole slice of the classes and reduce-adds it once at the end
     // A = P' as an MN-major operand: stored [k = classes, m = samples] with the samples contiguous
     Operand a{W.probs, W.Bp, Cs, W.Bp}, b{W.what, W.Dp, Cs, W.Dp};
-    const int tiles = static_cast<int>(((B + kBM - 1) / kBM) * ((D + kBNTile - 1) / kBNTile));
-    int split = sms / (tiles > 0 ? tiles : 1);
-    if (split < 1) split = 1;
     EpiRedAdd::Params ep{(int)B, (int)D, W.cvec};
     LaunchScope ls(ARCB_K_DX_GEMM, st);
-    cudaError_t e;
-    if (flags & ARCB_BWD_SINGLE_CTA) {
-      e = launch_gemm<EpiRedAdd, kBNTile, 3, true, true>(a, b, &tmDx, B, D, Cs, split, ep, st);
-    } else {
-      b.mn_extent = W.Dp;
-      const int ptiles = static_cast<int>(((B + 2 * kBM - 1) / (2 * kBM)) * ((D + kBNTile - 1) / kBNTile));
-      int psplit = (sms / 2) / (ptiles > 0 ? ptiles : 1);
-      if (psplit < 1) psplit = 1;
-      e = launch_gemm_pair<EpiRedAdd, kBNTile, 5, true, true>(a, b, &tmDx, B, D, Cs, psplit, ep, st);
-    }
+    const int ptiles = static_cast<int>(((B + 2 * kBM - 1) / (2 * kBM)) * ((D + kBNTile - 1) / kBNTile));
+    int psplit = (sms / 2) / (ptiles > 0 ? ptiles : 1);
+    if (psplit < 1) psplit = 1;
+    const cudaError_t e = launch_gemm_pair<EpiRedAdd, kBNTile, 5, true, true>(a, b, &tmDx, B, D, Cs, psplit, ep, st);
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
   }
   {
@@ -512,6 +506,7 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     ep.m_blocks = static_cast<int>(2 * ((blocks + 1) / 2));
     ep.pair = 1;
     const bool direct = !dw_tma;
+    const bool coop = !(flags & ARCB_BWD_NO_COOP);  // profiling only, see the header
     ep.debug &= 7;
     LaunchScope ls(ARCB_K_DW_GEMM, st);
     cudaError_t e;
@@ -519,9 +514,9 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
       EpiDWT<false>::Params ed;
       static_assert(sizeof(ed) == sizeof(ep), "same parameter block");
       memcpy(&ed, &ep, sizeof(ed));
-      e = launch_gemm_pair_row_slices<EpiDWT<false>, kBNTile, 5, false, true>(a, b, &tmDw, Cs, D, B, ed, st);
+      e = launch_gemm_pair_row_slices<EpiDWT<false>, kBNTile, 5, false, true>(a, b, &tmDw, Cs, D, B, ed, st, coop);
     } else {
-      e = launch_gemm_pair_row_slices<EpiDWT<true>, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st);
+      e = launch_gemm_pair_row_slices<EpiDWT<true>, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st, coop);
     }
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
   }
@@ -969,7 +964,7 @@ int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64
                               int easy_margin, float* stats, void* stream) {
   int rc = check_dims(B, Cs, D);
   if (rc) return rc;
-  const int64_t need = carve(nullptr, B, Cs, D).total;
+  const int64_t need = carve(nullptr, B, Cs, D).total;  // forward only: nothing is kept for a backward
   if (need > kStaticWsBytes)
     return fail(ARCB_ERR_WORKSPACE,
                 "arcb_shard_forward_static: B=%lld, Cs=%lld, D=%lld needs %lld bytes of workspace but the built-in "
@@ -981,7 +976,7 @@ int arcb_shard_forward_static(const float* x, int64_t ldx, const float* w, int64
   // Nothing in the forward workspace has to start from zero: every region is fully rewritten
   // (normalised operands incl. their padding, per-sample target data, per-tile partials) before it is read.
   return arcb_shard_forward(x, ldx, w, ldw, labels, B, Cs, D, class_offset, s, m, easy_margin, ws, kStaticWsBytes,
-                            stats, 0, stream);
+                            stats, ARCB_BWD_RECOMPUTE, stream);
 }
 
 int arcb_shard_logits(const float* x, int64_t ldx, const float* w, int64_t ldw, const int64_t* labels, int64_t B,

@@ -41,9 +41,12 @@ struct ProbsSetup {
   long long n_t;
   unsigned int* zero_c;    // [n_c] class-tile arrival counters of EpiDWT
   long long n_c;
+  const int* fwd_mode;     // the workspace's forward-schedule word: bit 8 = this forward stored P'^T
 };
 
 __global__ void __launch_bounds__(256) probs_setup_kernel(const ProbsSetup su) {
+  // a forward run with other flags left no probabilities in this workspace: abort instead of using stale memory
+  if (!(*su.fwd_mode & 0x100)) watchdog_abort(0xbad0u, static_cast<uint32_t>(*su.fwd_mode));
   const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long nthr = static_cast<long long>(gridDim.x) * blockDim.x;
   const int lane = threadIdx.x & 31;

@@ -271,7 +271,7 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
 template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
 inline cudaError_t launch_gemm_pair_row_slices(const Operand& a, const Operand& b, const CUtensorMap* tmC_opt, int64_t M,
                                                int64_t N, int64_t K, const typename Epi::Params& ep,
-                                               cudaStream_t stream) {
+                                               cudaStream_t stream, bool cooperative = true) {
   using L = Gemm2Smem<Epi, BN, STAGES>;
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
   CUtensorMap tmA, tmB, tmC;
@@ -317,7 +317,7 @@ inline cudaError_t launch_gemm_pair_row_slices(const Operand& a, const Operand& 
   attr[1].id = cudaLaunchAttributeCooperative;
   attr[1].val.cooperative = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 2;
+  cfg.numAttrs = cooperative ? 2 : 1;
   const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, sc, ep);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e;

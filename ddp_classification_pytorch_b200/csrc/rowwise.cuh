@@ -570,7 +570,7 @@ topk_rescore_kernel(const float* __restrict__ x, int64_t ldx, const float* __res
                     int64_t* __restrict__ top_idx) {
   // where the forward left the block maxima: the per-tile partials themselves (streaming schedule) or the separate
   // array of the resident schedule; a resident forward that was not asked to keep them cannot serve this kernel
-  const int mode = *fwd_mode;
+  const int mode = *fwd_mode & 0xff;  // (bit 8: the forward also kept its probabilities)
   if (mode == kFwdResident) __trap();  // arcb_shard_top3 after a forward without ARCB_FWD_BLOCK_MAXIMA: fail loudly
   const float* bm = (mode == kFwdStreaming) ? reinterpret_cast<const float*>(part) : bmax;
   const int bm_step = (mode == kFwdStreaming) ? 2 : 1;

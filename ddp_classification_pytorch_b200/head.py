@@ -412,6 +412,9 @@ class _FusedLossFn(torch.autograd.Function):
         B = xc.shape[0]
         if cfg.get("wcache") is not None:
             cfg = dict(cfg, w_tag=(w.data_ptr(), w._version))
+        if not (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]):
+            # no backward will follow (evaluation): the forward need not keep its probabilities for one
+            cfg = dict(cfg, flags=int(cfg.get("flags", 0)) | _lib.BWD_RECOMPUTE)
         peer = cfg["peer_factory"](B, xc.device) if (P > 1 and cfg.get("peer_factory") is not None) else None
         if peer is not None:  # the exchange is done by the merge / loss kernels themselves over NVLink peer memory
             px, gathered, flags_ptr = peer.next_exchange()

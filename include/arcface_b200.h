@@ -47,21 +47,26 @@ extern "C" {
 #define ARCB_FWD_STREAMING 0x8     /* never use the x_hat-resident schedule (default for Dp <= 512 and many classes: a
                                       CTA keeps its 128 samples in shared memory and only w_hat streams) */
 #define ARCB_FWD_BLOCK_MAXIMA 0x200 /* keep the per-128-class block maxima: REQUIRED by a following arcb_shard_top3 */
-/* arcb_shard_backward: schedule.  Default: ONE persistent cooperative kernel whose CTA pairs (cta_group::2, 256 x 256
- * tile per pair of SMs) claim tiles from the global tile list as they go.  All schedules give the same gradients. */
-#define ARCB_BWD_PER_CHUNK 0x10    /* one launch per GEMM and class chunk (no co-residency needed) */
-#define ARCB_BWD_SINGLE_CTA 0x20   /* persistent kernel with one CTA per 128 x 256 tile (what ncu can replay) */
-#define ARCB_BWD_STATIC_SHARE 0x40 /* persistent kernel, fixed share of the tile list per CTA pair (A/B runs) */
-#define ARCB_BWD_NO_COOP 0x80      /* PROFILING ONLY: default kernel launched without the cooperative attribute (ncu cannot
+/* arcb_shard_backward: schedule.  Default: from stored probabilities where that applies (below), else the recompute
+ * schedule: ONE persistent cooperative kernel whose CTA pairs (cta_group::2, 256 x 256 tile per pair of SMs) claim G / dX /
+ * dW tiles from the global tile list as they go.  The next three flags pick other variants of the recompute schedule (and
+ * imply ARCB_BWD_RECOMPUTE).  All schedules give the same gradients within the parity tolerance. */
+#define ARCB_BWD_PER_CHUNK 0x10    /* recompute, one launch per GEMM and class chunk (no co-residency needed) */
+#define ARCB_BWD_SINGLE_CTA 0x20   /* recompute, persistent kernel with one CTA per 128 x 256 tile */
+#define ARCB_BWD_STATIC_SHARE 0x40 /* recompute, persistent kernel, fixed share of the tile list per CTA pair (A/B runs) */
+#define ARCB_BWD_NO_COOP 0x80      /* PROFILING ONLY: default kernels launched without the cooperative attribute (ncu cannot
                                       replay cooperative + cluster launches).  Safe only on an otherwise idle GPU, where
                                       one CTA per SM is co-resident anyway; never set it in production. */
-/* arcb_ws_bytes + arcb_shard_forward* + arcb_shard_backward (the SAME flag in all three): the forward keeps the softmax
- * numerators P' = bf16(2^(s log2e (cos - 1))) of the whole shard in the workspace ([B, Cs] bf16: 2 GB at B = 1024,
- * Cs = 1M) and the backward runs as two plain GEMMs on them instead of recomputing the logits tile by tile: 6 B C D
- * executed flops instead of 8 B C D, paid for with 2 B C bytes of HBM per pass.  Applies where the resident forward does,
- * for 256 < D <= 512 and s <= 41 (arcb_keep_probs_active tells); elsewhere the flag is ignored and the default
- * recompute backward runs.  Same gradients within the parity tolerance either way. */
-#define ARCB_KEEP_PROBS 0x100
+/* Stored probabilities (the default where it applies).  The forward keeps the softmax numerators
+ * P' = bf16(2^(s log2e (cos - 1))) of the whole shard in the workspace, class-major ([Cs, B] bf16: 2 GB at B = 1024,
+ * Cs = 1M), and the backward runs as two plain GEMMs on them (dX, dW) instead of recomputing the logits tile by tile:
+ * 6 B C D executed flops instead of 8 B C D, paid for with 2 B C bytes of HBM per pass.  Applies for 256 < D <= 512,
+ * s <= 41, B >= 128 and >= 4096 classes per shard (arcb_keep_probs_active tells); elsewhere, and whenever one of the
+ * recompute-schedule flags above or ARCB_FWD_PAIR is given, the backward recomputes.  Same gradients within the parity
+ * tolerance either way.  arcb_ws_bytes, arcb_shard_forward* and arcb_shard_backward must be given the SAME flags: the
+ * workspace layout and what the forward leaves for the backward depend on them (a backward that expects probabilities the
+ * forward did not store is caught by a device-side check: its first kernel traps, arcb_stream_check reports it). */
+#define ARCB_BWD_RECOMPUTE 0x100 /* never keep probabilities (forward-only callers: saves the 2 B C bytes of stores) */
 /* arcb_gemm_bf16 (unit tests of the GEMM core) */
 #define ARCB_GEMM_PAIR 0x4         /* CTA-pair core (same bit as ARCB_FWD_PAIR) */
 
@@ -99,7 +104,7 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
 /* Bytes of persistent workspace a shard needs between forward and backward, for calls made with `flags`. */
 int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D, int flags);
 
-/* 1 when calls with these sizes, scale and flags use the stored-probabilities schedule (ARCB_KEEP_PROBS), else 0.
+/* 1 when calls with these sizes, scale and flags use the stored-probabilities schedule (see ARCB_BWD_RECOMPUTE), else 0.
  * In that case arcb_shard_backward needs no scratch (scratch may be NULL / scratch_bytes 0). */
 int arcb_keep_probs_active(int64_t B, int64_t Cs, int64_t D, float s, int flags);
 

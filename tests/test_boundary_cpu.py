@@ -33,10 +33,16 @@ def test_size_queries_without_gpu(built):
     L = built
     assert L.arcb_version() >= 20000
     assert L.arcb_padded_dim(512) == 512 and L.arcb_padded_dim(72) == 128
-    ws = L.arcb_ws_bytes(1024, 1_000_000, 512, 0)
+    ws = L.arcb_ws_bytes(1024, 1_000_000, 512, _lib.BWD_RECOMPUTE)
     assert ws == L.arcb_ws_bytes(1024, 1_000_000, 512, _lib.BWD_PER_CHUNK | _lib.FWD_NORM_FUSED)  # pure in its arguments
     # dominated by the bf16 copy of the normalised weight (2 B/elem) + per-tile softmax partials
     assert 1_000_000 * 512 * 2 < ws < 1_000_000 * 512 * 2 * 1.1
+    # the default for this shape keeps the bf16 softmax numerators P'^T [Cs, B] for the backward on top of that
+    kept = L.arcb_ws_bytes(1024, 1_000_000, 512, 0) - ws
+    assert L.arcb_keep_probs_active(1024, 1_000_000, 512, 30.0, 0) == 1
+    assert 1_000_000 * 1024 * 2 <= kept < 1_000_000 * 1024 * 2 * 1.03  # + block maxima, c (.) x_hat
+    assert L.arcb_keep_probs_active(1024, 1_000_000, 256, 30.0, 0) == 0
+    assert L.arcb_ws_bytes(1024, 1_000_000, 256, 0) == L.arcb_ws_bytes(1024, 1_000_000, 256, _lib.BWD_RECOMPUTE)
     assert L.arcb_scratch_bytes(1024, 128 * 148) == 128 * 148 * 1024 * 2
     assert L.arcb_ws_bytes(0, 10, 10, 0) < 0
     assert L.arcb_launch_count() == 0

@@ -496,7 +496,6 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     ep.t_acc = W.tproj;
     ep.arrivals = W.counters;
     ep.slices = static_cast<int>((D + kBNTile - 1) / kBNTile);
-    ep.debug = env_knobs().debug_epi;
     // a CTA's next tile: the pair core walks the class tiles with a stride of (CTAs / slices) 128-row blocks
     const int64_t blocks = (Cs + kBM - 1) / kBM;
     int pairs = sms / 2;
@@ -507,7 +506,6 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     ep.pair = 1;
     const bool direct = !dw_tma;
     const bool coop = !(flags & ARCB_BWD_NO_COOP);  // profiling only, see the header
-    ep.debug &= 7;
     LaunchScope ls(ARCB_K_DW_GEMM, st);
     cudaError_t e;
     if (direct) {

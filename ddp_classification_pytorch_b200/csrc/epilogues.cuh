@@ -214,10 +214,15 @@ struct EpiFwdStatsP {
     bool any = false;
     const int col_base = tc.n_blk * BN;
     uint8_t* buf = smem + wg * (64 * 256);
-    // my column inside the staging tile: box (64 samples) and the 2 bytes inside a 128-byte class row
-    const uint32_t sbox = smem_u32(buf) + static_cast<uint32_t>(row_in_tile >> 6) * (64 * 128);
-    const uint32_t scol = static_cast<uint32_t>(row_in_tile & 63) * 2;  // byte inside the row
-    const uint32_t chunk16 = scol >> 4, within = scol & 15;
+    // my column inside the staging tile: box (64 samples) and the 2 bytes inside a 128-byte class row; the 16-byte chunk
+    // is XOR-swizzled with (class row & 7): eight addresses cover every row
+    uint32_t soff[8];
+    {
+      const uint32_t sbox = smem_u32(buf) + static_cast<uint32_t>(row_in_tile >> 6) * (64 * 128);
+      const uint32_t scol = static_cast<uint32_t>(row_in_tile & 63) * 2;  // byte inside the row
+#pragma unroll
+      for (uint32_t k = 0; k < 8; ++k) soff[k] = sbox + (((scol >> 4) ^ k) << 4) + (scol & 15);
+    }
 #pragma unroll 1
     for (int bx = 0; bx < BN / 128; ++bx) {  // this warpgroup's two groups of 64 classes
       const int cls0 = col_base + wg * (BN / 2) + bx * 64;
@@ -255,18 +260,21 @@ struct EpiFwdStatsP {
           blk_m = fmaxf(blk_m, cm);
         }
         float a0 = 0.f, a1 = 0.f;
+        const uint32_t hrow = static_cast<uint32_t>(h) * (32 * 128);  // class rows h * 32 + j of the staging tile
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
+          const float e0 = ex2_approx(fmaf(v[j], p.s2, -p.s2)), e1 = ex2_approx(fmaf(v[j + 1], p.s2, -p.s2));
+          a0 += e0;
+          a1 += e1;
           // padding samples (row >= B) must contribute nothing to dW: their column of P'^T is zero
-          const uint32_t pk = row_ok ? pack_bf16x2(ex2_approx(fmaf(v[j], p.s2, -p.s2)), ex2_approx(fmaf(v[j + 1], p.s2, -p.s2))) : 0u;
-          a0 += __uint_as_float(pk << 16);  // the rounded values: what the backward will use
-          a1 += __uint_as_float(pk & 0xffff0000u);
-          // class rows (h * 32 + j) and (h * 32 + j + 1) of the staging tile, my column
-          const uint32_t r0 = static_cast<uint32_t>(h * 32 + j), r1 = r0 + 1;
-          const uint32_t a_lo = sbox + r0 * 128 + ((chunk16 ^ (r0 & 7)) << 4) + within;
-          const uint32_t a_hi = sbox + r1 * 128 + ((chunk16 ^ (r1 & 7)) << 4) + within;
-          asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_lo), "h"(static_cast<unsigned short>(pk & 0xffffu)) : "memory");
-          asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_hi), "h"(static_cast<unsigned short>(pk >> 16)) : "memory");
+          const uint32_t pk = row_ok ? pack_bf16x2(e0, e1) : 0u;
+          // (the row offsets are compile-time constants after unrolling: they fold into the store's immediate)
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(soff[j & 7] + hrow + static_cast<uint32_t>(j * 128)),
+                       "h"(static_cast<unsigned short>(pk & 0xffffu))
+                       : "memory");
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(soff[(j + 1) & 7] + hrow + static_cast<uint32_t>((j + 1) * 128)),
+                       "h"(static_cast<unsigned short>(pk >> 16))
+                       : "memory");
         }
         run_l += a0 + a1;
       }
@@ -683,7 +691,6 @@ struct EpiDWT {
     int next_tile_blocks;    // 128-row blocks between a CTA's consecutive tiles
     int m_blocks;            // 128-row blocks the launch walks over (pair launches: rounded up to even)
     int pair;                // 1: launched on the pair core (m_blk parity = CTA rank)
-    int debug;               // ARCB_DEBUG_EPI timing experiments (wrong results): 1 no stores, 2 no exchange, 3 neither, 4 no epilogue
   };
   struct State {
     int it;
@@ -721,7 +728,6 @@ struct EpiDWT {
                                  int row_in_tile, int epi_tid, uint8_t* smem) {
     static_assert(BN == 256, "each epilogue thread keeps its 128 columns of w_hat in registers");
     const EpiDW::Params& p = q.base;
-    if (q.debug == 4) return;
     const int wg = epi_tid >> 7;
     const int row_local = tc.m_blk * kBM + row_in_tile;
     const bool valid = row_local < p.rows_valid;
@@ -770,7 +776,7 @@ struct EpiDWT {
     }
     if (valid) atomicAdd(q.t_acc + cls, tpart);
     named_bar_sync(1, kEpiThreads);  // every epilogue thread of the CTA has added its share
-    if (epi_tid == 0 && !(q.debug & 2)) {
+    if (epi_tid == 0) {
       __threadfence();
       atomicAdd(q.arrivals + tc.m_blk, 1u);
       wait_counter(q.arrivals + tc.m_blk, static_cast<unsigned>(q.slices), 0xd00u);
@@ -795,12 +801,7 @@ struct EpiDWT {
           r[e * 8 + 2 * h + 1] = inv * fmaf(-tj, __uint_as_float(wr[h] & 0xffff0000u), v[e * 8 + 2 * h + 1]);
         }
       }
-      if (q.debug & 1) {
-        float acc = 0.f;
-#pragma unroll
-        for (int j2 = 0; j2 < 32; ++j2) acc += r[j2];
-        if (acc == 123.456f) p.dw[0] = acc;
-      } else if (STAGED && p.use_tma) {
+      if (STAGED && p.use_tma) {
         chunk_out_tma<false, 2>(tmC, smem, wg, epi_tid & 127, row_in_tile, st.it++, r, col0, p.row_off + tc.m_blk * kBM);
       } else if (valid) {
         float* o = p.dw + static_cast<int64_t>(cls) * p.D + col0;

@@ -61,7 +61,7 @@ extern "C" {
  * P' = bf16(2^(s log2e (cos - 1))) of the whole shard in the workspace, class-major ([Cs, B] bf16: 2 GB at B = 1024,
  * Cs = 1M), and the backward runs as two plain GEMMs on them (dX, dW) instead of recomputing the logits tile by tile:
  * 6 B C D executed flops instead of 8 B C D, paid for with 2 B C bytes of HBM per pass.  Applies for 256 < D <= 512,
- * s <= 41, B >= 128 and >= 4096 classes per shard (arcb_keep_probs_active tells); elsewhere, and whenever one of the
+ * s <= 41, B >= 128 and B * Cs >= 2^24 logits per shard (arcb_keep_probs_active tells); elsewhere, and whenever one of the
  * recompute-schedule flags above or ARCB_FWD_PAIR is given, the backward recomputes.  Same gradients within the parity
  * tolerance either way.  arcb_ws_bytes, arcb_shard_forward* and arcb_shard_backward must be given the SAME flags: the
  * workspace layout and what the forward leaves for the backward depend on them (a backward that expects probabilities the

@@ -181,7 +181,7 @@ int arcb_dx_peer_reduce(const float* x, int64_t ldx, int64_t B, int64_t D, const
  * (no cudaMalloc / cudaFree, no allocating library routine): the workspace is a fixed ARCB_STATIC_WS_BYTES block
  * that is part of the library image on every GPU that loads it (held until the process exits).
  *   - Arguments and the stats output are exactly those of arcb_shard_forward, minus ws / ws_bytes.
- *   - Sizes whose workspace (arcb_ws_bytes(B, Cs, D, 0)) exceeds ARCB_STATIC_WS_BYTES are rejected with
+ *   - Sizes whose workspace (arcb_ws_bytes(B, Cs, D, ARCB_BWD_RECOMPUTE)) exceeds ARCB_STATIC_WS_BYTES are rejected with
  *     ARCB_ERR_WORKSPACE and a message naming both numbers; nothing is launched.  (32 MiB covers e.g.
  *     B=256, Cs=16384, D=512 or B=1024, Cs=8192, D=1024.)
  *   - The first call on each device looks up the block's device address (with that device current) and caches
@@ -189,7 +189,8 @@ int arcb_dx_peer_reduce(const float* x, int64_t ldx, int64_t B, int64_t D, const
  *     when the library's device code is loaded on that GPU (with lazy loading: at the first call into the library
  *     there), so a host that freezes its memory plan should make one library call per device during start-up, before
  *     the freeze; the cached address does not survive cudaDeviceReset().
- *   - Arguments are those of arcb_shard_forward with flags = 0 (library defaults).
+ *   - Arguments are those of arcb_shard_forward with flags = ARCB_BWD_RECOMPUTE (forward only: nothing is kept for
+ *     a backward; otherwise the library defaults).
  *   - All calls on a device share the one block: two calls whose kernels overlap on the GPU (different streams,
  *     or different host threads) race on it -- serialise them.  The block keeps the previous call's contents;
  *     the forward rewrites every region before reading it, so nothing needs clearing between calls.

@@ -61,6 +61,7 @@ FWD_PAIR = 0x4
 FWD_STREAMING = 0x8
 FWD_BLOCK_MAXIMA = 0x200
 GEMM_PAIR = 0x4
+GEMM_PAIR_WIDE = 0x8
 BWD_PER_CHUNK = 0x10
 BWD_SINGLE_CTA = 0x20
 BWD_STATIC_SHARE = 0x40

@@ -481,10 +481,12 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     Operand a{W.probs, W.Bp, Cs, W.Bp}, b{W.what, W.Dp, Cs, W.Dp};
     EpiRedAdd::Params ep{(int)B, (int)D, W.cvec};
     LaunchScope ls(ARCB_K_DX_GEMM, st);
-    const int ptiles = static_cast<int>(((B + 2 * kBM - 1) / (2 * kBM)) * ((D + kBNTile - 1) / kBNTile));
+    // wide tiles: a pair owns 256 samples x the WHOLE feature row (two 256-column accumulators = all of TMEM), so that
+    // every element of P'^T is fetched by exactly one pair
+    const int ptiles = static_cast<int>(((B + 2 * kBM - 1) / (2 * kBM)) * ((D + 2 * kBNTile - 1) / (2 * kBNTile)));
     int psplit = (sms / 2) / (ptiles > 0 ? ptiles : 1);
     if (psplit < 1) psplit = 1;
-    const cudaError_t e = launch_gemm_pair<EpiRedAdd, kBNTile, 5, true, true>(a, b, &tmDx, B, D, Cs, psplit, ep, st);
+    const cudaError_t e = launch_gemm_pair<EpiRedAdd, kBNTile, 3, true, true, 2>(a, b, &tmDx, B, D, Cs, psplit, ep, st);
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dX GEMM launch: %s", cudaGetErrorString(e));
   }
   {
@@ -653,6 +655,10 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
       return fail(ARCB_ERR_INVALID, "pair GEMM: an MN-major operand needs a leading dimension that is a multiple of 64");
     if (a_mn) a.mn_extent = lda;
     if (b_mn) b.mn_extent = ldb;
+    if (effective_flags(flags) & ARCB_GEMM_PAIR_WIDE) {  // two column tiles per pair tile (the dX GEMM of the backward)
+      if (!(a_mn && b_mn)) return fail(ARCB_ERR_INVALID, "wide pair GEMM: built for MN-major operands only");
+      e = launch_gemm_pair<EpiStore, 256, 4, true, true, 2>(a, b, nullptr, M, N, K, split_k, ep, st);
+    } else
     if (!a_mn && !b_mn) e = launch_gemm_pair<EpiStore, 256, 6, false, false>(a, b, nullptr, M, N, K, split_k, ep, st);
     else if (a_mn && !b_mn) e = launch_gemm_pair<EpiStore, 256, 6, true, false>(a, b, nullptr, M, N, K, split_k, ep, st);
     else if (!a_mn && b_mn) e = launch_gemm_pair<EpiStore, 256, 6, false, true>(a, b, nullptr, M, N, K, split_k, ep, st);

@@ -22,10 +22,14 @@
 
 namespace arcb {
 
-template <class Epi, int BN, int STAGES>
+// NSUB = 2 ("wide" tiles): a pair works on TWO neighbouring BN-wide column tiles at once -- one A stage feeds two MMAs,
+// the two accumulators fill all 512 TMEM columns (no double buffering: meant for split-K launches where a pair has ONE
+// output tile for its whole life), and A is fetched once instead of once per column tile.
+template <class Epi, int BN, int STAGES, int NSUB = 1>
 struct Gemm2Smem {
   static constexpr int kABytes = kBM * kBK * 2;        // this CTA's 128 rows of A
-  static constexpr int kBBytes = (BN / 2) * kBK * 2;   // this CTA's half of the B tile
+  static constexpr int kBSubBytes = (BN / 2) * kBK * 2;  // this CTA's half of one B tile
+  static constexpr int kBBytes = NSUB * kBSubBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kEpiOff = STAGES * kStageBytes;
   static constexpr int kBarOff = kEpiOff + Epi::kSmemBytes;
@@ -55,12 +59,14 @@ __device__ __forceinline__ TileCoord decode_tile_pair(const GemmSched& sc, int t
   return c;
 }
 
-template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
+template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN, int NSUB = 1>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                    const __grid_constant__ CUtensorMap tmC, const GemmSched sc, const typename Epi::Params ep) {
-  using L = Gemm2Smem<Epi, BN, STAGES>;
+  using L = Gemm2Smem<Epi, BN, STAGES, NSUB>;
   static_assert(BN == 256, "pair MMA: N = 256 (128 rows of B per CTA)");
+  static_assert(NSUB == 1 || NSUB == 2, "one or two column tiles per pair tile");
+  constexpr int kAccStages = 2 / NSUB;  // NSUB = 2: both accumulators belong to the same tile
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* full = bars;
@@ -123,12 +129,16 @@ gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           } else {
             tma_load_3d_pair(sa, &tmA, full_leader, 0, kb * kBK, tc.m_blk * (kBM / 64), kEvictNormal);
           }
-          if constexpr (!B_MN) {
-            tma_load_2d_pair(sb, &tmB, full_leader, kb * kBK, tc.n_blk * BN + static_cast<int>(rank) * (BN / 2),
-                             kEvictNormal);
-          } else {
-            tma_load_3d_pair(sb, &tmB, full_leader, 0, kb * kBK,
-                             tc.n_blk * (BN / 64) + static_cast<int>(rank) * (BN / 128), kEvictNormal);
+#pragma unroll
+          for (int j = 0; j < NSUB; ++j) {  // column tile n_blk * NSUB + j (out-of-range boxes arrive as zeros)
+            const int nb = tc.n_blk * NSUB + j;
+            if constexpr (!B_MN) {
+              tma_load_2d_pair(sb + j * L::kBSubBytes, &tmB, full_leader, kb * kBK,
+                               nb * BN + static_cast<int>(rank) * (BN / 2), kEvictNormal);
+            } else {
+              tma_load_3d_pair(sb + j * L::kBSubBytes, &tmB, full_leader, 0, kb * kBK,
+                               nb * (BN / 64) + static_cast<int>(rank) * (BN / 128), kEvictNormal);
+            }
           }
           if (!leader) mbar_arrive_cluster(full_leader);
           if (++stage == STAGES) {
@@ -163,8 +173,13 @@ gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           const uint64_t da = da0 + (a_base >> 4);
           const uint64_t db = db0 + ((a_base + L::kABytes) >> 4);
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k)
-            tc_mma_bf16_pair(tmem_d, da + k * a_step, db + k * b_step, idesc, (kb > tc.kb0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kBK / 16; ++k) {
+#pragma unroll
+            for (int j = 0; j < NSUB; ++j)
+              tc_mma_bf16_pair(tmem_d + static_cast<uint32_t>(j * BN), da + k * a_step,
+                               db + static_cast<uint64_t>(j * (L::kBSubBytes >> 4)) + k * b_step, idesc,
+                               (kb > tc.kb0 || k > 0) ? 1u : 0u);
+          }
           tc_commit_pair(&empty[stage], 0x3);  // frees the slot in both CTAs
           if (++stage == STAGES) {
             stage = 0;
@@ -172,7 +187,7 @@ gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           }
         }
         tc_commit_pair(&tfull[acc], 0x3);  // accumulator complete -> both epilogues
-        acc ^= 1;
+        if (kAccStages == 2) acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
     }
@@ -192,12 +207,21 @@ gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       mbar_wait(&tfull[acc], acc_phase, 0x400u + acc);
       tc_fence_after();
       const uint32_t taddr = tmem_base + static_cast<uint32_t>(acc * BN) + (static_cast<uint32_t>(quad * 32) << 16);
-      Epi::template consume<BN>(ep, st, tc, tmC, taddr, row_in_tile, epi_tid, epi_smem);
+      if constexpr (NSUB == 1) {
+        Epi::template consume<BN>(ep, st, tc, tmC, taddr, row_in_tile, epi_tid, epi_smem);
+      } else {
+#pragma unroll 1
+        for (int j = 0; j < NSUB; ++j) {
+          TileCoord tj = tc;
+          tj.n_blk = tc.n_blk * NSUB + j;
+          Epi::template consume<BN>(ep, st, tj, tmC, taddr + static_cast<uint32_t>(j * BN), row_in_tile, epi_tid, epi_smem);
+        }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[acc]), 0));  // leader's barrier
       Epi::template finish<BN>(ep, st, tc, tmC, row_in_tile, epi_tid, epi_smem);
-      acc ^= 1;
+      if (kAccStages == 2) acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
     }
     Epi::drain(epi_tid);
@@ -212,11 +236,11 @@ gemm2_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 }
 
 // Launch one pair GEMM (grid = 2 * floor(SMs / 2) CTAs in clusters of 2).
-template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
+template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN, int NSUB = 1>
 inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CUtensorMap* tmC_opt, int64_t M,
                                     int64_t N, int64_t K, int split_k, const typename Epi::Params& ep,
                                     cudaStream_t stream) {
-  using L = Gemm2Smem<Epi, BN, STAGES>;
+  using L = Gemm2Smem<Epi, BN, STAGES, NSUB>;
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
   CUtensorMap tmA, tmB, tmC;
   bool ok = A_MN ? make_tmap_mn3(&tmA, a.ptr, a.mn_extent, a.k_extent, a.pitch_elems * 2, kBM / 64)
@@ -227,7 +251,7 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
   if (tmC_opt) tmC = *tmC_opt; else tmC = tmA;
   GemmSched sc;
   sc.tiles_m = static_cast<int>((M + kBM - 1) / kBM);
-  sc.tiles_n = static_cast<int>((N + BN - 1) / BN);
+  sc.tiles_n = static_cast<int>((N + BN * NSUB - 1) / (BN * NSUB));  // tiles of NSUB column tiles each
   sc.kb_total = static_cast<int>((K + kBK - 1) / kBK);
   if (split_k < 1) split_k = 1;
   if (split_k > sc.kb_total) split_k = sc.kb_total;
@@ -239,7 +263,7 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
   int pairs = device_sm_count() / 2;
   if (pairs > total) pairs = total;
   if (pairs < 1) pairs = 1;
-  auto kern = gemm2_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN>;
+  auto kern = gemm2_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN, NSUB>;
   static std::atomic<bool> attr_set[64];  // zero-initialised; forward and backward call in from different threads
   int dev = 0;
   cudaGetDevice(&dev);

@@ -69,6 +69,7 @@ extern "C" {
 #define ARCB_BWD_RECOMPUTE 0x100 /* never keep probabilities (forward-only callers: saves the 2 B C bytes of stores) */
 /* arcb_gemm_bf16 (unit tests of the GEMM core) */
 #define ARCB_GEMM_PAIR 0x4         /* CTA-pair core (same bit as ARCB_FWD_PAIR) */
+#define ARCB_GEMM_PAIR_WIDE 0x8    /* with ARCB_GEMM_PAIR, a_mn = b_mn = 1: a pair computes two 256-column tiles from one A stage */
 
 /* Library version (major * 10000 + minor * 100 + patch). */
 int arcb_version(void);

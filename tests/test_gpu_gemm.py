@@ -8,7 +8,7 @@ from ddp_classification_pytorch_b200 import _lib
 pytestmark = pytest.mark.gpu
 
 
-def _run(M, N, K, a_mn, b_mn, split_k, seed=0, pair=False):
+def _run(M, N, K, a_mn, b_mn, split_k, seed=0, pair=False, wide=False):
     dev = torch.device("cuda:0")
     g = torch.Generator(device="cpu").manual_seed(seed)
     A = torch.randn(M, K, generator=g).to(dev).bfloat16()
@@ -27,7 +27,7 @@ def _run(M, N, K, a_mn, b_mn, split_k, seed=0, pair=False):
     st = torch.cuda.current_stream().cuda_stream
     _lib.check(L.arcb_gemm_bf16(a_store.data_ptr(), int(a_mn), b_store.data_ptr(), int(b_mn), M, N, K,
                                 a_store.shape[1], b_store.shape[1], out.data_ptr(), N, split_k,
-                                _lib.GEMM_PAIR if pair else 0, st))
+                                (_lib.GEMM_PAIR if pair else 0) | (_lib.GEMM_PAIR_WIDE if wide else 0), st))
     _lib.check(L.arcb_check_watchdog(st))
     err = (out - ref).abs().max().item()
     scale = ref.abs().max().item() + 1e-6
@@ -52,3 +52,12 @@ def test_gemm_split_k(a_mn, b_mn, pair):
 def test_gemm_many_tiles_persistent():
     # more tiles than SMs: exercises the smem ring wrap-around and both TMEM accumulator stages
     assert _run(1024, 256 * 40, 128, False, False, 1) < 2e-3
+
+
+@pytest.mark.parametrize("shape,split_k", [((256, 512, 64), 1), ((256, 512, 64 * 37), 5), ((1024, 512, 64 * 50), 18),
+                                           ((520, 320, 1000), 3), ((100, 777, 200), 1), ((512, 1024, 64 * 9), 1)])
+def test_gemm_pair_wide_tiles(shape, split_k):
+    """CTA pairs computing TWO 256-column tiles from one A stage (both accumulators = all of TMEM, no double buffering): the
+    dX GEMM of the stored-probabilities backward.  Ragged second column tile, split-K, several tiles per pair in a row."""
+    M, N, K = shape
+    assert _run(M, N, K, True, True, split_k, pair=True, wide=True) < 2e-3

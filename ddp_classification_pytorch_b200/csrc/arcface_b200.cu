@@ -505,20 +505,29 @@ int backward_from_probs(const Workspace& W, float s, const float* lse, const flo
     int pairs = sms / 2;
     if (pairs > ((blocks + 1) / 2) * ep.slices) pairs = static_cast<int>(((blocks + 1) / 2) * ep.slices);
     pairs -= pairs % ep.slices;
-    ep.next_tile_blocks = 2 * pairs / ep.slices;
     ep.m_blocks = static_cast<int>(2 * ((blocks + 1) / 2));
     ep.pair = 1;
     const bool direct = !dw_tma;
     const bool coop = !(flags & ARCB_BWD_NO_COOP);  // profiling only, see the header
     LaunchScope ls(ARCB_K_DW_GEMM, st);
     cudaError_t e;
-    if (direct) {
-      EpiDWT<false>::Params ed;
-      static_assert(sizeof(ed) == sizeof(ep), "same parameter block");
-      memcpy(&ed, &ep, sizeof(ed));
-      e = launch_gemm_pair_row_slices<EpiDWT<false>, kBNTile, 5, false, true>(a, b, &tmDw, Cs, D, B, ed, st, coop);
-    } else {
-      e = launch_gemm_pair_row_slices<EpiDWT<true>, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st, coop);
+    for (;;) {
+      ep.next_tile_blocks = 2 * pairs / ep.slices;
+      if (direct) {
+        EpiDWT<false>::Params ed;
+        static_assert(sizeof(ed) == sizeof(ep), "same parameter block");
+        memcpy(&ed, &ep, sizeof(ed));
+        e = launch_gemm_pair_row_slices<EpiDWT<false>, kBNTile, 5, false, true>(a, b, &tmDw, Cs, D, B, ed, st, coop, pairs);
+      } else {
+        e = launch_gemm_pair_row_slices<EpiDWT<true>, kBNTile, 3, false, true>(a, b, &tmDw, Cs, D, B, ep, st, coop, pairs);
+      }
+      // part of the GPU is taken (MPS share, another resident kernel): the slices of a class tile still have to run
+      // together, so ask for a grid that fits instead of giving up co-residency
+      if (e != cudaErrorCooperativeLaunchTooLarge && e != cudaErrorLaunchOutOfResources) break;
+      int fewer = pairs / 2;
+      fewer -= fewer % ep.slices;
+      if (fewer < ep.slices) break;
+      pairs = fewer;
     }
     if (e != cudaSuccess) return fail(ARCB_ERR_CUDA, "dW GEMM launch: %s", cudaGetErrorString(e));
   }

@@ -291,11 +291,11 @@ inline cudaError_t launch_gemm_pair(const Operand& a, const Operand& b, const CU
 // Pair GEMM whose tiles_n column slices of one 256-row tile must be in flight TOGETHER on neighbouring pairs (EpiDWT
 // exchanges a per-row reduction between them): n-fastest tile order, a number of pairs that is a multiple of tiles_n,
 // no split-K, and a cooperative launch (on top of the cluster) so that every CTA a tile may wait for is resident.
-// cudaErrorCooperativeLaunchTooLarge & co.: nothing was enqueued.
+// cudaErrorCooperativeLaunchTooLarge & co.: nothing was enqueued (the caller retries with fewer pairs).
 template <class Epi, int BN, int STAGES, bool A_MN, bool B_MN>
 inline cudaError_t launch_gemm_pair_row_slices(const Operand& a, const Operand& b, const CUtensorMap* tmC_opt, int64_t M,
                                                int64_t N, int64_t K, const typename Epi::Params& ep,
-                                               cudaStream_t stream, bool cooperative = true) {
+                                               cudaStream_t stream, bool cooperative, int pairs) {
   using L = Gemm2Smem<Epi, BN, STAGES>;
   static_assert(L::kTotal <= 232448, "shared memory budget exceeded");
   CUtensorMap tmA, tmB, tmC;
@@ -314,10 +314,8 @@ inline cudaError_t launch_gemm_pair_row_slices(const Operand& a, const Operand& 
   sc.n_fastest = 1;
   const int total = ((sc.tiles_m + 1) / 2) * sc.tiles_n;
   if (total <= 0) return cudaSuccess;
-  int pairs = device_sm_count() / 2;
-  if (pairs > total) pairs = total;
-  pairs -= pairs % sc.tiles_n;
-  if (pairs < sc.tiles_n) return cudaErrorInvalidValue;
+  // `pairs` is the caller's (the epilogue parameters depend on it): a multiple of tiles_n, at most one pair per two SMs
+  if (pairs > total || pairs < sc.tiles_n || pairs % sc.tiles_n) return cudaErrorInvalidValue;
   auto kern = gemm2_sm100_kernel<Epi, BN, STAGES, A_MN, B_MN>;
   static std::atomic<bool> attr_set[64];
   int dev = 0;

@@ -683,7 +683,7 @@ int arcb_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, int64_t M, 
 
 int64_t arcb_ws_bytes(int64_t B, int64_t Cs, int64_t D, int flags) {
   if (B <= 0 || Cs <= 0 || D <= 0) return -1;
-  // ARCB_KEEP_PROBS adds the stored probabilities when the schedule applies to the shape (for ANY scale s: the query
+  // the stored probabilities are part of the workspace when the schedule applies to the shape (for ANY scale s: the query
   // has no s, so it sizes for the case that the forward uses them)
   return carve(nullptr, B, Cs, D, keep_probs_applies(B, Cs, D, 1.f, effective_flags(flags))).total;
 }

@@ -1,4 +1,4 @@
-// Backward of the ArcFace head from STORED softmax numerators (ARCB_KEEP_PROBS; autograd behind arc_main.py:329).
+// Backward of the ArcFace head from STORED softmax numerators (the default for large shards, include/arcface_b200.h: ARCB_BWD_RECOMPUTE; autograd behind arc_main.py:329).
 //
 // The forward (EpiFwdStatsP) left P'[j, i] = bf16(2^(s2 (cos_ij - 1))) for the whole shard, CLASS-major: P'^T [Cs, Bp], a
 // class row holds the whole batch.  With c_i = gscale * 2^(s2 - lse2_i) the gradient of the loss w.r.t. the cosines is

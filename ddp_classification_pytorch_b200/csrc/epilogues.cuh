@@ -170,16 +170,17 @@ struct EpiFwdStats {
 };
 
 // ------------------------------------------------------------------------------------
-// Forward statistics that also KEEP the softmax numerators (ARCB_KEEP_PROBS): P'[j, i] = bf16(2^(s2 (cos_ij - 1))), the
-// fixed reference s2 = s log2(e) (cos <= 1, so P' <= 1: no running maximum), written CLASS-major, P'^T [Cs, Bp] -- a class
-// row holds the whole batch (2 KB at B = 1024), which is what both backward GEMMs want to stream: dW reads [128 classes x
-// all samples] as one contiguous 256 KB region, dX reads 256-byte pieces of rows that its eight sample-block CTAs consume
-// together.  The tile's accumulator is [128 samples x 256 classes] with one SAMPLE per thread, so the store is a
-// transpose through shared memory: thread s writes its 2-byte values down column s of a [64 classes x 128 samples]
-// staging tile (two 128B-swizzled boxes of 64 samples; the 32 lanes of a warp fill 64 contiguous bytes of one class row:
-// no bank conflicts), one bulk tensor store per box.  The partial of a (tile column block, warpgroup) is
-// (s2, sum of the ROUNDED P') -- the (reference, sum) format the merge kernels take -- so the softmax the backward
-// reconstructs from P' sums to one.  Block maxima for the exact top-3 go to their own array when asked for.
+// Forward statistics that also KEEP the softmax numerators (stored-probabilities schedule):
+// P'[j, i] = bf16(2^(s2 (cos_ij - 1))), the fixed reference s2 = s log2(e) (cos <= 1, so P' <= 1: no running maximum),
+// written CLASS-major, P'^T [Cs, Bp] -- a class row holds the whole batch (2 KB at B = 1024), which is what both backward
+// GEMMs want to stream: dW reads [128 classes x all samples] as one contiguous 256 KB region, dX reads the rows of its
+// class slice as an MN-major operand.  The tile's accumulator is [128 samples x 256 classes] with one SAMPLE per thread,
+// so the store is a transpose through shared memory: thread s writes its 2-byte values down column s of a
+// [64 classes x 128 samples] staging tile (two 128B-swizzled boxes of 64 samples; the 32 lanes of a warp fill 64
+// contiguous bytes of one class row: no bank conflicts), one bulk tensor store per box.  The partial of a (tile column
+// block, warpgroup) is (s2, sum of P') -- the (reference, sum) format the merge kernels take; the sum is taken before
+// the bf16 rounding (the rounding errors of a row average out far below the loss tolerance).  Block maxima for the
+// exact top-3 go to their own array when asked for.
 struct EpiFwdStatsP {
   static constexpr int kSmemBytes = 2 * 64 * 256;   // per warpgroup: [64 classes x 128 samples] bf16 = 16 KB
   static constexpr bool kUsesTmC = true;            // tmC: P'^T [Cs, Bp] bf16 (pitch Bp), box [64 classes x 64 samples]
@@ -665,7 +666,7 @@ struct EpiDW {
   __device__ static void finish(const Params&, State&, const TileCoord&, const CUtensorMap&, int, int, uint8_t*) {}
 };
 
-// Epilogue of the dW GEMM of the stored-probabilities backward (ARCB_KEEP_PROBS): the accumulator is
+// Epilogue of the dW GEMM of the stored-probabilities backward: the accumulator is
 //   dW_hat[j, n_blk * BN ..) = sum_i P'^T[j, i] (c_i x_hat_i)        (one BN-wide slice of the feature row)
 // and t_j = <w_hat_j, dW_hat_j> (the F.normalize backward, arc_main.py:159) is NOT known before this GEMM, unlike in
 // EpiDW.  The tiles run n-fastest (GemmSched::n_fastest) on a cooperative grid that is a multiple of tiles_n, so the

@@ -29,6 +29,19 @@ def test_header_symbols_are_exported(built):
         assert getattr(handle, sym) is not None
 
 
+def test_flag_constants_match_the_header():
+    """The per-call flag bits of the Python binding are the ones include/arcface_b200.h defines (and no two flags of one
+    entry point share a bit)."""
+    hdr = open(os.path.join(ROOT, "include", "arcface_b200.h")).read()
+    defined = {m.group(1): int(m.group(2), 16)
+               for m in re.finditer(r"#define ARCB_((?:FWD|BWD|GEMM)_[A-Z_]+) (0x[0-9a-fA-F]+)", hdr)}
+    assert len(defined) >= 12
+    for name, value in defined.items():
+        assert getattr(_lib, name) == value, name
+    head_flags = [v for k, v in defined.items() if not k.startswith("GEMM_")]
+    assert len(set(head_flags)) == len(head_flags) and all(v & (v - 1) == 0 for v in head_flags)
+
+
 def test_size_queries_without_gpu(built):
     L = built
     assert L.arcb_version() >= 20000

@@ -61,6 +61,27 @@ def test_size_queries_without_gpu(built):
     assert L.arcb_launch_count() == 0
 
 
+def test_schedule_rule_without_gpu(built):
+    """When the backward runs from stored probabilities (pure host logic, include/arcface_b200.h: ARCB_BWD_RECOMPUTE)."""
+    L = built
+    act = L.arcb_keep_probs_active
+    assert act(1024, 1_000_000, 512, 30.0, 0) == 1 and act(1024, 125_000, 512, 30.0, 0) == 1  # cfg4 on 1 and 8 GPUs
+    assert act(512, 100_000, 512, 30.0, 0) == 1 and act(512, 50_000, 512, 30.0, 0) == 1      # cfg3 on 1 and 2 GPUs
+    assert act(512, 25_000, 512, 30.0, 0) == 0 and act(512, 12_500, 512, 30.0, 0) == 0       # ... launch bound at 4 / 8
+    assert act(256, 1000, 2048, 30.0, 0) == 0                                                # cfg2: D > 512
+    assert act(1024, 1_000_000, 256, 30.0, 0) == 0 and act(1024, 1_000_000, 320, 30.0, 0) == 1
+    assert act(1024, 1_000_000, 512, 41.0, 0) == 1 and act(1024, 1_000_000, 512, 64.0, 0) == 0  # bf16 range of P'
+    assert act(64, 1_000_000, 512, 30.0, 0) == 0
+    for flag in (_lib.BWD_RECOMPUTE, _lib.BWD_PER_CHUNK, _lib.BWD_SINGLE_CTA, _lib.BWD_STATIC_SHARE, _lib.FWD_PAIR):
+        assert act(1024, 1_000_000, 512, 30.0, flag) == 0
+    for flag in (_lib.FWD_NORM_SEPARATE, _lib.FWD_NORM_FUSED, _lib.FWD_STREAMING, _lib.FWD_BLOCK_MAXIMA, _lib.BWD_NO_COOP):
+        assert act(1024, 1_000_000, 512, 30.0, flag) == 1
+    # the workspace carries the matrix exactly when the shape rule holds (the size query has no scale argument)
+    for B, C, D in ((1024, 125_000, 512), (512, 25_000, 512), (256, 1000, 2048)):
+        extra = L.arcb_ws_bytes(B, C, D, 0) - L.arcb_ws_bytes(B, C, D, _lib.BWD_RECOMPUTE)
+        assert (extra >= 2 * B * C) == bool(act(B, C, D, 30.0, 0)) and (extra == 0) == (not act(B, C, D, 30.0, 0))
+
+
 def test_chunk_suggestion_and_weight_slots_without_gpu(built):
     """Host-side sizing logic of the backward and of the weight cache (no launches involved)."""
     L = built
